@@ -1,0 +1,200 @@
+/* ptb200.h -- C ABI of the B200-native wavefront path tracer (libptb200.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of HugoPeters1024/cuda_pathtracer:
+ *   class Application { Init(); Render(const Camera&, float, float, bool shouldClear); Finish(); }
+ *   (reference src/application.h:7-20, implemented by Pathtracer, src/pathtracer.h:46-310).
+ * The reference has no FFI; its host code hands the kernels a by-value `SceneBuffers`
+ * (src/types.h:689-703), a `Camera` (src/types.h:586-677) and a `RandState` (src/types.h:679-687).
+ * Every POD struct below is layout-compatible with the reference struct it cites (sizes and
+ * offsets are pinned against the reference's own headers by tests/test_abi.py), so reference-side
+ * host code can pass its arrays straight through.  All entry points return 0 on success or a
+ * negative pt_status; nothing here calls exit() (the reference's cudaSafe does, use_cuda.h:32-40).
+ * There is no CPU fallback behind this ABI: every compute entry point needs a CUDA device.
+ */
+#ifndef PTB200_H
+#define PTB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PT_ALIGN(n) __attribute__((aligned(n)))
+#define PT_API __attribute__((visibility("default")))
+#else
+#define PT_ALIGN(n)
+#define PT_API
+#endif
+
+typedef enum {
+    PT_OK = 0,
+    PT_ERR_INVALID = -1,   /* bad argument / call order */
+    PT_ERR_CUDA = -2,      /* a CUDA runtime call failed; see pt_last_error */
+    PT_ERR_NO_DEVICE = -3, /* no CUDA device: there is no CPU fallback */
+    PT_ERR_OOM = -4,
+    PT_ERR_IO = -5
+} pt_status;
+
+/* ---- POD mirrors of the reference structs (src/types.h) -------------------------------------- */
+typedef struct { float x, y, z; } pt_float3;            /* CUDA float3: 12 B, align 4 */
+typedef struct PT_ALIGN(8) { float x, y; } pt_float2;   /* CUDA float2: 8 B, align 8  */
+typedef struct PT_ALIGN(16) { float x, y, z, w; } pt_float4;
+
+/* Material, src/types.h:33-56 (88 B, align 8).  `texture`/`normal_texture` are CUDA texture
+ * object handles valid in the calling process (cudaTextureObject_t, or pt_texture_create). */
+typedef struct {
+    pt_float3 diffuse_color;
+    pt_float3 specular_color;
+    pt_float3 emission;
+    float reflect, glossy, transmit, refractive_index;
+    pt_float3 absorption;
+    uint64_t texture;
+    uint64_t normal_texture;
+    uint8_t hasTexture, hasNormalMap;
+    uint8_t _pad[6];
+} pt_material;
+
+typedef struct { pt_float3 pos; float radius; uint32_t material; } pt_sphere;   /* types.h:58-69  */
+typedef struct { pt_float3 normal; float d; uint32_t material; } pt_plane;      /* types.h:124-133 */
+
+typedef struct PT_ALIGN(16) { pt_float3 v0, v1, v2; uint32_t _pad[3]; } pt_triangle_v;   /* types.h:79-83, 48 B */
+typedef struct PT_ALIGN(16) {                                                            /* types.h:85-96, 80 B */
+    pt_float3 normal, tangent, bitangent;
+    pt_float2 uv0, uv1, uv2;
+    uint32_t material;
+} pt_triangle_d;
+
+typedef struct PT_ALIGN(16) {          /* RadianceCache, types.h:98-104, 112 B */
+    float radianceCache[8];
+    float additionCache[8];
+    float additionCacheCount[8];
+    float radianceTotal;
+} pt_radiance_cache;
+
+typedef struct { uint32_t triangle_index, instance_index; } pt_triangle_light;   /* types.h:106-110 */
+
+typedef struct PT_ALIGN(16) { pt_float4 origin; pt_float4 direction; } pt_ray;   /* RayPacked, types.h:273-294:
+                                            origin.w = length (tmax), direction.w = pixel index (uint bits) */
+typedef struct PT_ALIGN(16) {          /* HitInfo / HitInfoPacked, types.h:299-334 */
+    uint32_t primitive_type;           /* 0 TRIANGLE, 1 SPHERE, 2 PLANE (types.h:296) */
+    uint32_t primitive_id;             /* 0xffffffff = miss */
+    uint32_t instance_id;
+    float t;
+} pt_hit;
+
+typedef struct PT_ALIGN(16) {          /* SampleCache, types.h:339-345 */
+    uint32_t sample_type;              /* 0 IGNORE, 1 TERMINATE, 2 BUCKET (types.h:337) */
+    uint32_t triangle_id;
+    int32_t cache_bucket_id;
+    pt_float3 cum_mask;
+} pt_sample_cache;
+
+typedef struct PT_ALIGN(16) { pt_float4 vmin; pt_float4 vmax; } pt_bvh_node;   /* BVHNode, types.h:347-375:
+                                            vmin.w = child1 | t_start (uint bits), vmax.w = t_count (leaf iff > 0) */
+typedef struct PT_ALIGN(16) {          /* Model, types.h:377-383 */
+    const pt_bvh_node* bvh;
+    uint32_t triangleStart, nrTriangles, nrBvhNodes;
+} pt_model;
+
+typedef struct { pt_float4 r1, r2, r3; } pt_mat4x3;     /* types.h:385-406, rows of the 3x4 matrix */
+typedef struct PT_ALIGN(16) {          /* Instance, types.h:408-414, 128 B */
+    uint32_t model_id;
+    pt_mat4x3 transform;
+    pt_mat4x3 invTransform;
+    uint32_t material_id;              /* 0xffffffff => per-triangle material */
+} pt_instance;
+
+typedef struct PT_ALIGN(16) {          /* TopLevelBVH, types.h:431-459, 32 B */
+    pt_float3 vmin, vmax;
+    uint32_t children;                 /* child1 | child2 << 16; 0 => leaf */
+    uint32_t leaf;
+} pt_tlas_node;
+
+typedef struct {                       /* Camera, types.h:586-677, 76 B (first member is the private bool) */
+    uint32_t _has_moved;
+    pt_float3 eye, viewDir;
+    pt_float3 lt, u, v;
+    float d, focalLength, aperture;
+} pt_camera;
+
+/* Host-pointer scene description == what Pathtracer::Init uploads (src/pathtracer.h:129-190,216-217).
+ * Mirrors SceneBuffers (types.h:689-703) + the host vectors of Scene (scene.h:124-133). */
+typedef struct {
+    const pt_triangle_v* vertices;     /* post-permute, global triangle order */
+    const pt_triangle_d* vertexData;
+    uint32_t num_triangles;
+    const pt_model* models;            /* bvh = HOST pointers to the per-model BVH2 (createBVHBinned output) */
+    uint32_t num_models;
+    const pt_material* materials;
+    uint32_t num_materials;
+    const pt_instance* instances;
+    uint32_t num_instances;
+    const pt_tlas_node* topBvh;        /* 2*num_instances-1 nodes (scene.h:358) */
+    uint32_t num_tlas_nodes;
+    const pt_sphere* spheres;
+    uint32_t num_spheres;
+    const pt_plane* planes;
+    uint32_t num_planes;
+} pt_scene_desc;
+
+/* Run-time replacement for the reference's compile-time constants (src/constants.h:4-14). */
+typedef struct {
+    uint32_t width, height;            /* WINDOW_WIDTH / WINDOW_HEIGHT */
+    uint32_t max_ray_depth;            /* MAX_RAY_DEPTH (reference: 32) */
+    uint32_t interactive_depth;        /* Scene::interactive_depth (scene.h:137) */
+    uint32_t guiding_frames;           /* frames during which the radiance cache trains (pathtracer.h:292: 100) */
+    uint32_t blue_noise_frames;        /* rand() uses blue noise while sampleIdx < this (kernels.h:23: 1) */
+    int32_t device;                    /* CUDA device ordinal */
+    uint32_t rank, world_size;         /* tile partition: this context renders tiles t with t % world_size == rank */
+    uint32_t flags;                    /* PT_FLAG_* */
+} pt_config;
+#define PT_FLAG_DEFAULT 0u
+
+typedef struct {                       /* device-side ray counters since the last pt_reset_stats */
+    uint64_t primary_rays, extend_rays, shadow_rays, shade_calls, samples;
+} pt_stats;
+
+typedef struct pt_ctx pt_ctx;
+
+/* Called between the local radiance-cache update and the propagate step of a training frame
+ * (north_star: NCCL all-reduce of additionCache||additionCacheCount).  `dev_additions` is a device
+ * pointer to 16*num_triangles floats (SoA: [16][num_triangles]); the hook must enqueue an in-place
+ * SUM all-reduce on `cuda_stream`. */
+typedef int (*pt_allreduce_hook)(void* user, float* dev_additions, size_t count, void* cuda_stream);
+
+PT_API const char* pt_version(void);
+PT_API void pt_default_config(pt_config* cfg);
+PT_API int  pt_create(pt_ctx** out, const pt_config* cfg);          /* ~ Pathtracer ctor + allocation half of Init() (pathtracer.h:192-209) */
+PT_API void pt_destroy(pt_ctx* ctx);
+PT_API const char* pt_last_error(const pt_ctx* ctx);                /* ctx may be NULL: last create error */
+
+PT_API int  pt_upload_scene(pt_ctx*, const pt_scene_desc*);         /* ~ upload half of Init() (pathtracer.h:129-190,216-220) */
+PT_API int  pt_update_instances(pt_ctx*, const pt_instance*, uint32_t n, const pt_tlas_node*, uint32_t n_nodes); /* pathtracer.h:245-246 */
+PT_API int  pt_set_toggles(pt_ctx*, int nee, int guiding);          /* HNEE / HCACHE (globals.h:19-20); takes effect on the next should_clear render (pathtracer.h:242-243) */
+PT_API int  pt_set_skydome(pt_ctx*, const float* rgba, uint32_t w, uint32_t h);   /* ~ loadTextureHDR (use_cuda.h:202-263): rows already flipped */
+PT_API int  pt_set_blue_noise(pt_ctx*, const float* lum, uint32_t w, uint32_t h); /* ~ loadTextureL (use_cuda.h:166-200) */
+PT_API int  pt_texture_create(pt_ctx*, const float* rgba, uint32_t w, uint32_t h, uint64_t* out_handle); /* ~ loadTexture (use_cuda.h:108-164) */
+PT_API int  pt_set_allreduce_hook(pt_ctx*, pt_allreduce_hook hook, void* user);
+
+PT_API int  pt_render(pt_ctx*, const pt_camera*, int should_clear);   /* == Pathtracer::Render (pathtracer.h:224-302); asynchronous */
+PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
+PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
+PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
+PT_API int  pt_get_stats(pt_ctx*, pt_stats* out);
+PT_API int  pt_reset_stats(pt_ctx*);
+PT_API int  pt_get_rand_state(pt_ctx*, uint32_t* sampleIdx, uint32_t* randIdx);
+
+/* Stage-level parity hooks (host buffers in, host buffers out; pixel index = RayPacked.direction.w). */
+PT_API int  pt_debug_primary_rays(pt_ctx*, const pt_camera*, uint32_t randIdx, pt_ray* host_out /* width*height, indexed by pixel */);
+PT_API int  pt_debug_trace(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, pt_hit* host_out);
+/* Device-resident variant used for kernel-only timing: rays stay in HBM, returns elapsed ms (CUDA events). */
+PT_API int  pt_debug_trace_resident(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, uint32_t repeats, float* out_ms, pt_hit* host_out);
+
+PT_API void* pt_cuda_stream(pt_ctx*);   /* the stream every launch of this context goes to */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB200_H */
