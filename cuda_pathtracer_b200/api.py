@@ -1,0 +1,209 @@
+"""Host-side mirror of the reference's operator surface over the C ABI (include/ptb200.h).
+
+``Pathtracer`` has the shape of the reference's ``class Pathtracer : public Application``
+(reference src/application.h:7-20, src/pathtracer.h:46-310): ``Init()``, ``Render(camera, currentTime,
+frameTime, shouldClear)``, ``Finish()``, plus the two host toggles HNEE / HCACHE (src/globals.h:19-20).
+There is no CPU fallback: loading fails loudly when libptb200.so is missing, and pt_create fails
+loudly without a CUDA device.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class PtError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "libptb200.so")
+
+
+def load_library():
+    """Load libptb200.so (built in-tree by __graft_entry__.build()).  Raises if it is missing."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    p = lib_path()
+    if not os.path.exists(p):
+        raise PtError("libptb200.so not found at %s -- run __graft_entry__.build(); there is no fallback path" % p)
+    L = C.CDLL(p)
+    L.pt_version.restype = C.c_char_p
+    L.pt_last_error.restype = C.c_char_p
+    L.pt_last_error.argtypes = [C.c_void_p]
+    L.pt_cuda_stream.restype = C.c_void_p
+    L.pt_cuda_stream.argtypes = [C.c_void_p]
+    L.pt_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(abi.Config)]
+    L.pt_destroy.argtypes = [C.c_void_p]
+    L.pt_destroy.restype = None
+    L.pt_upload_scene.argtypes = [C.c_void_p, C.POINTER(abi.SceneDesc)]
+    L.pt_update_instances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+    L.pt_set_toggles.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.pt_set_skydome.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    L.pt_set_sky_constant.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float]
+    L.pt_set_blue_noise.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    L.pt_texture_create.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+    L.pt_set_allreduce_hook.argtypes = [C.c_void_p, abi.ALLREDUCE_HOOK, C.c_void_p]
+    L.pt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    L.pt_finish.argtypes = [C.c_void_p]
+    L.pt_read_image.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    L.pt_read_radiance_cache.argtypes = [C.c_void_p, C.c_void_p]
+    L.pt_get_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
+    L.pt_reset_stats.argtypes = [C.c_void_p]
+    L.pt_get_rand_state.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    L.pt_debug_primary_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.pt_debug_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+    L.pt_debug_trace_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.POINTER(C.c_float), C.c_void_p]
+    _LIB = L
+    return L
+
+
+class Pathtracer:
+    """Drop-in for the reference's Pathtracer application object.
+
+    scene: dict of numpy arrays (abi.make_scene_desc keys) -- the host vectors of the reference's
+    ``Scene`` (src/scene.h:124-133) -- or a ``cuda_pathtracer_b200.scene.Scene``.
+    """
+
+    def __init__(self, scene, config=None):
+        self.L = load_library()
+        self.cfg = config if config is not None else abi.default_config()
+        self.scene = scene
+        self.h = None
+        self.HNEE = True      # globals.h:19, set in Init (pathtracer.h:213)
+        self.HCACHE = True    # globals.h:20, set in Init (pathtracer.h:214)
+        self._keep = []
+        self._hook = None
+
+    # -- error plumbing --
+    def _ck(self, r, what):
+        if r < 0:
+            msg = self.L.pt_last_error(self.h)
+            raise PtError("%s failed (%d): %s" % (what, r, (msg or b"").decode()))
+        return r
+
+    def _arrays(self):
+        return self.scene.arrays() if hasattr(self.scene, "arrays") else self.scene
+
+    # -- Application interface --
+    def Init(self):
+        h = C.c_void_p()
+        r = self.L.pt_create(C.byref(h), C.byref(self.cfg))
+        if r < 0:
+            raise PtError("pt_create failed (%d): %s" % (r, (self.L.pt_last_error(None) or b"").decode()))
+        self.h = h
+        desc, keep = abi.make_scene_desc(self._arrays())
+        self._keep.append(keep)
+        self.num_lights = self._ck(self.L.pt_upload_scene(self.h, C.byref(desc)), "pt_upload_scene")
+        self.num_triangles = desc.num_triangles
+        self.HNEE = True
+        self.HCACHE = True
+        return self
+
+    def Render(self, camera, currentTime=0.0, frameTime=0.0, shouldClear=False):
+        """camera: numpy record of abi.CAMERA (lt/u/v prepared like Camera::recalculate, types.h:590-600)."""
+        if shouldClear:
+            # pathtracer.h:242-246: toggles and instances/TLAS are re-synced only on a clearing frame
+            self._ck(self.L.pt_set_toggles(self.h, int(self.HNEE), int(self.HCACHE)), "pt_set_toggles")
+            a = self._arrays()
+            if len(a["instances"]):
+                inst = np.ascontiguousarray(a["instances"])
+                tlas = np.ascontiguousarray(a["topBvh"])
+                self._ck(self.L.pt_update_instances(self.h, abi.ptr(inst), len(inst), abi.ptr(tlas), len(tlas)), "pt_update_instances")
+        cam = np.ascontiguousarray(camera)
+        self._ck(self.L.pt_render(self.h, abi.ptr(cam), int(bool(shouldClear))), "pt_render")
+
+    def Finish(self):
+        self._ck(self.L.pt_finish(self.h), "pt_finish")
+
+    # -- headless replacements for the GL textures --
+    def read_image(self, which=0, out=None):
+        if out is None:
+            out = np.empty((self.cfg.height, self.cfg.width, 4), np.float32)
+        self._ck(self.L.pt_read_image(self.h, abi.ptr(out), which), "pt_read_image")
+        return out
+
+    def read_radiance_cache(self):
+        out = np.zeros(self.num_triangles, abi.RADIANCE_CACHE)
+        self._ck(self.L.pt_read_radiance_cache(self.h, abi.ptr(out)), "pt_read_radiance_cache")
+        return out
+
+    # -- environment --
+    def set_skydome(self, rgba):
+        rgba = np.ascontiguousarray(rgba, np.float32)
+        self._ck(self.L.pt_set_skydome(self.h, abi.ptr(rgba), rgba.shape[1], rgba.shape[0]), "pt_set_skydome")
+
+    def set_sky_constant(self, r, g, b):
+        self._ck(self.L.pt_set_sky_constant(self.h, r, g, b), "pt_set_sky_constant")
+
+    def set_blue_noise(self, lum):
+        lum = np.ascontiguousarray(lum, np.float32)
+        self._ck(self.L.pt_set_blue_noise(self.h, abi.ptr(lum), lum.shape[1], lum.shape[0]), "pt_set_blue_noise")
+
+    def create_texture(self, rgba):
+        rgba = np.ascontiguousarray(rgba, np.float32)
+        out = C.c_uint64()
+        self._ck(self.L.pt_texture_create(self.h, abi.ptr(rgba), rgba.shape[1], rgba.shape[0], C.byref(out)), "pt_texture_create")
+        return out.value
+
+    def set_allreduce_hook(self, fn):
+        """fn(dev_ptr:int, count:int, stream:int) -> 0 on success; called once per guiding-training frame."""
+        if fn is None:
+            self._hook = abi.ALLREDUCE_HOOK(0)
+        else:
+            self._hook = abi.ALLREDUCE_HOOK(lambda user, p, n, s: int(fn(p or 0, n, s or 0)))
+        self._ck(self.L.pt_set_allreduce_hook(self.h, self._hook, None), "pt_set_allreduce_hook")
+
+    # -- statistics / stage hooks --
+    def stats(self):
+        st = abi.Stats()
+        self._ck(self.L.pt_get_stats(self.h, C.byref(st)), "pt_get_stats")
+        return st
+
+    def reset_stats(self):
+        self._ck(self.L.pt_reset_stats(self.h), "pt_reset_stats")
+
+    def rand_state(self):
+        a, b = C.c_uint32(), C.c_uint32()
+        self.L.pt_get_rand_state(self.h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def stream(self):
+        return self.L.pt_cuda_stream(self.h)
+
+    def debug_primary_rays(self, camera, rand_idx):
+        out = np.zeros(self.cfg.width * self.cfg.height, abi.RAY)
+        cam = np.ascontiguousarray(camera)
+        self._ck(self.L.pt_debug_primary_rays(self.h, abi.ptr(cam), rand_idx, abi.ptr(out)), "pt_debug_primary_rays")
+        return out
+
+    def debug_trace(self, rays, any_hit=False):
+        rays = np.ascontiguousarray(rays)
+        out = np.zeros(len(rays), abi.HIT)
+        self._ck(self.L.pt_debug_trace(self.h, abi.ptr(rays), len(rays), int(any_hit), abi.ptr(out)), "pt_debug_trace")
+        return out
+
+    def debug_trace_timed(self, rays, any_hit=False, repeats=5):
+        rays = np.ascontiguousarray(rays)
+        out = np.zeros(len(rays), abi.HIT)
+        ms = C.c_float()
+        self._ck(self.L.pt_debug_trace_resident(self.h, abi.ptr(rays), len(rays), int(any_hit), repeats, C.byref(ms), abi.ptr(out)),
+                 "pt_debug_trace_resident")
+        return out, ms.value
+
+    def close(self):
+        if self.h:
+            self.L.pt_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

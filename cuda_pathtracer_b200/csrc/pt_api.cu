@@ -1,0 +1,501 @@
+// pt_api.cu -- context + C ABI of libptb200.so (include/ptb200.h).  Host orchestration of the
+// wavefront stages == what reference src/pathtracer.h:73-310 (Pathtracer::Init/Render/Finish) does,
+// minus the GL interop (headless float4 device images instead of GL textures).
+// Compiled for sm_100a only; every compute entry point fails loudly without a CUDA device.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "pt_kernels.cuh"
+#include "wide_bvh.h"
+
+using namespace ptb;
+
+static thread_local std::string g_createError;
+
+struct pt_ctx {
+    pt_config cfg;
+    std::string err;
+    cudaStream_t stream = nullptr;
+    int numSMs = 0;
+    TileMap map;
+    Queues q;
+    float4 *masks = nullptr, *accucolors = nullptr, *lights = nullptr;
+    pt_sample_cache* sampleCache = nullptr;
+    float4 *image = nullptr, *albedo = nullptr;
+    unsigned long long* stats = nullptr;
+    // scene
+    DScene sc;
+    bool haveScene = false;
+    std::vector<void*> sceneAllocs;
+    uint32_t numInstancesCap = 0, numTlasCap = 0;
+    // textures
+    FrameTex tex;
+    std::vector<cudaArray_t> arrays;
+    std::vector<cudaTextureObject_t> textures;
+    // state mirrored from Pathtracer
+    bool HNEE = true, HCACHE = true;      // pathtracer.h:213-214
+    bool DNEE = false, DCACHE = false;    // __constant__ copies, synced on shouldClear (pathtracer.h:242-243)
+    uint32_t sampleIdx = 0, randIdx = 0;
+    pt_allreduce_hook hook = nullptr;
+    void* hookUser = nullptr;
+    int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0;
+    // debug buffers
+    pt_ray* dbgRays = nullptr; pt_hit* dbgHits = nullptr; uint32_t dbgCap = 0; uint* dbgCursor = nullptr;
+};
+
+#define CK(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) {                                                                          \
+            char buf_[512];                                                                               \
+            snprintf(buf_, sizeof(buf_), "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            ctx->err = buf_;                                                                              \
+            return e_ == cudaErrorMemoryAllocation ? PT_ERR_OOM : PT_ERR_CUDA;                            \
+        }                                                                                                 \
+    } while (0)
+
+static int fail(pt_ctx* ctx, int code, const char* msg) { ctx->err = msg; return code; }
+
+template <typename T>
+static int devAlloc(pt_ctx* ctx, T** p, size_t n, bool sceneOwned) {
+    *p = nullptr;
+    CK(cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T)));
+    if (sceneOwned) ctx->sceneAllocs.push_back((void*)*p);
+    return PT_OK;
+}
+template <typename T>
+static int devUpload(pt_ctx* ctx, T** p, const T* host, size_t n, bool sceneOwned) {
+    int r = devAlloc(ctx, p, n, sceneOwned);
+    if (r) return r;
+    if (n) CK(cudaMemcpyAsync(*p, host, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    return PT_OK;
+}
+
+extern "C" {
+
+PT_API const char* pt_version(void) { return "ptb200 0.1 (sm_100a)"; }
+
+PT_API void pt_default_config(pt_config* c) {
+    memset(c, 0, sizeof(*c));
+    c->width = 640; c->height = 480;          // constants.h:4-5
+    c->max_ray_depth = 32;                    // constants.h:13
+    c->interactive_depth = 1;                 // scene.h:137
+    c->guiding_frames = 100;                  // pathtracer.h:292
+    c->blue_noise_frames = 1;                 // kernels.h:23
+    c->device = 0; c->rank = 0; c->world_size = 1; c->flags = PT_FLAG_DEFAULT;
+}
+
+PT_API const char* pt_last_error(const pt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+PT_API void pt_destroy(pt_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (auto t : ctx->textures) cudaDestroyTextureObject(t);
+    for (auto a : ctx->arrays) cudaFreeArray(a);
+    for (void* p : ctx->sceneAllocs) cudaFree(p);
+    void* bufs[] = {ctx->q.rayO[0], ctx->q.rayO[1], ctx->q.rayD[0], ctx->q.rayD[1], ctx->q.shO, ctx->q.shD, ctx->q.hits, ctx->q.cnt,
+                    ctx->masks, ctx->accucolors, ctx->lights, ctx->sampleCache, ctx->image, ctx->albedo, ctx->stats,
+                    ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
+    for (void* p : bufs) if (p) cudaFree(p);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
+    if (!out || !cfg) { g_createError = "pt_create: null argument"; return PT_ERR_INVALID; }
+    *out = nullptr;
+    if (cfg->width == 0 || cfg->height == 0 || cfg->world_size == 0 || cfg->rank >= cfg->world_size ||
+        cfg->max_ray_depth == 0 || cfg->max_ray_depth > PT_MAX_BOUNCES || cfg->interactive_depth + 1 > PT_MAX_BOUNCES) {
+        g_createError = "pt_create: invalid config (size, rank/world_size or depth out of range; max depth 64)";
+        return PT_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || cfg->device >= ndev) {
+        cudaGetLastError();
+        g_createError = "pt_create: no CUDA device available -- libptb200 has no CPU fallback";
+        return PT_ERR_NO_DEVICE;
+    }
+    pt_ctx* ctx = new pt_ctx();
+    ctx->cfg = *cfg;
+    memset(&ctx->q, 0, sizeof(ctx->q)); memset(&ctx->sc, 0, sizeof(ctx->sc)); memset(&ctx->tex, 0, sizeof(ctx->tex));
+    ctx->tex.skyConst = make_float3(1.0f, 1.0f, 1.0f);
+    auto bail = [&](int code) { g_createError = ctx->err; pt_destroy(ctx); return code; };
+    auto body = [&]() -> int {
+        CK(cudaSetDevice(cfg->device));
+        CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        CK(cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, cfg->device));
+        TileMap& m = ctx->map;
+        m.W = cfg->width; m.H = cfg->height;
+        m.tilesX = (m.W + 31) / 32; m.tilesY = (m.H + 31) / 32;
+        m.rank = cfg->rank; m.world = cfg->world_size;
+        const uint32_t T = m.tilesX * m.tilesY;
+        m.nLocalTiles = T > m.rank ? (T - m.rank + m.world - 1) / m.world : 0;
+        m.nSlots = m.nLocalTiles * 1024u;
+        const size_t cap = std::max<uint32_t>(m.nSlots, 1024u);
+        int r;
+        for (int i = 0; i < 2; i++) {
+            if ((r = devAlloc(ctx, &ctx->q.rayO[i], cap, false))) return r;
+            if ((r = devAlloc(ctx, &ctx->q.rayD[i], cap, false))) return r;
+        }
+        if ((r = devAlloc(ctx, &ctx->q.shO, cap, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->q.shD, cap, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->q.hits, cap, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->q.cnt, (size_t)CNT_TOTAL, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->masks, cap, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->accucolors, cap, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->lights, cap, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->sampleCache, cap * PT_MAX_CACHE_DEPTH, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->image, (size_t)m.W * m.H, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->albedo, (size_t)m.W * m.H, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->stats, (size_t)8, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->dbgCursor, (size_t)1, false))) return r;
+        CK(cudaMemsetAsync(ctx->q.cnt, 0, CNT_TOTAL * sizeof(uint), ctx->stream));
+        CK(cudaMemsetAsync(ctx->lights, 0, cap * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->masks, 0, cap * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->accucolors, 0, cap * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->sampleCache, 0, cap * PT_MAX_CACHE_DEPTH * sizeof(pt_sample_cache), ctx->stream));
+        CK(cudaMemsetAsync(ctx->image, 0, (size_t)m.W * m.H * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->albedo, 0, (size_t)m.W * m.H * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->stats, 0, 8 * sizeof(unsigned long long), ctx->stream));
+        int occ = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<false>, 128, 0));
+        ctx->gridTraceExt = ctx->numSMs * std::max(occ, 1);
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<true>, 128, 0));
+        ctx->gridTraceAny = ctx->numSMs * std::max(occ, 1);
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, 128, 0));
+        ctx->gridShade = ctx->numSMs * std::max(occ, 1);
+        CK(cudaStreamSynchronize(ctx->stream));
+        return PT_OK;
+    };
+    int r = body();
+    if (r) return bail(r);
+    *out = ctx;
+    return PT_OK;
+}
+
+static int makeTexture(pt_ctx* ctx, const float* data, uint32_t w, uint32_t h, int channels, bool linear, cudaTextureObject_t* out) {
+    // loadTexture / loadTextureL / loadTextureHDR (use_cuda.h:108-263): normalised coords, wrap, element type
+    cudaChannelFormatDesc desc = channels == 4 ? cudaCreateChannelDesc(32, 32, 32, 32, cudaChannelFormatKindFloat)
+                                               : cudaCreateChannelDesc(32, 0, 0, 0, cudaChannelFormatKindFloat);
+    cudaArray_t arr = nullptr;
+    CK(cudaMallocArray(&arr, &desc, w, h));
+    ctx->arrays.push_back(arr);
+    const size_t pitch = (size_t)w * channels * sizeof(float);
+    CK(cudaMemcpy2DToArray(arr, 0, 0, data, pitch, pitch, h, cudaMemcpyHostToDevice));
+    cudaResourceDesc res; memset(&res, 0, sizeof(res));
+    res.resType = cudaResourceTypeArray; res.res.array.array = arr;
+    cudaTextureDesc td; memset(&td, 0, sizeof(td));
+    td.normalizedCoords = 1;
+    td.addressMode[0] = cudaAddressModeWrap; td.addressMode[1] = cudaAddressModeWrap;
+    td.filterMode = linear ? cudaFilterModeLinear : cudaFilterModePoint;
+    td.readMode = cudaReadModeElementType;
+    CK(cudaCreateTextureObject(out, &res, &td, nullptr));
+    ctx->textures.push_back(*out);
+    return PT_OK;
+}
+
+PT_API int pt_set_skydome(pt_ctx* ctx, const float* rgba, uint32_t w, uint32_t h) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (!rgba) { ctx->tex.sky = 0; return PT_OK; }
+    cudaTextureObject_t t; int r = makeTexture(ctx, rgba, w, h, 4, true, &t);
+    if (r) return r;
+    ctx->tex.sky = t;
+    return PT_OK;
+}
+PT_API int pt_set_sky_constant(pt_ctx* ctx, float r, float g, float b) {
+    if (!ctx) return PT_ERR_INVALID;
+    ctx->tex.sky = 0; ctx->tex.skyConst = make_float3(r, g, b);
+    return PT_OK;
+}
+PT_API int pt_set_blue_noise(pt_ctx* ctx, const float* lum, uint32_t w, uint32_t h) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (!lum) { ctx->tex.blue = 0; return PT_OK; }
+    cudaTextureObject_t t; int r = makeTexture(ctx, lum, w, h, 1, false, &t);
+    if (r) return r;
+    ctx->tex.blue = t;
+    ctx->tex.invBlueSize = make_float2(1.0f / (float)w, 1.0f / (float)h);      // pathtracer.h:79
+    return PT_OK;
+}
+PT_API int pt_texture_create(pt_ctx* ctx, const float* rgba, uint32_t w, uint32_t h, uint64_t* out_handle) {
+    if (!ctx || !rgba || !out_handle) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    cudaTextureObject_t t; int r = makeTexture(ctx, rgba, w, h, 4, true, &t);
+    if (r) return r;
+    *out_handle = (uint64_t)t;
+    return PT_OK;
+}
+PT_API int pt_set_allreduce_hook(pt_ctx* ctx, pt_allreduce_hook hook, void* user) {
+    if (!ctx) return PT_ERR_INVALID;
+    ctx->hook = hook; ctx->hookUser = user;
+    return PT_OK;
+}
+PT_API int pt_set_toggles(pt_ctx* ctx, int nee, int guiding) {
+    if (!ctx) return PT_ERR_INVALID;
+    ctx->HNEE = nee != 0; ctx->HCACHE = guiding != 0;
+    return PT_OK;
+}
+PT_API void* pt_cuda_stream(pt_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+static uint32_t tlasDepth(const pt_tlas_node* n, uint32_t count, uint32_t idx, uint32_t depth) {
+    if (idx >= count || depth > 70) return depth;
+    if (n[idx].children == 0) return depth;
+    return std::max(tlasDepth(n, count, n[idx].children & 0xffffu, depth + 1), tlasDepth(n, count, (n[idx].children >> 16) & 0xffffu, depth + 1));
+}
+
+PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
+    if (!ctx || !d) return PT_ERR_INVALID;
+    if (d->num_models == 0 && d->num_instances > 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instances without models");
+    CK(cudaSetDevice(ctx->cfg.device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (void* p : ctx->sceneAllocs) cudaFree(p);
+    ctx->sceneAllocs.clear();
+    ctx->haveScene = false;
+    DScene& sc = ctx->sc;
+    memset(&sc, 0, sizeof(sc));
+    // wide BVH per model (host), one node array / one triangle-record array for the whole scene
+    std::vector<WideNode> nodes; std::vector<WideTri> wtris; std::vector<DModel> models(d->num_models);
+    for (uint32_t m = 0; m < d->num_models; m++) {
+        const pt_model& pm = d->models[m];
+        if (!pm.bvh || pm.nrBvhNodes == 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: model without BVH");
+        WideBuildStats st;
+        models[m].rootNode = buildWideBVH(pm.bvh, pm.nrBvhNodes, d->vertices, nodes, wtris, &st);
+        models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;
+        if (st.max_depth >= PT_STACK - 1) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: wide BVH deeper than the traversal stack");
+        if (st.tris != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
+    }
+    for (uint32_t i = 0; i < d->num_instances; i++)
+        if (d->instances[i].model_id >= d->num_models) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instance model_id out of range");
+    if (d->num_instances && d->num_tlas_nodes && tlasDepth(d->topBvh, d->num_tlas_nodes, 0, 0) >= PT_STACK)
+        return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: top-level BVH deeper than the traversal stack");
+    // emissive triangles (pathtracer.h:155-167)
+    std::vector<pt_triangle_light> lights;
+    for (uint32_t i = 0; i < d->num_instances; i++) {
+        const pt_instance& inst = d->instances[i];
+        const pt_model& model = d->models[inst.model_id];
+        for (uint32_t t = model.triangleStart; t < model.triangleStart + model.nrTriangles; t++) {
+            const uint32_t mat_id = inst.material_id == 0xffffffffu ? d->vertexData[t].material : inst.material_id;
+            if (mat_id >= d->num_materials) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: material id out of range");
+            const pt_float3 e = d->materials[mat_id].emission;
+            if (fmaxf(e.x, fmaxf(e.y, e.z)) < PT_EPS) continue;
+            lights.push_back(pt_triangle_light{t, i});
+        }
+    }
+    int r;
+    float4 *dn, *dt; pt_triangle_v* dv; pt_triangle_d* dd; pt_material* dm; pt_instance* di; pt_tlas_node* dl; DModel* dmo;
+    pt_sphere* ds; pt_plane* dp; pt_triangle_light* dli;
+    if ((r = devUpload(ctx, (WideNode**)&dn, nodes.data(), nodes.size(), true))) return r;
+    if ((r = devUpload(ctx, (WideTri**)&dt, wtris.data(), wtris.size(), true))) return r;
+    if ((r = devUpload(ctx, &dv, d->vertices, d->num_triangles, true))) return r;
+    if ((r = devUpload(ctx, &dd, d->vertexData, d->num_triangles, true))) return r;
+    if ((r = devUpload(ctx, &dm, d->materials, d->num_materials, true))) return r;
+    if ((r = devUpload(ctx, &di, d->instances, d->num_instances, true))) return r;
+    if ((r = devUpload(ctx, &dl, d->topBvh, d->num_tlas_nodes, true))) return r;
+    if ((r = devUpload(ctx, &dmo, models.data(), models.size(), true))) return r;
+    if ((r = devUpload(ctx, &ds, d->spheres, d->num_spheres, true))) return r;
+    if ((r = devUpload(ctx, &dp, d->planes, d->num_planes, true))) return r;
+    if ((r = devUpload(ctx, &dli, lights.data(), lights.size(), true))) return r;
+    if ((r = devAlloc(ctx, &sc.rcRadiance, (size_t)d->num_triangles * 3, true))) return r;
+    if ((r = devAlloc(ctx, &sc.rcAdditions, (size_t)d->num_triangles * 16, true))) return r;
+    sc.nodes = dn; sc.wtris = dt; sc.vertices = dv; sc.vertexData = dd; sc.materials = dm; sc.instances = di; sc.tlas = dl;
+    sc.models = dmo; sc.spheres = ds; sc.planes = dp; sc.lights = dli;
+    sc.num_triangles = d->num_triangles; sc.num_instances = d->num_instances; sc.num_spheres = d->num_spheres;
+    sc.num_planes = d->num_planes; sc.num_lights = (uint)lights.size();
+    ctx->numInstancesCap = d->num_instances; ctx->numTlasCap = d->num_tlas_nodes;
+    if (d->num_triangles) {
+        k_rc_init<<<(d->num_triangles + 255) / 256, 256, 0, ctx->stream>>>(sc.rcRadiance, sc.rcAdditions, d->num_triangles);   // pathtracer.h:220
+        CK(cudaGetLastError());
+    }
+    CK(cudaStreamSynchronize(ctx->stream));      // host vectors above go out of scope
+    ctx->haveScene = true;
+    return (int)lights.size();
+}
+
+PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n, const pt_tlas_node* tlas, uint32_t n_nodes) {
+    if (!ctx || !ctx->haveScene) return PT_ERR_INVALID;
+    if (n != ctx->numInstancesCap || n_nodes != ctx->numTlasCap) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: counts differ from the uploaded scene");
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (tlasDepth(tlas, n_nodes, 0, 0) >= PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: top-level BVH too deep");
+    // pathtracer.h:245-246; pageable sources are staged before the call returns
+    CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync((void*)ctx->sc.tlas, tlas, n_nodes * sizeof(pt_tlas_node), cudaMemcpyHostToDevice, ctx->stream));
+    return PT_OK;
+}
+
+static DCamera toDCamera(const pt_camera* c) {
+    DCamera d;
+    d.eye = make_float3(c->eye.x, c->eye.y, c->eye.z); d.viewDir = make_float3(c->viewDir.x, c->viewDir.y, c->viewDir.z);
+    d.lt = make_float3(c->lt.x, c->lt.y, c->lt.z); d.u = make_float3(c->u.x, c->u.y, c->u.z); d.v = make_float3(c->v.x, c->v.y, c->v.z);
+    d.d = c->d; d.focalLength = c->focalLength; d.aperture = c->aperture;
+    return d;
+}
+
+// Pathtracer::Render, pathtracer.h:224-302.  Asynchronous: only enqueues work on the context's stream.
+PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
+    if (!ctx || !cam) return PT_ERR_INVALID;
+    if (!ctx->haveScene) return fail(ctx, PT_ERR_INVALID, "pt_render: no scene uploaded");
+    CK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t s = ctx->stream;
+    const TileMap& map = ctx->map;
+    const DCamera dcam = toDCamera(cam);
+    const uint32_t npix = map.W * map.H;
+    if (should_clear) {
+        ctx->DNEE = ctx->HNEE; ctx->DCACHE = ctx->HCACHE;                                  // :242-243
+        k_clear_image<<<(npix + 255) / 256, 256, 0, s>>>(ctx->image, ctx->albedo, npix);    // :248-249
+        ctx->sampleIdx = 0; ctx->randIdx = 0;                                              // :250-251
+    }
+    const uint32_t nsamples = should_clear ? ctx->cfg.interactive_depth : 1;               // :255
+    const bool deviceNEE = ctx->DNEE && ctx->sc.num_lights > 0;                            // globals.h:23
+    for (uint32_t sample = 0; sample < nsamples; sample++) {
+        CK(cudaMemsetAsync(ctx->q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                   // :265 (+ cursors)
+        if (map.nSlots) k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, ctx->q, ctx->masks, ctx->accucolors);   // :258,:266
+        ctx->randIdx++;                                                                    // :267
+        uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
+        if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
+        else max_bounces = should_clear ? ctx->cfg.interactive_depth + 1 : ctx->cfg.max_ray_depth;
+        for (uint32_t bounce = 0; bounce < max_bounces; bounce++) {                        // :276-290
+            const int buf = bounce & 1;
+            k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->q.rayO[buf], ctx->q.rayD[buf], ctx->q.cnt + CNT_EXT(bounce),
+                                                             ctx->q.cnt + CUR_EXT(bounce), ctx->q.hits, nullptr, nullptr);
+            ShadeParams P;
+            P.sc = ctx->sc; P.map = map; P.tex = ctx->tex;
+            P.masks = ctx->masks; P.accucolors = ctx->accucolors; P.lights = ctx->lights;
+            P.sampleCache = ctx->sampleCache; P.albedo = ctx->albedo;
+            P.sampleIdx = ctx->sampleIdx; P.randIdx = ctx->randIdx; P.blueFrames = ctx->cfg.blue_noise_frames;
+            P.bounce = (int)bounce; P.nee = deviceNEE; P.cache = ctx->DCACHE;
+            k_shade<<<ctx->gridShade, 128, 0, s>>>(P, ctx->q, buf);
+            ctx->randIdx++;                                                                // :283
+            if (ctx->HNEE && deviceNEE)                                                    // :286 (no shadow rays exist when the device _NEE is false)
+                k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, ctx->q.shO, ctx->q.shD, ctx->q.cnt + CNT_SHADOW(bounce),
+                                                                ctx->q.cnt + CUR_CONN(bounce), nullptr, ctx->lights, ctx->accucolors);
+        }
+        if (!should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots) {   // :292-296
+            k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            if (ctx->hook) {
+                int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
+                if (hr) return fail(ctx, PT_ERR_INVALID, "pt_render: all-reduce hook failed");
+            }
+            k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+        }
+        if (map.nSlots) k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->image, ctx->q.cnt, ctx->stats, max_bounces);   // :299
+        ctx->sampleIdx++;                                                                  // :300
+    }
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+PT_API int pt_finish(pt_ctx* ctx) {                                                        // pathtracer.h:305-310
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+PT_API int pt_read_image(pt_ctx* ctx, float* host_rgbw, int which) {
+    if (!ctx || !host_rgbw) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    CK(cudaMemcpyAsync(host_rgbw, which == 0 ? ctx->image : ctx->albedo, (size_t)ctx->map.W * ctx->map.H * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+PT_API int pt_read_radiance_cache(pt_ctx* ctx, pt_radiance_cache* out) {
+    if (!ctx || !out || !ctx->haveScene) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    const uint32_t T = ctx->sc.num_triangles;
+    std::vector<float> rc((size_t)T * 12), add((size_t)T * 16);
+    CK(cudaMemcpyAsync(rc.data(), ctx->sc.rcRadiance, rc.size() * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(add.data(), ctx->sc.rcAdditions, add.size() * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (uint32_t i = 0; i < T; i++) {
+        for (int b = 0; b < 8; b++) {
+            out[i].radianceCache[b] = rc[(size_t)i * 12 + b];
+            out[i].additionCache[b] = add[(size_t)b * T + i];
+            out[i].additionCacheCount[b] = add[(size_t)(8 + b) * T + i];
+        }
+        out[i].radianceTotal = rc[(size_t)i * 12 + 8];
+    }
+    return PT_OK;
+}
+
+PT_API int pt_get_stats(pt_ctx* ctx, pt_stats* out) {
+    if (!ctx || !out) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    unsigned long long h[8];
+    CK(cudaMemcpyAsync(h, ctx->stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    out->primary_rays = h[0]; out->extend_rays = h[1]; out->shadow_rays = h[2]; out->shade_calls = h[3]; out->samples = h[4];
+    return PT_OK;
+}
+PT_API int pt_reset_stats(pt_ctx* ctx) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    CK(cudaMemsetAsync(ctx->stats, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    return PT_OK;
+}
+PT_API int pt_get_rand_state(pt_ctx* ctx, uint32_t* sampleIdx, uint32_t* randIdx) {
+    if (!ctx) return PT_ERR_INVALID;
+    if (sampleIdx) *sampleIdx = ctx->sampleIdx;
+    if (randIdx) *randIdx = ctx->randIdx;
+    return PT_OK;
+}
+
+PT_API int pt_debug_primary_rays(pt_ctx* ctx, const pt_camera* cam, uint32_t randIdx, pt_ray* host_out) {
+    if (!ctx || !cam || !host_out) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    const uint32_t W = ctx->map.W, H = ctx->map.H;
+    pt_ray* d = nullptr;
+    CK(cudaMalloc((void**)&d, (size_t)W * H * sizeof(pt_ray)));
+    k_primary_debug<<<dim3((W + 15) / 16, (H + 15) / 16), dim3(16, 16), 0, ctx->stream>>>(toDCamera(cam), W, H, randIdx, d);
+    cudaError_t e = cudaMemcpyAsync(host_out, d, (size_t)W * H * sizeof(pt_ray), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    CK(e);
+    return PT_OK;
+}
+
+static int debugTrace(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_hit, uint32_t repeats, float* out_ms, pt_hit* host_out) {
+    if (!ctx || !host_rays || !ctx->haveScene) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (n > ctx->dbgCap) {
+        if (ctx->dbgRays) cudaFree(ctx->dbgRays);
+        if (ctx->dbgHits) cudaFree(ctx->dbgHits);
+        ctx->dbgRays = nullptr; ctx->dbgHits = nullptr; ctx->dbgCap = 0;
+        CK(cudaMalloc((void**)&ctx->dbgRays, (size_t)n * sizeof(pt_ray)));
+        CK(cudaMalloc((void**)&ctx->dbgHits, (size_t)n * sizeof(pt_hit)));
+        ctx->dbgCap = n;
+    }
+    cudaStream_t s = ctx->stream;
+    CK(cudaMemcpyAsync(ctx->dbgRays, host_rays, (size_t)n * sizeof(pt_ray), cudaMemcpyHostToDevice, s));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    float total = 0.0f;
+    for (uint32_t r = 0; r < std::max(repeats, 1u); r++) {
+        CK(cudaMemsetAsync(ctx->dbgCursor, 0, sizeof(uint), s));
+        CK(cudaEventRecord(e0, s));
+        if (any_hit) k_trace_debug<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, ctx->dbgRays, n, ctx->dbgCursor, ctx->dbgHits);
+        else k_trace_debug<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->dbgRays, n, ctx->dbgCursor, ctx->dbgHits);
+        CK(cudaEventRecord(e1, s));
+        CK(cudaStreamSynchronize(s));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (r > 0 || repeats <= 1) total += ms;     // first repeat is the warm-up when repeats > 1
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (out_ms) *out_ms = repeats > 1 ? total / (float)(repeats - 1) : total;
+    if (host_out) {
+        CK(cudaMemcpyAsync(host_out, ctx->dbgHits, (size_t)n * sizeof(pt_hit), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    return PT_OK;
+}
+PT_API int pt_debug_trace(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_hit, pt_hit* host_out) {
+    return debugTrace(ctx, host_rays, n, any_hit, 1, nullptr, host_out);
+}
+PT_API int pt_debug_trace_resident(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_hit, uint32_t repeats, float* out_ms, pt_hit* host_out) {
+    return debugTrace(ctx, host_rays, n, any_hit, repeats, out_ms, host_out);
+}
+}  // extern "C"

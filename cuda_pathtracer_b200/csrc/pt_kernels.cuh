@@ -1,0 +1,260 @@
+// pt_kernels.cuh -- the wavefront stages as CUDA kernels for sm_100a.
+//   k_primary      clear_state + generate_primary_rays (reference kernels.h:485-501), compacted append
+//   k_trace<ANY>   extend / connect (kernels.h:503-510, 799-810): persistent warps, dynamic ray fetch
+//   k_shade        kernel_shade (kernels.h:513-796) + warp-aggregated compaction of survivors
+//   k_accumulate   add_to_screen (kernels.h:812-824) + per-sample ray statistics
+//   k_rc_*         init / update / propagate radiance cache (kernels.h:848-905)
+// Queues: SoA float4 streams (origin|tmax, direction|slot), ping-pong by bounce parity; per-bounce
+// counters and work cursors live in one small device array that is zeroed once per sample, which
+// replaces the reference's kernel_clear_rays / kernel_swap_and_clear <<<1,1>>> launches.
+#pragma once
+#include "pt_shade.cuh"
+
+namespace ptb {
+
+// counter array layout (uint32 each)
+#define CNT_EXT(b) (b)                              /* rays queued for extend at bounce b          */
+#define CNT_SHADOW(b) (PT_MAX_BOUNCES + 1 + (b))    /* shadow rays queued at bounce b              */
+#define CUR_EXT(b) (2 * (PT_MAX_BOUNCES + 1) + (b)) /* dynamic-fetch cursors of the persistent kernels */
+#define CUR_CONN(b) (3 * (PT_MAX_BOUNCES + 1) + (b))
+#define CNT_TOTAL (4 * (PT_MAX_BOUNCES + 1))
+
+struct Queues {
+    float4* rayO[2]; float4* rayD[2];   // extension rays, ping-pong
+    float4* shO; float4* shD;           // shadow rays
+    float4* hits;                       // HitInfoPacked per extension ray (types.h:310-334)
+    uint* cnt;
+};
+
+__device__ __forceinline__ uint laneId() { uint l; asm("mov.u32 %0, %%laneid;" : "=r"(l)); return l; }
+// One atomic per warp: ballot the survivors, the first one reserves popc slots, everyone writes at
+// base + rank.  Must be called by all 32 lanes.
+__device__ __forceinline__ uint warpAppend(bool pred, uint* counter) {
+    const uint m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return 0;
+    const uint leader = __ffs(m) - 1;
+    uint base = 0;
+    if (laneId() == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(m & ((1u << laneId()) - 1u));
+}
+
+// ---- primary rays: types.h:641-658 (Camera::getRay), 669-676 (distort) ----------------------------------
+__device__ __forceinline__ float3 camDistort(const DCamera& c, float3 p) {
+    float3 center = c.eye + c.d * c.viewDir;
+    float3 fromCenter = p - center;
+    float r = length(p - center);
+    float rd = r + 0.2f * r * r * r;
+    return center + fromCenter * (rd / fmaxf(0.0001f, r));
+}
+__device__ __forceinline__ void camGetRay(const DCamera& c, uint x, uint y, uint& seed, uint W, uint H, float3& o, float3& d) {
+    float xf = ((float)x + rnd(seed)) / (float)W;
+    float yf = ((float)y + rnd(seed)) / (float)H;
+    float3 origin = camDistort(c, c.lt + xf * c.u + yf * c.v);
+    float3 direction = origin - c.eye;
+    const float correction = length(direction);
+    direction = direction / correction;
+    const float3 focalPoint = origin + (c.focalLength - c.d) * direction;
+    const float offsetR = sqrtf(rnd(seed));
+    const float offsetA = rnd(seed) * 2.0f * PT_PI;
+    const float fx = offsetR * sinf(offsetA), fy = offsetR * cosf(offsetA);
+    origin += c.aperture * (fx * c.u + fy * c.v);
+    direction = normalize(focalPoint - origin);
+    if (dot(direction, c.viewDir) < 0) direction = -direction;
+    o = origin - correction * direction; d = direction;
+}
+
+__global__ void __launch_bounds__(256) k_primary(DCamera cam, TileMap map, uint randIdx, Queues q, float4* masks, float4* accucolors) {
+    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;      // grid covers nSlots exactly (multiple of 1024)
+    uint x, y;
+    const bool valid = slotToPixel(map, slot, x, y);
+    float3 o = f3(0), d = f3(0);
+    if (valid) {
+        accucolors[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                    // kernels.h:489
+        masks[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(1u));           // kernels.h:490
+        uint seed = getSeed(x, y, randIdx, map.W);
+        camGetRay(cam, x, y, seed, map.W, map.H, o, d);
+    }
+    const uint idx = warpAppend(valid, q.cnt + CNT_EXT(0));
+    if (valid) {
+        q.rayO[0][idx] = make_float4(o.x, o.y, o.z, 9999999.0f);
+        q.rayD[0][idx] = make_float4(d.x, d.y, d.z, __uint_as_float(slot));
+    }
+}
+
+// debug variant: rays written at their PIXEL index in reference RayPacked form (pt_debug_primary_rays)
+__global__ void k_primary_debug(DCamera cam, uint W, uint H, uint randIdx, pt_ray* out) {
+    const uint x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= H) return;
+    uint seed = getSeed(x, y, randIdx, W);
+    float3 o, d; camGetRay(cam, x, y, seed, W, H, o, d);
+    pt_ray r; r.origin.x = o.x; r.origin.y = o.y; r.origin.z = o.z; r.origin.w = 9999999.0f;
+    r.direction.x = d.x; r.direction.y = d.y; r.direction.z = d.z; r.direction.w = __uint_as_float(x + y * W);
+    out[x + y * W] = r;
+}
+
+// ---- extend / connect ---------------------------------------------------------------------------------------
+// Persistent warps: each warp claims 32 consecutive queue entries with one atomic, traces them, and
+// comes back for more, so a warp that drew short rays does not idle while another is still deep in
+// the tree.  count/cursor are device-side: the host never reads queue sizes (reference README.md:201).
+template <bool ANY>
+__global__ void __launch_bounds__(128) k_trace(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+                                               const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
+                                               const float4* __restrict__ lights, float4* accucolors) {
+    const uint n = *count;
+    const uint lane = laneId();
+    while (true) {
+        uint base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint i = base + lane;
+        if (i < n) {
+            const float4 o4 = rayO[i], d4 = rayD[i];
+            const Hit h = traceTop<ANY>(sc, f3(o4), f3(d4), o4.w);
+            if (ANY) {
+                if (h.id == 0xffffffffu) {                                   // unoccluded: kernels.h:806-809
+                    const uint slot = __float_as_uint(d4.w);
+                    const float4 l = lights[slot];
+                    float4 a = accucolors[slot];
+                    a.x += l.x; a.y += l.y; a.z += l.z;
+                    accucolors[slot] = a;
+                }
+            } else {
+                hits[i] = make_float4(__uint_as_float(h.type), __uint_as_float(h.id), __uint_as_float(h.inst), h.t);
+            }
+        }
+    }
+}
+
+// stage-parity hook: reference-format rays in, reference-format hits out (pt_debug_trace)
+template <bool ANY>
+__global__ void __launch_bounds__(128) k_trace_debug(DScene sc, const pt_ray* __restrict__ rays, uint n, uint* cursor, pt_hit* __restrict__ out) {
+    const uint lane = laneId();
+    while (true) {
+        uint base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint i = base + lane;
+        if (i < n) {
+            const float4 o4 = *reinterpret_cast<const float4*>(&rays[i].origin), d4 = *reinterpret_cast<const float4*>(&rays[i].direction);
+            Hit h = traceTop<ANY>(sc, f3(o4), f3(d4), o4.w);
+            if (h.id == 0xffffffffu) { h.type = 0; h.inst = 0; }
+            else if (ANY) { h.type = 0; h.inst = 0; h.id = 0; }
+            else if (h.type != 0) h.inst = 0;
+            pt_hit p; p.primitive_type = h.type; p.primitive_id = h.id; p.instance_id = h.inst; p.t = h.t;
+            out[i] = p;
+        }
+    }
+}
+
+// ---- shade ----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_shade(ShadeParams P, Queues q, int inBuf) {
+    const uint n = q.cnt[CNT_EXT(P.bounce)];
+    const uint warpsTotal = (gridDim.x * blockDim.x) >> 5;
+    const uint warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint lane = laneId();
+    const float4* rayO = q.rayO[inBuf]; const float4* rayD = q.rayD[inBuf];
+    float4* outO = q.rayO[inBuf ^ 1]; float4* outD = q.rayD[inBuf ^ 1];
+    for (uint base = warp * 32u; base < n; base += warpsTotal * 32u) {
+        const uint i = base + lane;
+        ShadeOut so; so.pushExt = so.pushShadow = false;
+        uint slot = 0;
+        if (i < n) {
+            const float4 o4 = rayO[i], d4 = rayD[i], h4 = q.hits[i];
+            slot = __float_as_uint(d4.w);
+            Hit h; h.type = __float_as_uint(h4.x); h.id = __float_as_uint(h4.y); h.inst = __float_as_uint(h4.z); h.t = h4.w;
+            shadeOne(P, f3(o4), f3(d4), slot, h, so);
+        }
+        const uint si = warpAppend(so.pushShadow, q.cnt + CNT_SHADOW(P.bounce));
+        if (so.pushShadow) {
+            q.shO[si] = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
+            q.shD[si] = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
+        }
+        const uint ei = warpAppend(so.pushExt, q.cnt + CNT_EXT(P.bounce + 1));
+        if (so.pushExt) {
+            outO[ei] = make_float4(so.ext.o.x, so.ext.o.y, so.ext.o.z, so.ext.len);
+            outD[ei] = make_float4(so.ext.d.x, so.ext.d.y, so.ext.d.z, __uint_as_float(slot));
+        }
+    }
+}
+
+// ---- accumulate + statistics -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* __restrict__ accucolors, float4* image,
+                                                    const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces) {
+    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint x, y;
+    if (slotToPixel(map, slot, x, y)) {
+        const float4 c = accucolors[slot];
+        const uint pix = x + y * map.W;
+        const float4 p = image[pix];
+        image[pix] = make_float4(fmaxf(0.0f, p.x) + c.x, fmaxf(0.0f, p.y) + c.y, fmaxf(0.0f, p.z) + c.z, p.w + 1.0f);
+    }
+    if (slot == 0) {
+        unsigned long long ext = 0, sh = 0;
+        for (uint b = 0; b < maxBounces; b++) { ext += cnt[CNT_EXT(b)]; sh += cnt[CNT_SHADOW(b)]; }
+        stats[0] += cnt[CNT_EXT(0)]; stats[1] += ext; stats[2] += sh; stats[3] += ext; stats[4] += 1;
+    }
+}
+__global__ void k_clear_image(float4* a, float4* b, uint n) {
+    const uint i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { a[i] = make_float4(0, 0, 0, 0); b[i] = make_float4(0, 0, 0, 0); }
+}
+
+// ---- radiance cache (path guiding) ----------------------------------------------------------------------------------
+// Layout: rcRadiance = 3 x float4 per triangle {radianceCache[0..3]}{radianceCache[4..7]}{radianceTotal,-,-,-};
+// rcAdditions = SoA planes [16][T] (additionCache[8] | additionCacheCount[8]) -- one contiguous buffer,
+// which is what the multi-GPU all-reduce sums.
+__global__ void k_rc_init(float4* rc, float* add, uint T) {                          // kernels.h:848-861
+    const uint i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T) return;
+    rc[(size_t)i * 3] = make_float4(0.1f, 0.1f, 0.1f, 0.1f);
+    rc[(size_t)i * 3 + 1] = make_float4(0.1f, 0.1f, 0.1f, 0.1f);
+    rc[(size_t)i * 3 + 2] = make_float4(8 * 0.1f, 0.0f, 0.0f, 0.0f);
+    for (uint b = 0; b < 16; b++) add[(size_t)b * T + i] = 0.0f;
+}
+__global__ void __launch_bounds__(256) k_rc_update(TileMap map, const float4* __restrict__ accucolors,
+                                                   const pt_sample_cache* __restrict__ sampleCache, float* add, uint T) {   // kernels.h:863-882
+    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint x, y;
+    if (!slotToPixel(map, slot, x, y)) return;
+    const float3 totalEnergy = f3(accucolors[slot]);
+    for (uint bounce = 0; bounce < PT_MAX_CACHE_DEPTH; bounce++) {
+        const pt_sample_cache c = sampleCache[(size_t)bounce * map.nSlots + slot];
+        if (c.sample_type == 1) return;
+        if (c.sample_type == 0) continue;
+        const float energy = fminf(100.0f, luminance(totalEnergy / f3(c.cum_mask.x, c.cum_mask.y, c.cum_mask.z)));
+        atomicAdd(add + (size_t)c.cache_bucket_id * T + c.triangle_id, energy);          // RED.ADD.F32, no return value used
+        atomicAdd(add + (size_t)(8 + c.cache_bucket_id) * T + c.triangle_id, 1.0f);
+    }
+}
+__global__ void __launch_bounds__(256) k_rc_propagate(float4* rc, float* add, uint T) {                                   // kernels.h:884-905
+    const uint i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T) return;
+    float4 r0 = rc[(size_t)i * 3], r1 = rc[(size_t)i * 3 + 1], r2 = rc[(size_t)i * 3 + 2];
+    float v[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    float total = r2.x;
+    const float alpha = 0.95f;
+    bool dirty = false;
+#pragma unroll
+    for (uint t = 0; t < 8; t++) {
+        const float additionCount = add[(size_t)(8 + t) * T + i];
+        if (additionCount < PT_EPS) continue;
+        const float oldValue = v[t];
+        const float incomingEnergy = add[(size_t)t * T + i] / additionCount;
+        const float newValue = clampf(alpha * oldValue + (1 - alpha) * incomingEnergy, 0.1f, 2.0f);
+        total += newValue - oldValue;
+        v[t] = newValue;
+        add[(size_t)t * T + i] = 0.0f;
+        add[(size_t)(8 + t) * T + i] = 0.0f;
+        dirty = true;
+    }
+    if (dirty) {
+        rc[(size_t)i * 3] = make_float4(v[0], v[1], v[2], v[3]);
+        rc[(size_t)i * 3 + 1] = make_float4(v[4], v[5], v[6], v[7]);
+        rc[(size_t)i * 3 + 2] = make_float4(total, 0.0f, 0.0f, 0.0f);
+    }
+}
+
+}  // namespace ptb

@@ -1,0 +1,194 @@
+// wide_bvh.cpp -- BVH2 (reference createBVHBinned output) -> 8-wide compressed BVH.  See wide_bvh.h.
+#include "wide_bvh.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <deque>
+
+namespace ptb {
+namespace {
+
+struct Box3 {
+    float lo[3], hi[3];
+    void reset() { for (int a = 0; a < 3; a++) { lo[a] = 3.0e38f; hi[a] = -3.0e38f; } }
+    void grow(const float* p) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    void grow(const Box3& b) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    float area() const {
+        float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+        return (x < 0 || y < 0 || z < 0) ? 0.0f : 2.0f * (x * y + x * z + y * z);
+    }
+};
+
+// Temporary binary tree: the reference BVH2 with every leaf cut down to <= 3 triangles (the wide node
+// encodes a leaf's triangle count in 3 unary bits).  Triangle ranges stay in reference order.
+struct TNode { Box3 box; int left, right; uint32_t first, count; };
+
+static Box3 triBounds(const pt_triangle_v* tris, uint32_t first, uint32_t count) {
+    Box3 b; b.reset();
+    for (uint32_t i = first; i < first + count; i++) { b.grow(&tris[i].v0.x); b.grow(&tris[i].v1.x); b.grow(&tris[i].v2.x); }
+    return b;
+}
+
+static int splitLeaf(std::vector<TNode>& t, const pt_triangle_v* tris, uint32_t first, uint32_t count, const Box3* known) {
+    TNode n; n.left = n.right = -1; n.first = first; n.count = count;
+    n.box = known ? *known : triBounds(tris, first, count);
+    int idx = (int)t.size(); t.push_back(n);
+    if (count > 3) {
+        uint32_t lc = count / 2;
+        int l = splitLeaf(t, tris, first, lc, nullptr);
+        int r = splitLeaf(t, tris, first + lc, count - lc, nullptr);
+        t[idx].left = l; t[idx].right = r; t[idx].count = 0;
+    }
+    return idx;
+}
+
+static int convert(std::vector<TNode>& t, const pt_bvh_node* bvh2, const pt_triangle_v* tris, uint32_t root) {
+    // explicit stack: reference trees can be deep (no depth bound in createBVHBinned)
+    struct Item { uint32_t node; int parent; bool isRight; };
+    std::vector<Item> stack; stack.push_back({root, -1, false});
+    int rootIdx = -1;
+    while (!stack.empty()) {
+        Item it = stack.back(); stack.pop_back();
+        const pt_bvh_node& b = bvh2[it.node];
+        uint32_t first, count; memcpy(&first, &b.vmin.w, 4); memcpy(&count, &b.vmax.w, 4);
+        Box3 box; box.lo[0] = b.vmin.x; box.lo[1] = b.vmin.y; box.lo[2] = b.vmin.z; box.hi[0] = b.vmax.x; box.hi[1] = b.vmax.y; box.hi[2] = b.vmax.z;
+        int idx;
+        if (count > 0) idx = splitLeaf(t, tris, first, count, &box);
+        else {
+            TNode n; n.box = box; n.left = n.right = -1; n.first = 0; n.count = 0;
+            idx = (int)t.size(); t.push_back(n);
+            stack.push_back({first + 1, idx, true});
+            stack.push_back({first, idx, false});
+        }
+        if (it.parent < 0) rootIdx = idx;
+        else if (it.isRight) t[it.parent].right = idx;
+        else t[it.parent].left = idx;
+    }
+    return rootIdx;
+}
+
+static inline uint32_t fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static inline float bitsf(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+
+}  // namespace
+
+uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangle_v* triangles,
+                      std::vector<WideNode>& nodes, std::vector<WideTri>& tris, WideBuildStats* stats) {
+    (void)n_bvh2;
+    std::vector<TNode> t;
+    t.reserve(n_bvh2 * 2);
+    const int troot = convert(t, bvh2, triangles, 0);
+
+    const uint32_t rootIndex = (uint32_t)nodes.size();
+    nodes.push_back(WideNode());
+    struct Work { int tnode; uint32_t wide; uint32_t depth; };
+    std::deque<Work> queue;
+    queue.push_back({troot, rootIndex, 1});
+    uint32_t nLeaves = 0, maxDepth = 0;
+    double sah = 0.0;
+    const float rootArea = std::max(t[troot].box.area(), 1e-30f);
+
+    while (!queue.empty()) {
+        Work w = queue.front(); queue.pop_front();
+        maxDepth = std::max(maxDepth, w.depth);
+        const TNode& r = t[w.tnode];
+        // ---- collapse: open the child with the largest surface area until 8 children ----
+        int ch[8]; int nch = 0;
+        if (r.left < 0) ch[nch++] = w.tnode;                 // degenerate model: the root itself is a leaf
+        else { ch[nch++] = r.left; ch[nch++] = r.right; }
+        while (nch < 8) {
+            int best = -1; float bestArea = -1.0f;
+            for (int i = 0; i < nch; i++)
+                if (t[ch[i]].left >= 0) { float a = t[ch[i]].box.area(); if (a > bestArea) { bestArea = a; best = i; } }
+            if (best < 0) break;
+            int c = ch[best];
+            ch[best] = t[c].left; ch[nch++] = t[c].right;
+        }
+        // leaf triangles per node are limited to 24 (3 x 8) by construction.
+        // ---- assign children to slots so that slot ^ octant orders them front to back ----
+        float ctr[3]; for (int a = 0; a < 3; a++) ctr[a] = 0.5f * (r.box.lo[a] + r.box.hi[a]);
+        float cost[8][8];
+        for (int i = 0; i < nch; i++) {
+            const Box3& b = t[ch[i]].box;
+            float d[3]; for (int a = 0; a < 3; a++) d[a] = 0.5f * (b.lo[a] + b.hi[a]) - ctr[a];
+            for (int s = 0; s < 8; s++) {
+                float sx = (s & 4) ? 1.0f : -1.0f, sy = (s & 2) ? 1.0f : -1.0f, sz = (s & 1) ? 1.0f : -1.0f;
+                cost[i][s] = d[0] * sx + d[1] * sy + d[2] * sz;
+            }
+        }
+        int slotOf[8]; int childIn[8];
+        for (int i = 0; i < 8; i++) { slotOf[i] = -1; childIn[i] = -1; }
+        for (int k = 0; k < nch; k++) {
+            int bi = -1, bs = -1; float bc = -3.0e38f;
+            for (int i = 0; i < nch; i++) if (slotOf[i] < 0)
+                for (int s = 0; s < 8; s++) if (childIn[s] < 0 && cost[i][s] > bc) { bc = cost[i][s]; bi = i; bs = s; }
+            slotOf[bi] = bs; childIn[bs] = ch[bi];
+        }
+        // ---- quantisation frame ----
+        uint32_t ebyte[3]; float scale[3];
+        for (int a = 0; a < 3; a++) {
+            float ext = r.box.hi[a] - r.box.lo[a];
+            int e = ext > 0.0f ? (int)std::ceil(std::log2(ext / 255.0f)) : -126;
+            e = std::max(-126, std::min(127, e));
+            // make sure ceil((hi-lo)/2^e) <= 255 despite rounding
+            while (e < 127 && std::ceil(ext / std::ldexp(1.0f, e)) > 255.0f) e++;
+            ebyte[a] = (uint32_t)(e + 127);
+            scale[a] = std::ldexp(1.0f, e);
+        }
+        WideNode out; memset(&out, 0, sizeof(out));
+        uint8_t* bytes = (uint8_t*)out.w;
+        uint32_t imask = 0, nInternal = 0, triOffset = 0;
+        const uint32_t triBase = (uint32_t)tris.size();
+        uint32_t childBase = (uint32_t)nodes.size();
+        for (int s = 0; s < 8; s++) {
+            int c = childIn[s];
+            if (c < 0) continue;                                 // meta = 0, empty box (lo=255? keep 0/0 with meta 0 => never hit)
+            const TNode& cn = t[c];
+            uint8_t meta;
+            if (cn.left >= 0) {
+                imask |= 1u << s; meta = (uint8_t)(0x20 | (24 + s));
+                nodes.push_back(WideNode());
+                queue.push_back({c, childBase + nInternal, w.depth + 1});
+                nInternal++;
+            } else {
+                static const uint8_t unary[4] = {0, 1, 3, 7};
+                meta = (uint8_t)((unary[cn.count] << 5) | triOffset);
+                for (uint32_t i = cn.first; i < cn.first + cn.count; i++) {
+                    const pt_triangle_v& tv = triangles[i];
+                    WideTri wt; memset(&wt, 0, sizeof(wt));
+                    wt.v0[0] = tv.v0.x; wt.v0[1] = tv.v0.y; wt.v0[2] = tv.v0.z; wt.id = i;
+                    wt.e1[0] = tv.v1.x - tv.v0.x; wt.e1[1] = tv.v1.y - tv.v0.y; wt.e1[2] = tv.v1.z - tv.v0.z;   // kernels.h:171
+                    wt.e2[0] = tv.v2.x - tv.v0.x; wt.e2[1] = tv.v2.y - tv.v0.y; wt.e2[2] = tv.v2.z - tv.v0.z;   // kernels.h:172
+                    tris.push_back(wt);
+                }
+                triOffset += cn.count;
+                nLeaves++;
+                sah += (double)cn.box.area() / rootArea * cn.count;
+            }
+            bytes[24 + s] = meta;                                // w1 bytes 8..15 = meta[0..7]
+            for (int a = 0; a < 3; a++) {
+                float qlo = std::floor((cn.box.lo[a] - r.box.lo[a]) / scale[a]);
+                float qhi = std::ceil((cn.box.hi[a] - r.box.lo[a]) / scale[a]);
+                // guard against rounding in the division: the decoded box must contain the child box
+                while (qlo > 0.0f && r.box.lo[a] + qlo * scale[a] > cn.box.lo[a]) qlo -= 1.0f;
+                while (qhi < 255.0f && r.box.lo[a] + qhi * scale[a] < cn.box.hi[a]) qhi += 1.0f;
+                qlo = std::max(0.0f, std::min(255.0f, qlo)); qhi = std::max(0.0f, std::min(255.0f, qhi));
+                bytes[32 + a * 8 + s] = (uint8_t)qlo;           // w2.. : qlo_x[8] qlo_y[8] qlo_z[8]
+                bytes[56 + a * 8 + s] = (uint8_t)qhi;           //        qhi_x[8] qhi_y[8] qhi_z[8]
+            }
+            sah += (double)cn.box.area() / rootArea * (cn.left >= 0 ? 1.0 : 0.0);
+        }
+        out.w[0] = fbits(r.box.lo[0]); out.w[1] = fbits(r.box.lo[1]); out.w[2] = fbits(r.box.lo[2]);
+        out.w[3] = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
+        out.w[4] = childBase; out.w[5] = triBase;
+        nodes[w.wide] = out;
+    }
+    if (stats) {
+        stats->nodes = (uint32_t)nodes.size() - rootIndex; stats->leaves = nLeaves; stats->max_depth = maxDepth;
+        stats->tris = 0; for (const TNode& n : t) if (n.left < 0) stats->tris += n.count;
+        stats->sah_cost = sah;
+    }
+    return rootIndex;
+}
+
+}  // namespace ptb

@@ -174,6 +174,7 @@ PT_API int  pt_upload_scene(pt_ctx*, const pt_scene_desc*);         /* ~ upload 
 PT_API int  pt_update_instances(pt_ctx*, const pt_instance*, uint32_t n, const pt_tlas_node*, uint32_t n_nodes); /* pathtracer.h:245-246 */
 PT_API int  pt_set_toggles(pt_ctx*, int nee, int guiding);          /* HNEE / HCACHE (globals.h:19-20); takes effect on the next should_clear render (pathtracer.h:242-243) */
 PT_API int  pt_set_skydome(pt_ctx*, const float* rgba, uint32_t w, uint32_t h);   /* ~ loadTextureHDR (use_cuda.h:202-263): rows already flipped */
+PT_API int  pt_set_sky_constant(pt_ctx*, float r, float g, float b);            /* constant sky radiance (default 1,1,1) when no HDR dome is available */
 PT_API int  pt_set_blue_noise(pt_ctx*, const float* lum, uint32_t w, uint32_t h); /* ~ loadTextureL (use_cuda.h:166-200) */
 PT_API int  pt_texture_create(pt_ctx*, const float* rgba, uint32_t w, uint32_t h, uint64_t* out_handle); /* ~ loadTexture (use_cuda.h:108-164) */
 PT_API int  pt_set_allreduce_hook(pt_ctx*, pt_allreduce_hook hook, void* user);
