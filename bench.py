@@ -1,0 +1,271 @@
+#!/usr/bin/env python
+"""bench.py -- Mrays/s (and spp/s) of the wavefront path tracer on the sibenik 1080p configuration
+(BASELINE.json configs[2]: NEE + path guiding, MAX_RAY_DEPTH 8), tile-sharded over N GPUs.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one converge sample of the whole 1920x1080 image (Pathtracer::Render(shouldClear=false),
+reference src/pathtracer.h:255-301): primary rays, <= 8 x (extend, shade, connect), radiance-cache update
+(+ all-reduce over ranks) + propagate, accumulate.  A ray = one entry processed by extend or connect.
+`value` is timed on the device (CUDA events on the context's stream) with the scene resident in HBM;
+`e2e` goes through the public Pathtracer API with host buffers: per step the instances/TLAS/camera go
+host->device and the accumulated image comes back device->host.
+--impl reference times the CPU implementation of the same path on the host cores (bounded sample).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, DEPTH = 1920, 1080, 8
+METRIC = "Mrays/s on sibenik 1080p (NEE + path guiding, depth 8)"
+WORKLOAD = "sibenik-proxy (cathedral+statue+emissive cube+2 spheres, 158k tris) 1920x1080, NEE on, guiding on, MAX_RAY_DEPTH 8"
+CPU_W, CPU_H = 480, 270      # bounded CPU sample: same scene/camera/depth at 1/16 of the pixels
+
+
+def read_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows if len(r) > 2 + i)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]) if self.rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def build_scene():
+    from cuda_pathtracer_b200 import scenes
+    return scenes.sibenik_scene()
+
+
+def camera_for(step, w, h):
+    from cuda_pathtracer_b200 import scenes
+    cams = scenes.camera_sweep("sibenik", w, h, 16)
+    return cams[step % len(cams)]
+
+
+def cpu_leg(scene_arrays, threads, samples=1):
+    """Runs the CPU oracle on the bounded sample; returns (Mrays/s, per-ray traversal counters, seconds, rays)."""
+    from cuda_pathtracer_b200 import abi
+    from oracle.oracle_py import OracleLib
+    cfg = abi.default_config(CPU_W, CPU_H, max_ray_depth=DEPTH, interactive_depth=1)
+    ora = OracleLib(cfg)
+    desc, keep = abi.make_scene_desc(scene_arrays)
+    ora.upload_scene(desc, keep)
+    ora.set_threads(threads)
+    cam = camera_for(0, CPU_W, CPU_H)
+    ora.render(cam, True)                   # clearing frame: syncs the toggles (pathtracer.h:242-243)
+    ora.reset_stats()
+    t0 = time.time()
+    for _ in range(samples):
+        ora.render(cam, False)
+    dt = time.time() - t0
+    st, cnt = ora.stats()
+    rays = st.extend_rays + st.shadow_rays
+    per_ray = {"ext_inner": cnt[0] / max(1, st.extend_rays), "ext_tris": cnt[1] / max(1, st.extend_rays),
+               "conn_inner": cnt[3] / max(1, st.shadow_rays), "conn_tris": cnt[4] / max(1, st.shadow_rays),
+               "ext_per_pixel": st.extend_rays / (CPU_W * CPU_H * samples), "shadow_per_pixel": st.shadow_rays / (CPU_W * CPU_H * samples)}
+    ora.close()
+    return rays / dt / 1e6, per_ray, dt, rays
+
+
+
+def reference_arm(args):
+    """--impl reference: the CPU implementation of the path (the oracle port of the reference's kernels,
+    kind "port": the reference has no CPU build of kernel_shade/connect) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    arrays = build_scene().arrays()
+    for _ in range(min(args.warmup, 1)):
+        cpu_leg(arrays, threads, 1)
+    t0 = time.time()
+    total_rays, total_s = 0, 0.0
+    for _ in range(args.steps):
+        _, _, dt, rays = cpu_leg(arrays, threads, 1)
+        total_rays += rays
+        total_s += dt
+    v = total_rays / total_s / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": WORKLOAD, "sample": "%dx%d pixels of the same scene/camera/depth per step" % (CPU_W, CPU_H)},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
+                             "sample": "oracle/pt_oracle.cpp, 1 converge sample at %dx%d per step, OpenMP %d threads" % (CPU_W, CPU_H, threads)},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "wall_s": time.time() - t0}
+    print(json.dumps(line), flush=True)
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from cuda_pathtracer_b200 import abi, api
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    arrays = build_scene().arrays()
+    cfg = abi.default_config(W, H, max_ray_depth=DEPTH, interactive_depth=1, device=local, rank=rank, world_size=world)
+    pt = api.Pathtracer(arrays, cfg).Init()
+    stream = torch.cuda.ExternalStream(pt.stream(), device=torch.device("cuda", local))
+    if world > 1:
+        class _Dev:      # wraps the radiance-cache additions buffer (device pointer from the C ABI) as a tensor
+            def __init__(self, p, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (p, False), "version": 2}
+
+        def hook(p, n, s):
+            t = torch.as_tensor(_Dev(p, n), device=torch.device("cuda", local))
+            with torch.cuda.stream(stream):
+                dist.all_reduce(t)      # NCCL sum over NVLink, ordered on the path tracer's stream
+            return 0
+        pt.set_allreduce_hook(hook)
+    cams = [camera_for(i, W, H) for i in range(16)]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    pt.Render(cams[0], shouldClear=True)
+    pt.Finish()
+    step = 0
+    for _ in range(max(args.warmup, 3)):
+        pt.Render(cams[step % 16]); step += 1
+    pt.Finish()
+    # ---- timed region: device time, scene + queues resident in HBM ----
+    pt.reset_stats()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        pt.Render(cams[step % 16]); step += 1
+    e1.record(stream)
+    pt.Finish()
+    barrier()
+    sampler.stop_flag = True
+    ms = e0.elapsed_time(e1)
+    st = pt.stats()
+    rays = torch.tensor([st.extend_rays + st.shadow_rays, st.extend_rays, st.shadow_rays], dtype=torch.float64, device="cuda")
+    tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(rays)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms = float(tms.item())
+    total_rays, ext_rays, sh_rays = (float(x) for x in rays.tolist())
+    value = total_rays / (ms * 1e-3) / 1e6
+    # ---- per-stage device time of the same steps (separate pass: event pairs around every launch) ----
+    pt.set_profiling(True)
+    pt.reset_stats()
+    for _ in range(args.steps):
+        pt.Render(cams[step % 16]); step += 1
+    pt.Finish()
+    prof = pt.profile()
+    pst = pt.stats()
+    pt.set_profiling(False)
+    # ---- end to end through the public API with host buffers ----
+    img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
+    inst, tlas = arrays["instances"], arrays["topBvh"]
+    pt.reset_stats()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        pt.update_instances(inst, tlas)            # host -> device: instances + TLAS (camera rides in the launch parameters)
+        pt.Render(cams[step % 16]); step += 1
+        pt.Finish()
+        pt.read_image(0, out=img)                   # device -> host: the accumulated float4 image
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    est = pt.stats()
+    e2 = torch.tensor([est.extend_rays + est.shadow_rays, e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        r2 = e2[:1].clone(); dist.all_reduce(r2)
+        t2 = e2[1:].clone(); dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2 = torch.cat([r2, t2])
+    e2e_value = float(e2[0].item()) / float(e2[1].item()) / 1e6
+    if rank == 0:
+        peak, peak_src = read_peaks()
+        cpu_v, per_ray, cpu_s, cpu_rays = cpu_leg(arrays, os.cpu_count() or 1, 1)
+        # ALGORITHMIC bytes of one extend launch: per ray 32 (RayPacked R) + 16 (HitInfoPacked W)
+        # + 64 * N_inner + 48 * N_tri, N_* counted by the CPU oracle on the reference's BVH2 for the same scene/camera/depth
+        bytes_per_ext_ray = 48.0 + 64.0 * per_ray["ext_inner"] + 48.0 * per_ray["ext_tris"]
+        ext_ms, ext_n = prof["extend"]
+        achieved = (pst.extend_rays * bytes_per_ext_ray) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+        tot_prof_ms = sum(v[0] for v in prof.values())
+        launches_per_step = 1 + DEPTH * 3 + 2 + 1
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
+                           "cameras": "16-camera sweep inside the nave, one camera per step", "global_pixels": W * H},
+                "spp_per_s": args.steps / (ms * 1e-3), "rays_per_step": total_rays / args.steps,
+                "clocks": sampler.summary(),
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(inst.nbytes + tlas.nbytes + 76),
+                        "d2h_bytes_per_step": int(W * H * 16)},
+                "gpu_launches": int(launches_per_step * args.steps),
+                "roofline": {"bound": "hbm", "kernel": "k_trace<false> (extend)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": peak_src, "bytes_per_ray": bytes_per_ext_ray,
+                             "avg_launch_ms": ext_ms / max(1, ext_n), "share_of_step": ext_ms / tot_prof_ms if tot_prof_ms else None,
+                             "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray); HBM copy peak is the denominator"},
+                "stage_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
+                "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
+                                 "sample": "oracle/pt_oracle.cpp: 1 converge sample of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_W, CPU_H, cpu_rays, cpu_s)}}
+        print(json.dumps(line), flush=True)
+    pt.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

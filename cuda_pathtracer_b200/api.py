@@ -56,6 +56,8 @@ def load_library():
     L.pt_read_radiance_cache.argtypes = [C.c_void_p, C.c_void_p]
     L.pt_get_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
     L.pt_reset_stats.argtypes = [C.c_void_p]
+    L.pt_set_profiling.argtypes = [C.c_void_p, C.c_int]
+    L.pt_get_profile.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     L.pt_get_rand_state.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.pt_debug_primary_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
     L.pt_debug_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
@@ -168,6 +170,23 @@ class Pathtracer:
 
     def reset_stats(self):
         self._ck(self.L.pt_reset_stats(self.h), "pt_reset_stats")
+
+    STAGES = ("extend", "shade", "connect", "guiding", "other")
+
+    def set_profiling(self, on):
+        self._ck(self.L.pt_set_profiling(self.h, int(on)), "pt_set_profiling")
+
+    def profile(self):
+        """{stage: (device ms summed over launches, launches)} since set_profiling(True); call after Finish()."""
+        ms = (C.c_double * 5)()
+        n = (C.c_uint64 * 5)()
+        self._ck(self.L.pt_get_profile(self.h, ms, n), "pt_get_profile")
+        return {k: (ms[i], int(n[i])) for i, k in enumerate(self.STAGES)}
+
+    def update_instances(self, instances, tlas):
+        inst = np.ascontiguousarray(instances)
+        tl = np.ascontiguousarray(tlas)
+        self._ck(self.L.pt_update_instances(self.h, abi.ptr(inst), len(inst), abi.ptr(tl), len(tl)), "pt_update_instances")
 
     def rand_state(self):
         a, b = C.c_uint32(), C.c_uint32()

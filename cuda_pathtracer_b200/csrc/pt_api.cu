@@ -41,6 +41,13 @@ struct pt_ctx {
     pt_allreduce_hook hook = nullptr;
     void* hookUser = nullptr;
     int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0;
+    // per-stage timing (pt_set_profiling): CUDA event pairs around every stage launch, resolved in pt_finish
+    bool prof = false;
+    std::vector<cudaEvent_t> evPool;
+    struct Pending { int stage; cudaEvent_t a, b; };
+    std::vector<Pending> pending;
+    double profMs[PT_NUM_STAGES] = {0, 0, 0, 0, 0};
+    unsigned long long profLaunches[PT_NUM_STAGES] = {0, 0, 0, 0, 0};
     // debug buffers
     pt_ray* dbgRays = nullptr; pt_hit* dbgHits = nullptr; uint32_t dbgCap = 0; uint* dbgCursor = nullptr;
 };
@@ -55,6 +62,23 @@ struct pt_ctx {
             return e_ == cudaErrorMemoryAllocation ? PT_ERR_OOM : PT_ERR_CUDA;                            \
         }                                                                                                 \
     } while (0)
+
+static cudaEvent_t getEvent(pt_ctx* ctx) {
+    if (!ctx->evPool.empty()) { cudaEvent_t e = ctx->evPool.back(); ctx->evPool.pop_back(); return e; }
+    cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+}
+struct StageTimer {      // records an event pair on the context's stream around one stage launch
+    pt_ctx* ctx; int stage; cudaEvent_t a = nullptr, b = nullptr;
+    StageTimer(pt_ctx* c, int st) : ctx(c), stage(st) { if (ctx->prof) { a = getEvent(ctx); b = getEvent(ctx); cudaEventRecord(a, ctx->stream); } }
+    ~StageTimer() { if (a) { cudaEventRecord(b, ctx->stream); ctx->pending.push_back({stage, a, b}); } }
+};
+static void resolveProfile(pt_ctx* ctx) {   // call after the stream has been synchronised
+    for (auto& p : ctx->pending) {
+        float ms = 0; if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) { ctx->profMs[p.stage] += ms; ctx->profLaunches[p.stage]++; }
+        ctx->evPool.push_back(p.a); ctx->evPool.push_back(p.b);
+    }
+    ctx->pending.clear();
+}
 
 static int fail(pt_ctx* ctx, int code, const char* msg) { ctx->err = msg; return code; }
 
@@ -93,6 +117,8 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    resolveProfile(ctx);
+    for (auto e : ctx->evPool) cudaEventDestroy(e);
     for (auto t : ctx->textures) cudaDestroyTextureObject(t);
     for (auto a : ctx->arrays) cudaFreeArray(a);
     for (void* p : ctx->sceneAllocs) cudaFree(p);
@@ -352,28 +378,32 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
     const bool deviceNEE = ctx->DNEE && ctx->sc.num_lights > 0;                            // globals.h:23
     for (uint32_t sample = 0; sample < nsamples; sample++) {
         CK(cudaMemsetAsync(ctx->q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                   // :265 (+ cursors)
-        if (map.nSlots) k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, ctx->q, ctx->masks, ctx->accucolors);   // :258,:266
+        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER); k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, ctx->q, ctx->masks, ctx->accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
         uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
         if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
         else max_bounces = should_clear ? ctx->cfg.interactive_depth + 1 : ctx->cfg.max_ray_depth;
         for (uint32_t bounce = 0; bounce < max_bounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
-            k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->q.rayO[buf], ctx->q.rayD[buf], ctx->q.cnt + CNT_EXT(bounce),
-                                                             ctx->q.cnt + CUR_EXT(bounce), ctx->q.hits, nullptr, nullptr);
+            { StageTimer tm(ctx, PT_STAGE_EXTEND);
+              k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->q.rayO[buf], ctx->q.rayD[buf], ctx->q.cnt + CNT_EXT(bounce),
+                                                               ctx->q.cnt + CUR_EXT(bounce), ctx->q.hits, nullptr, nullptr); }
             ShadeParams P;
             P.sc = ctx->sc; P.map = map; P.tex = ctx->tex;
             P.masks = ctx->masks; P.accucolors = ctx->accucolors; P.lights = ctx->lights;
             P.sampleCache = ctx->sampleCache; P.albedo = ctx->albedo;
             P.sampleIdx = ctx->sampleIdx; P.randIdx = ctx->randIdx; P.blueFrames = ctx->cfg.blue_noise_frames;
             P.bounce = (int)bounce; P.nee = deviceNEE; P.cache = ctx->DCACHE;
-            k_shade<<<ctx->gridShade, 128, 0, s>>>(P, ctx->q, buf);
+            { StageTimer tm(ctx, PT_STAGE_SHADE); k_shade<<<ctx->gridShade, 128, 0, s>>>(P, ctx->q, buf); }
             ctx->randIdx++;                                                                // :283
-            if (ctx->HNEE && deviceNEE)                                                    // :286 (no shadow rays exist when the device _NEE is false)
+            if (ctx->HNEE && deviceNEE) {                                                  // :286 (no shadow rays exist when the device _NEE is false)
+                StageTimer tm(ctx, PT_STAGE_CONNECT);
                 k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, ctx->q.shO, ctx->q.shD, ctx->q.cnt + CNT_SHADOW(bounce),
                                                                 ctx->q.cnt + CUR_CONN(bounce), nullptr, ctx->lights, ctx->accucolors);
+            }
         }
         if (!should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots) {   // :292-296
+            StageTimer tm(ctx, PT_STAGE_GUIDING);
             k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             if (ctx->hook) {
                 int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
@@ -381,7 +411,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             }
             k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
         }
-        if (map.nSlots) k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->image, ctx->q.cnt, ctx->stats, max_bounces);   // :299
+        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER); k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->image, ctx->q.cnt, ctx->stats, max_bounces); }   // :299
         ctx->sampleIdx++;                                                                  // :300
     }
     CK(cudaGetLastError());
@@ -392,6 +422,19 @@ PT_API int pt_finish(pt_ctx* ctx) {                                             
     if (!ctx) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
     CK(cudaStreamSynchronize(ctx->stream));
+    resolveProfile(ctx);
+    return PT_OK;
+}
+
+PT_API int pt_set_profiling(pt_ctx* ctx, int on) {
+    if (!ctx) return PT_ERR_INVALID;
+    ctx->prof = on != 0;
+    for (int i = 0; i < PT_NUM_STAGES; i++) { ctx->profMs[i] = 0; ctx->profLaunches[i] = 0; }
+    return PT_OK;
+}
+PT_API int pt_get_profile(pt_ctx* ctx, double* ms, uint64_t* launches) {
+    if (!ctx) return PT_ERR_INVALID;
+    for (int i = 0; i < PT_NUM_STAGES; i++) { if (ms) ms[i] = ctx->profMs[i]; if (launches) launches[i] = ctx->profLaunches[i]; }
     return PT_OK;
 }
 

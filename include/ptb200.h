@@ -183,6 +183,15 @@ PT_API int  pt_render(pt_ctx*, const pt_camera*, int should_clear);   /* == Path
 PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
 PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
 PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
+/* Per-stage device time, CUDA events around every stage launch on the context's stream; resolved by pt_finish. */
+#define PT_STAGE_EXTEND 0
+#define PT_STAGE_SHADE 1
+#define PT_STAGE_CONNECT 2
+#define PT_STAGE_GUIDING 3
+#define PT_STAGE_OTHER 4
+#define PT_NUM_STAGES 5
+PT_API int  pt_set_profiling(pt_ctx*, int on);                         /* also resets the accumulators */
+PT_API int  pt_get_profile(pt_ctx*, double* ms /*[PT_NUM_STAGES]*/, uint64_t* launches /*[PT_NUM_STAGES]*/);
 PT_API int  pt_get_stats(pt_ctx*, pt_stats* out);
 PT_API int  pt_reset_stats(pt_ctx*);
 PT_API int  pt_get_rand_state(pt_ctx*, uint32_t* sampleIdx, uint32_t* randIdx);

@@ -113,7 +113,7 @@ class OracleLib:
 
     def stats(self):
         st = abi.Stats()
-        cnt = (C.c_uint64 * 3)()
+        cnt = (C.c_uint64 * 6)()
         self.L.ora_get_stats(self.h, C.byref(st), cnt)
         return st, list(cnt)
 

@@ -445,7 +445,7 @@ struct Oracle {
     std::vector<pt_hit> hits;
     std::vector<pt_sample_cache> sampleCache;   // NR_PIXELS * MAX_CACHE_DEPTH, pathtracer.h:209
     std::vector<F4> image, albedo;              // stand-ins for the two GL RGBA32F textures (main.cpp:214-260)
-    Counters cnt;
+    Counters cnt, cntConn;      // extend / connect traversal counters (algorithmic bytes)
     pt_stats stats;
     int threads;
 };
@@ -728,7 +728,7 @@ static void connect(Oracle& o) {
         F4& a = o.accucolors[sr.pixeli];
         a.x += l.x; a.y += l.y; a.z += l.z; a.w += 0.0f;
     }
-    o.cnt.inner += inner; o.cnt.tris += tris; o.cnt.tlas += tlas;
+    o.cntConn.inner += inner; o.cntConn.tris += tris; o.cntConn.tlas += tlas;
     o.stats.shadow_rays += n;
 }
 // kernel_add_to_screen, kernels.h:812-824
@@ -844,7 +844,7 @@ ORA_API void* ora_create(const pt_config* cfg) {
     o->sampleCache.assign((size_t)o->NP * MAX_CACHE_DEPTH, sc0);
     memset(&o->sc.d, 0, sizeof(o->sc.d));
     o->sc.hasSky = false; o->sc.skyConst = mk3(1, 1, 1); o->sc.hasBlue = false;
-    memset(&o->cnt, 0, sizeof(o->cnt)); memset(&o->stats, 0, sizeof(o->stats));
+    memset(&o->cnt, 0, sizeof(o->cnt)); memset(&o->cntConn, 0, sizeof(o->cntConn)); memset(&o->stats, 0, sizeof(o->stats));
     o->threads = 0;
     return o;
 }
@@ -889,9 +889,10 @@ ORA_API void ora_read_image(void* h, float* out, int which) {
 ORA_API void ora_read_radiance_cache(void* h, pt_radiance_cache* out) { Oracle& o = *(Oracle*)h; memcpy(out, o.sc.rc.data(), o.sc.rc.size() * sizeof(pt_radiance_cache)); }
 ORA_API void ora_get_stats(void* h, pt_stats* st, uint64_t* counters3) {
     Oracle& o = *(Oracle*)h; if (st) *st = o.stats;
-    if (counters3) { counters3[0] = o.cnt.inner; counters3[1] = o.cnt.tris; counters3[2] = o.cnt.tlas; }
+    if (counters3) { counters3[0] = o.cnt.inner; counters3[1] = o.cnt.tris; counters3[2] = o.cnt.tlas;
+                     counters3[3] = o.cntConn.inner; counters3[4] = o.cntConn.tris; counters3[5] = o.cntConn.tlas; }   // [0..2] extend, [3..5] connect
 }
-ORA_API void ora_reset_stats(void* h) { Oracle& o = *(Oracle*)h; memset(&o.cnt, 0, sizeof(o.cnt)); memset(&o.stats, 0, sizeof(o.stats)); }
+ORA_API void ora_reset_stats(void* h) { Oracle& o = *(Oracle*)h; memset(&o.cnt, 0, sizeof(o.cnt)); memset(&o.cntConn, 0, sizeof(o.cntConn)); memset(&o.stats, 0, sizeof(o.stats)); }
 ORA_API void ora_get_rand_state(void* h, uint32_t* sampleIdx, uint32_t* randIdx) { Oracle& o = *(Oracle*)h; *sampleIdx = o.sampleIdx; *randIdx = o.randIdx; }
 
 // Camera as the reference's host prepares it: ctor + update() with no key down (types.h:609-637):
