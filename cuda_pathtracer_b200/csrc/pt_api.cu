@@ -130,6 +130,28 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     delete ctx;
 }
 
+static TileMap makeTileMap(const pt_config* cfg) {
+    TileMap m;
+    m.W = cfg->width; m.H = cfg->height;
+    m.tilesX = (m.W + 31) / 32; m.tilesY = (m.H + 31) / 32;
+    m.rank = cfg->rank; m.world = cfg->world_size;
+    const uint32_t T = m.tilesX * m.tilesY;
+    m.nLocalTiles = T > m.rank ? (T - m.rank + m.world - 1) / m.world : 0;
+    m.nSlots = m.nLocalTiles * 1024u;
+    return m;
+}
+// Host view of the tile partition (no GPU needed): the same mapping the kernels use.
+PT_API uint32_t pt_tile_num_slots(const pt_config* cfg) {
+    if (!cfg || cfg->world_size == 0 || cfg->rank >= cfg->world_size) return 0;
+    return makeTileMap(cfg).nSlots;
+}
+PT_API int pt_tile_slot_to_pixel(const pt_config* cfg, uint32_t slot, uint32_t* x, uint32_t* y) {
+    if (!cfg || !x || !y || cfg->world_size == 0 || cfg->rank >= cfg->world_size) return PT_ERR_INVALID;
+    const TileMap m = makeTileMap(cfg);
+    if (slot >= m.nSlots) return PT_ERR_INVALID;
+    return slotToPixel(m, slot, *x, *y) ? 1 : 0;
+}
+
 PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
     if (!out || !cfg) { g_createError = "pt_create: null argument"; return PT_ERR_INVALID; }
     *out = nullptr;
@@ -154,12 +176,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
         CK(cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, cfg->device));
         TileMap& m = ctx->map;
-        m.W = cfg->width; m.H = cfg->height;
-        m.tilesX = (m.W + 31) / 32; m.tilesY = (m.H + 31) / 32;
-        m.rank = cfg->rank; m.world = cfg->world_size;
-        const uint32_t T = m.tilesX * m.tilesY;
-        m.nLocalTiles = T > m.rank ? (T - m.rank + m.world - 1) / m.world : 0;
-        m.nSlots = m.nLocalTiles * 1024u;
+        m = makeTileMap(cfg);
         const size_t cap = std::max<uint32_t>(m.nSlots, 1024u);
         int r;
         for (int i = 0; i < 2; i++) {

@@ -202,7 +202,12 @@ PT_API int  pt_debug_trace(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any
 /* Device-resident variant used for kernel-only timing: rays stay in HBM, returns elapsed ms (CUDA events). */
 PT_API int  pt_debug_trace_resident(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, uint32_t repeats, float* out_ms, pt_hit* host_out);
 
-PT_API void* pt_cuda_stream(pt_ctx*);   /* the stream every launch of this context goes to */
+PT_API void* pt_cuda_stream(pt_ctx*);
+
+/* Tile partition, host-callable without a GPU: 32x32-pixel tiles dealt round-robin to
+ * ranks; a rank's local slot = (local tile, 8x4 block, lane).  Returns 1 (pixel), 0 (slot off the image). */
+PT_API uint32_t pt_tile_num_slots(const pt_config* cfg);
+PT_API int  pt_tile_slot_to_pixel(const pt_config* cfg, uint32_t slot, uint32_t* x, uint32_t* y);   /* the stream every launch of this context goes to */
 
 #ifdef __cplusplus
 }

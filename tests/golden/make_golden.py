@@ -22,6 +22,22 @@ CAM_TEAPOT = ((0, 2, -6), (0, 0, 1), 1.5, 5, 0.01)
 CAM_OUTSIDE = ((9.81771, 13.5924, -1.12687), (-0.65847, -0.544656, 0.519391), 1.5, 8.49543, 6.50994e-10)   # save.txt:1-5
 
 
+def obj_order_soup(path):
+    """Triangle vertices in OBJ file order (before any BVH permutation), float32 (n, 9)."""
+    v, tris = [], []
+    for line in open(path):
+        t = line.split()
+        if not t:
+            continue
+        if t[0] == "v":
+            v.append([np.float32(float(x)) for x in t[1:4]])
+        elif t[0] == "f":
+            idx = [int(x.split("/")[0]) - 1 for x in t[1:]]
+            assert len(idx) == 3
+            tris.append(v[idx[0]] + v[idx[1]] + v[idx[2]])
+    return np.array(tris, np.float32)
+
+
 def pack(arrays):
     out = {k: v for k, v in arrays.items() if k != "bvh"}
     for i, b in enumerate(arrays["bvh"]):
@@ -65,6 +81,8 @@ def main():
         a["rays_160x120"] = rays
         a["hits_160x120"] = s.trace(rays, False, 1)
         a["anyhits_160x120"] = s.trace(rays, True, 1)
+        if name == "teapot":
+            a["soup_obj_order"] = obj_order_soup("/root/reference/teapot.obj")
         np.savez_compressed(os.path.join(HERE, name + "_scene.npz"), **a)
     s = teapot(ref_full)
     rays = ref_full.primary_rays(*CAM_TEAPOT, 0)
