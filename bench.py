@@ -147,16 +147,8 @@ def gpu_arm(args):
     pt = api.Pathtracer(arrays, cfg).Init()
     stream = torch.cuda.ExternalStream(pt.stream(), device=torch.device("cuda", local))
     if world > 1:
-        class _Dev:      # wraps the radiance-cache additions buffer (device pointer from the C ABI) as a tensor
-            def __init__(self, p, n):
-                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (p, False), "version": 2}
-
-        def hook(p, n, s):
-            t = torch.as_tensor(_Dev(p, n), device=torch.device("cuda", local))
-            with torch.cuda.stream(stream):
-                dist.all_reduce(t)      # NCCL sum over NVLink, ordered on the path tracer's stream
-            return 0
-        pt.set_allreduce_hook(hook)
+        from cuda_pathtracer_b200.distributed import make_allreduce_hook
+        pt.set_allreduce_hook(make_allreduce_hook(torch.device("cuda", local), stream))   # NCCL sum over NVLink on the tracer's stream
     cams = [camera_for(i, W, H) for i in range(16)]
 
     def barrier():

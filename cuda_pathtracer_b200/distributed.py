@@ -1,0 +1,50 @@
+"""Multi-GPU plumbing: one process per GPU, image tiles dealt round-robin to ranks (pt_config.rank /
+world_size), scene replicated, and ONE collective per guiding-training frame: an in-place SUM all-reduce of
+the radiance-cache additions (additionCache || additionCacheCount, 16 floats per triangle) between the
+local update and the propagate step (reference kernels: src/kernels.h:863-905).
+torch.distributed is the transport (NCCL over NVLink on GPUs, gloo in the CPU tests)."""
+import ctypes as C
+
+import numpy as np
+
+
+class _DevBuf:
+    """__cuda_array_interface__ view of a raw device pointer handed out by the C ABI."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def wrap_float_buffer(ptr, n, device):
+    """torch view (no copy) of n floats at `ptr`: device memory for cuda devices, host memory for 'cpu'."""
+    import torch
+    if str(device).startswith("cuda"):
+        return torch.as_tensor(_DevBuf(ptr, n), device=device)
+    buf = (C.c_float * n).from_address(int(ptr))
+    return torch.from_numpy(np.frombuffer(buf, dtype=np.float32, count=n))
+
+
+def make_allreduce_hook(device, stream=None, group=None):
+    """Returns fn(ptr, count, stream_handle) -> 0 for Pathtracer.set_allreduce_hook: sums the additions buffer
+    over all ranks in place, ordered on the path tracer's stream."""
+    import torch
+    import torch.distributed as dist
+
+    def hook(ptr, count, _stream_handle):
+        t = wrap_float_buffer(ptr, count, device)
+        if stream is not None:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(t, group=group)
+        else:
+            dist.all_reduce(t, group=group)
+        return 0
+    return hook
+
+
+def gather_image(local_image, group=None):
+    """Every rank holds a full-size float4 image with zeros outside its tiles: the sum is the framebuffer."""
+    import torch
+    import torch.distributed as dist
+    t = local_image if isinstance(local_image, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(local_image))
+    dist.all_reduce(t, group=group)
+    return t

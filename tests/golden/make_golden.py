@@ -35,7 +35,7 @@ def obj_order_soup(path):
             idx = [int(x.split("/")[0]) - 1 for x in t[1:]]
             assert len(idx) == 3
             tris.append(v[idx[0]] + v[idx[1]] + v[idx[2]])
-    return np.array(tris, np.float32)
+    return np.array(tris, np.float32) + np.float32(0.0)   # the identity bake-in transform (scene.h:285-291) turns -0 into +0
 
 
 def pack(arrays):

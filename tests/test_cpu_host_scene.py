@@ -1,0 +1,153 @@
+"""CPU tests of the product's host scene code (libptb200.so, no GPU): the binned-SAH builder, TLAS,
+instance matrices, camera and OBJ reader must produce arrays bit-identical to the reference's own host
+code -- checked against the committed golden arrays everywhere, and directly against oracle/_ref (the
+reference's headers compiled here) when that library is present (marker `ref`)."""
+import os
+
+import numpy as np
+import pytest
+
+from cuda_pathtracer_b200 import abi, scenes
+from cuda_pathtracer_b200.scene import Scene, make_camera, material
+from oracle import oracle_py
+from util import load_golden_scene
+
+HAVE_REF = oracle_py.ref_available(160, 120)
+REFDIR = "/root/reference"
+
+
+def _same_bits(x, y):
+    return np.array_equal(np.ascontiguousarray(x).view(np.uint32), np.ascontiguousarray(y).view(np.uint32))
+
+
+def assert_scene_equal(mine, ref, uv=True):
+    assert len(mine["vertices"]) == len(ref["vertices"])
+    for f in ("v0", "v1", "v2"):
+        assert _same_bits(mine["vertices"][f], ref["vertices"][f]), "vertices." + f
+    fields = ("normal", "material") + (("uv0", "uv1", "uv2") if uv else ())
+    for f in fields:
+        assert _same_bits(mine["vertexData"][f], ref["vertexData"][f]), "vertexData." + f
+    for f in ("triangleStart", "nrTriangles", "nrBvhNodes"):
+        assert np.array_equal(mine["models"][f], ref["models"][f]), "models." + f
+    for i, (a, b) in enumerate(zip(mine["bvh"], ref["bvh"])):
+        assert a.tobytes() == b.tobytes(), "BVH2 of model %d" % i
+    for f in ("model_id", "transform", "invTransform", "material_id"):
+        assert _same_bits(mine["instances"][f], ref["instances"][f]), "instances." + f
+    a, b = mine["topBvh"], ref["topBvh"]
+    assert len(a) == len(b)
+    for f in ("vmin", "vmax", "children"):
+        assert _same_bits(a[f], b[f]), "topBvh." + f
+    leaf = a["children"] == 0
+    assert np.array_equal(a["leaf"][leaf], b["leaf"][leaf])      # `leaf` of inner nodes is uninitialised in the reference
+    assert mine["spheres"].tobytes() == ref["spheres"].tobytes() and mine["planes"].tobytes() == ref["planes"].tobytes()
+
+
+def test_builder_reproduces_golden_teapot(built):
+    """createBVHBinned restated: OBJ-order soup -> the reference's permuted triangles and 4129-node BVH2."""
+    g = load_golden_scene("teapot")
+    s = Scene()
+    m = s.addMaterial(material())
+    s.addObject(s.addModelSoup(g["soup_obj_order"], material=m))
+    s.finalize()
+    a = s.arrays()
+    assert_scene_equal(a, g, uv=False)
+    cam = make_camera(g["cam_in"][0:3], g["cam_in"][3:6], g["cam_in"][6], g["cam_in"][7], g["cam_in"][8], 160, 120)
+    for f in ("eye", "viewDir", "lt", "u", "v", "d", "focalLength", "aperture"):
+        assert _same_bits(np.asarray(cam[0][f]), np.asarray(g["camera_160x120"][0][f])), f
+
+
+def test_outside_preset_matches_golden_layout(built):
+    """getOutsideScene preset: 10 glass cube instances + checker plane; instance matrices and TLAS from the
+    golden positions must be reproduced bit for bit (glm restatement, agglomerative TLAS)."""
+    g = load_golden_scene("outside")
+    s = Scene()
+    s.addMaterial(material((0.4, 0.4, 0.4)))
+    cube = s.addMaterial(material((1, 1, 1), transmit=1.0, refractive_index=1.1, glossy=0.02, absorption=(0.1, 0.5, 0.8)))
+    # rebuild from the golden triangles in golden order is not order-neutral; use positions/rotations only
+    mod = s.addModelSoup(np.concatenate([g["vertices"]["v0"], g["vertices"]["v1"], g["vertices"]["v2"]], axis=1), material=cube)
+    inst = g["instances"]
+    f = np.float32(0)
+    for i in range(10):
+        pos = (float(inst["transform"][i][0][3]), float(inst["transform"][i][1][3]), float(inst["transform"][i][2][3]))
+        s.addObject(mod, position=pos, rotation=(float(f), 0, 0))
+        f = np.float32(f + np.float32(2 * 0.3141592))
+    s.addPlane((0, -1, 0), -3, 0)
+    s.finalize()
+    a = s.arrays()
+    for fld in ("transform", "invTransform"):
+        assert _same_bits(a["instances"][fld], inst[fld]), fld
+    # the cube BVH rebuilt from already-permuted triangles keeps the root box, so the TLAS is comparable
+    for fld in ("vmin", "vmax", "children"):
+        assert _same_bits(a["topBvh"][fld], g["topBvh"][fld]), fld
+
+
+def test_tile_map_covers_every_pixel_once(built):
+    import ctypes as C
+    from cuda_pathtracer_b200 import api
+    L = api.load_library()
+    L.pt_tile_num_slots.restype = C.c_uint32
+    for (w, h, world) in ((100, 70, 1), (100, 70, 3), (1920, 1080, 8)):
+        seen = np.zeros((h, w), np.int32)
+        for rank in range(world):
+            cfg = abi.default_config(w, h, rank=rank, world_size=world)
+            n = L.pt_tile_num_slots(C.byref(cfg))
+            assert n % 1024 == 0
+            step = 1 if w * h < 100000 else 37          # sample the big case
+            x, y = C.c_uint32(), C.c_uint32()
+            for slot in range(0, n, step):
+                r = L.pt_tile_slot_to_pixel(C.byref(cfg), slot, C.byref(x), C.byref(y))
+                assert r in (0, 1)
+                if r == 1:
+                    seen[y.value, x.value] += 1
+                    assert ((y.value // 32) * ((w + 31) // 32) + x.value // 32) % world == rank
+        if w * h < 100000:
+            assert np.all(seen == 1)
+        else:
+            assert seen.max() == 1
+
+
+@pytest.mark.ref
+@pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("obj,scale,rot,off", [("teapot.obj", 1.0, (0, 0, 0), (0, 0, 0)), ("cube.obj", 1.0, (0, 0, 0), (0, 0, 0)),
+                                               ("house.obj", 0.04, (0.3, -1.2, 0.5), (1, 2, 3))])
+def test_obj_loader_and_builder_vs_reference(built, obj, scale, rot, off):
+    """Scene::addModel on the reference's own OBJ assets (triangles and 4/5-gons): same triangle order, same BVH2,
+    same instances and TLAS as the reference's tinyobjloader + createBVHBinned + glm + BuildTopLevelBVH."""
+    path = os.path.join(REFDIR, obj)
+    ref = oracle_py.RefLib(160, 120)
+    rs = oracle_py.RefScene(ref)
+    m = rs.add_material()
+    mod = rs.add_model_obj(path, scale, rot, off, m)
+    objs = [((1, 2, 3), (0.1, 0.2, 0.3), (1, 1, 1)), ((-4, 0, 1), (1, 0, 2), (0.5, 0.5, 0.5)), ((8, 1, -3), (0, 0, 0), (1, 1, 1))]
+    for p, r, sc in objs:
+        rs.add_object(mod, pos=p, rot=r, scale=sc)
+    rs.add_sphere((0, 1, 2), 2, 0)
+    rs.add_plane((0, -1, 0), -3, 0)
+    rs.finalize()
+    s = Scene()
+    s.addMaterial(material())
+    mod = s.addModel(path, scale, rot, off, 0)
+    for p, r, sc in objs:
+        s.addObject(mod, position=p, rotation=r, scale=sc)
+    s.addSphere((0, 1, 2), 2, 0)
+    s.addPlane((0, -1, 0), -3, 0)
+    s.finalize()
+    # house.obj has faces without vt: the reference then reads texcoords[-2] (scene.h:272, index -1) -> skip uv there
+    assert_scene_equal(s.arrays(), rs.arrays(), uv=(obj != "house.obj"))
+
+
+@pytest.mark.ref
+@pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref not built (needs /root/reference)")
+def test_procedural_proxy_builds_identically_in_reference(built):
+    """The sibenik proxy soup through the reference's createBVHBinned vs the product's builder (138k triangles)."""
+    soup = scenes.cathedral_soup(1)
+    ref = oracle_py.RefLib(160, 120)
+    rs = oracle_py.RefScene(ref)
+    m = rs.add_material()
+    rs.add_object(rs.add_model_soup(soup, material=m), pos=(0, 12, 0))
+    rs.finalize()
+    s = Scene()
+    s.addMaterial(material())
+    s.addObject(s.addModelSoup(soup, material=0), position=(0, 12, 0))
+    s.finalize()
+    assert_scene_equal(s.arrays(), rs.arrays(), uv=True)
