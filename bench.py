@@ -122,7 +122,7 @@ def reference_arm(args):
         total_s += dt
     v = total_rays / total_s / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": {"workload": WORKLOAD, "sample": "%dx%d pixels of the same scene/camera/depth per step" % (CPU_W, CPU_H)},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
                              "sample": "oracle/pt_oracle.cpp, 1 converge sample at %dx%d per step, OpenMP %d threads" % (CPU_W, CPU_H, threads)},
@@ -225,7 +225,7 @@ def gpu_arm(args):
         tot_prof_ms = sum(v[0] for v in prof.values())
         launches_per_step = 1 + DEPTH * 3 + 2 + 1
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
                            "cameras": "16-camera sweep inside the nave, one camera per step", "global_pixels": W * H},
                 "spp_per_s": args.steps / (ms * 1e-3), "rays_per_step": total_rays / args.steps,
