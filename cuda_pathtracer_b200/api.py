@@ -22,7 +22,8 @@ class PtError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libptb200.so")
+    # PTB200_LIB: developer knob for kernel tuning (tools/tune.sh builds variants of the same library)
+    return os.environ.get("PTB200_LIB") or os.path.join(_HERE, "libptb200.so")
 
 
 def load_library():

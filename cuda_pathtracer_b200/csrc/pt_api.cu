@@ -29,7 +29,7 @@ struct pt_ctx {
     DScene sc;
     bool haveScene = false;
     std::vector<void*> sceneAllocs;
-    uint32_t numInstancesCap = 0, numTlasCap = 0;
+    uint32_t numInstancesCap = 0, numTlasCap = 0, maxWideDepth = 0;
     // textures
     FrameTex tex;
     std::vector<cudaArray_t> arrays;
@@ -302,19 +302,22 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     memset(&sc, 0, sizeof(sc));
     // wide BVH per model (host), one node array / one triangle-record array for the whole scene
     std::vector<WideNode> nodes; std::vector<WideTri> wtris; std::vector<DModel> models(d->num_models);
+    uint32_t maxWide = 0;
     for (uint32_t m = 0; m < d->num_models; m++) {
         const pt_model& pm = d->models[m];
         if (!pm.bvh || pm.nrBvhNodes == 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: model without BVH");
         WideBuildStats st;
         models[m].rootNode = buildWideBVH(pm.bvh, pm.nrBvhNodes, d->vertices, nodes, wtris, &st);
         models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;
-        if (st.max_depth >= PT_STACK - 1) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: wide BVH deeper than the traversal stack");
+        maxWide = std::max(maxWide, st.max_depth);
         if (st.tris != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
     }
     for (uint32_t i = 0; i < d->num_instances; i++)
         if (d->instances[i].model_id >= d->num_models) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instance model_id out of range");
-    if (d->num_instances && d->num_tlas_nodes && tlasDepth(d->topBvh, d->num_tlas_nodes, 0, 0) >= PT_STACK)
-        return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: top-level BVH deeper than the traversal stack");
+    // unified traversal stack: TLAS entries below the node groups of the instance being traversed
+    ctx->maxWideDepth = maxWide;
+    if (d->num_instances && d->num_tlas_nodes && tlasDepth(d->topBvh, d->num_tlas_nodes, 0, 0) + maxWide + 2 > PT_STACK)
+        return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: top-level + bottom-level BVH deeper than the traversal stack");
     // emissive triangles (pathtracer.h:155-167)
     std::vector<pt_triangle_light> lights;
     for (uint32_t i = 0; i < d->num_instances; i++) {
@@ -362,7 +365,7 @@ PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n,
     if (!ctx || !ctx->haveScene) return PT_ERR_INVALID;
     if (n != ctx->numInstancesCap || n_nodes != ctx->numTlasCap) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: counts differ from the uploaded scene");
     CK(cudaSetDevice(ctx->cfg.device));
-    if (tlasDepth(tlas, n_nodes, 0, 0) >= PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: top-level BVH too deep");
+    if (tlasDepth(tlas, n_nodes, 0, 0) + ctx->maxWideDepth + 2 > PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: top-level BVH too deep");
     // pathtracer.h:245-246; pageable sources are staged before the call returns
     CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync((void*)ctx->sc.tlas, tlas, n_nodes * sizeof(pt_tlas_node), cudaMemcpyHostToDevice, ctx->stream));

@@ -17,6 +17,8 @@ typedef unsigned int uint;
 #define PT_MAX_CACHE_DEPTH 3                /* constants.h:14 */
 #define PT_MAX_BOUNCES 64
 
+__device__ __forceinline__ uint laneId() { uint l; asm("mov.u32 %0, %%laneid;" : "=r"(l)); return l; }
+
 // ---- float3 helpers with the reference's operator semantics (src/cutil_math.h) -------------------
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 __device__ __forceinline__ float3 f3(float s) { return make_float3(s, s, s); }

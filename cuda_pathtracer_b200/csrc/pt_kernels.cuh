@@ -26,7 +26,6 @@ struct Queues {
     uint* cnt;
 };
 
-__device__ __forceinline__ uint laneId() { uint l; asm("mov.u32 %0, %%laneid;" : "=r"(l)); return l; }
 // One atomic per warp: ballot the survivors, the first one reserves popc slots, everyone writes at
 // base + rank.  Must be called by all 32 lanes.
 __device__ __forceinline__ uint warpAppend(bool pred, uint* counter) {
@@ -94,59 +93,21 @@ __global__ void k_primary_debug(DCamera cam, uint W, uint H, uint randIdx, pt_ra
 }
 
 // ---- extend / connect ---------------------------------------------------------------------------------------
-// Persistent warps: each warp claims 32 consecutive queue entries with one atomic, traces them, and
-// comes back for more, so a warp that drew short rays does not idle while another is still deep in
-// the tree.  count/cursor are device-side: the host never reads queue sizes (reference README.md:201).
+// Persistent warps running the flat two-level traversal with dynamic ray fetch (pt_trace.cuh traceLoop).
+// count/cursor are device-side: the host never reads queue sizes (reference README.md:201).
 template <bool ANY>
 __global__ void __launch_bounds__(128) k_trace(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
                                                const float4* __restrict__ lights, float4* accucolors) {
-    const uint n = *count;
-    const uint lane = laneId();
-    while (true) {
-        uint base = 0;
-        if (lane == 0) base = atomicAdd(cursor, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const uint i = base + lane;
-        if (i < n) {
-            const float4 o4 = rayO[i], d4 = rayD[i];
-            const Hit h = traceTop<ANY>(sc, f3(o4), f3(d4), o4.w);
-            if (ANY) {
-                if (h.id == 0xffffffffu) {                                   // unoccluded: kernels.h:806-809
-                    const uint slot = __float_as_uint(d4.w);
-                    const float4 l = lights[slot];
-                    float4 a = accucolors[slot];
-                    a.x += l.x; a.y += l.y; a.z += l.z;
-                    accucolors[slot] = a;
-                }
-            } else {
-                hits[i] = make_float4(__uint_as_float(h.type), __uint_as_float(h.id), __uint_as_float(h.inst), h.t);
-            }
-        }
-    }
+    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors;
+    traceLoop<ANY>(sc, *count, cursor, io);
 }
 
 // stage-parity hook: reference-format rays in, reference-format hits out (pt_debug_trace)
 template <bool ANY>
 __global__ void __launch_bounds__(128) k_trace_debug(DScene sc, const pt_ray* __restrict__ rays, uint n, uint* cursor, pt_hit* __restrict__ out) {
-    const uint lane = laneId();
-    while (true) {
-        uint base = 0;
-        if (lane == 0) base = atomicAdd(cursor, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const uint i = base + lane;
-        if (i < n) {
-            const float4 o4 = *reinterpret_cast<const float4*>(&rays[i].origin), d4 = *reinterpret_cast<const float4*>(&rays[i].direction);
-            Hit h = traceTop<ANY>(sc, f3(o4), f3(d4), o4.w);
-            if (h.id == 0xffffffffu) { h.type = 0; h.inst = 0; }
-            else if (ANY) { h.type = 0; h.inst = 0; h.id = 0; }
-            else if (h.type != 0) h.inst = 0;
-            pt_hit p; p.primitive_type = h.type; p.primitive_id = h.id; p.instance_id = h.inst; p.t = h.t;
-            out[i] = p;
-        }
-    }
+    DebugIO io; io.rays = rays; io.out = out;
+    traceLoop<ANY>(sc, n, cursor, io);
 }
 
 // ---- shade ----------------------------------------------------------------------------------------------------

@@ -69,144 +69,240 @@ __device__ __forceinline__ bool triIntersect(float3 o, float3 d, float3 v0, floa
     return t > 0.0f;
 }
 
-#define PT_STACK 32
 
-// Bottom level: 8-wide compressed BVH, one thread per ray, node-group stack (Ylitie et al. 2017).
-// Closest hit keeps the candidate with the smallest t (strict <, like kernels.h:228); among exactly
-// equal t the lowest reference triangle id wins, which makes the result independent of visit order.
-template <bool ANY>
-__device__ __forceinline__ bool traceBLAS(const DScene& sc, uint rootNode, float3 o, float3 d, float& tbest, uint& hitId) {
-    const float ooeps = 8.271806125530277e-25f;   // 2^-80
-    float3 idir;
-    idir.x = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-    idir.y = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-    idir.z = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-    const uint octinv = (d.x < 0.0f ? 0u : 4u) | (d.y < 0.0f ? 0u : 2u) | (d.z < 0.0f ? 0u : 1u);
-    const uint octinv4 = octinv * 0x01010101u;
-    float tcull = tbest * 1.000001f;               // slack: box distances are not computed like triangle distances
+#define PT_STACK 40            /* unified stack: TLAS entries + BLAS node groups + postponed triangle groups */
+#define PT_NONE 0xffffffffu
+#ifndef PT_TRIS_PER_ITER
+#define PT_TRIS_PER_ITER 2     /* triangle tests a lane performs per loop trip before node work resumes */
+#endif
+#ifndef PT_REFILL_DIV
+#define PT_REFILL_DIV 4        /* fetch new rays once width/PT_REFILL_DIV lanes of the warp are idle */
+#endif
 
-    uint2 stack[PT_STACK];
-    int sp = 0;
-    uint2 ngroup = make_uint2(rootNode, 0x80000000u);
-    bool found = false;
+// Per-lane traversal state of the flat (single-loop) two-level traversal.  A lane is in exactly one
+// of: TLAS step pending (curT), BLAS node group pending (ngroup), triangles pending (tgroup), or
+// needs a pop.  Logical per-ray order == the reference's nested loops (kernels.h:277-387 outside,
+// one bottom-level traversal per TLAS leaf inside): TLAS entries sit below the BLAS entries of the
+// instance being traversed, so an instance is finished before the top level resumes.
+struct LaneState {
+    float3 o, d, idir;          // ray in the CURRENT space (world in the top level, model inside an instance)
+    float tbest, tcull;
+    uint ray;                   // queue index of the ray in flight, PT_NONE when the lane is idle
+    uint hitId, hitInst, hitType;
+    uint curT;                  // TLAS node to process next (PT_NONE: none)
+    uint curInst;               // instance being traversed
+    uint octinv;
+    uint2 ngroup, tgroup;
+    int sp;
+    bool inBLAS, found;
+};
 
-    while (true) {
-        uint2 tgroup = make_uint2(0u, 0u);
-        if (ngroup.y > 0x00FFFFFFu) {
-            const uint bit = 31u - __clz(ngroup.y);
-            ngroup.y &= ~(1u << bit);
-            if (ngroup.y > 0x00FFFFFFu) { stack[sp++] = ngroup; }
-            const uint slot = (bit - 24u) ^ octinv;
-            const uint rel = __popc(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
-            const float4* np = sc.nodes + (size_t)(ngroup.x + rel) * 5;
-            const float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
-            const uint ew = __float_as_uint(n0.w);
-            const float sx = __uint_as_float((ew & 0xffu) << 23), sy = __uint_as_float(((ew >> 8) & 0xffu) << 23), sz = __uint_as_float(((ew >> 16) & 0xffu) << 23);
-            const float aix = sx * idir.x, aiy = sy * idir.y, aiz = sz * idir.z;
-            const float aox = (n0.x - o.x) * idir.x, aoy = (n0.y - o.y) * idir.y, aoz = (n0.z - o.z) * idir.z;
-            ngroup.x = __float_as_uint(n1.x);
-            tgroup.x = __float_as_uint(n1.y);
-            uint hitmask = 0;
-#pragma unroll
-            for (int half = 0; half < 2; half++) {
-                const uint meta4 = __float_as_uint(half ? n1.w : n1.z);
-                const uint is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint inner_mask4 = signExtendS8x4(is_inner4 << 3);
-                const uint bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
-                const uint child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint qlx = __float_as_uint(half ? n2.y : n2.x), qly = __float_as_uint(half ? n2.w : n2.z), qlz = __float_as_uint(half ? n3.y : n3.x);
-                const uint qhx = __float_as_uint(half ? n3.w : n3.z), qhy = __float_as_uint(half ? n4.y : n4.x), qhz = __float_as_uint(half ? n4.w : n4.z);
-                const uint nx = d.x < 0.0f ? qhx : qlx, fx = d.x < 0.0f ? qlx : qhx;
-                const uint ny = d.y < 0.0f ? qhy : qly, fy = d.y < 0.0f ? qly : qhy;
-                const uint nz = d.z < 0.0f ? qhz : qlz, fz = d.z < 0.0f ? qlz : qhz;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const float tnx = __fmaf_rn((float)extractByte(nx, j), aix, aox), tny = __fmaf_rn((float)extractByte(ny, j), aiy, aoy), tnz = __fmaf_rn((float)extractByte(nz, j), aiz, aoz);
-                    const float tfx = __fmaf_rn((float)extractByte(fx, j), aix, aox), tfy = __fmaf_rn((float)extractByte(fy, j), aiy, aoy), tfz = __fmaf_rn((float)extractByte(fz, j), aiz, aoz);
-                    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-                    const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tcull));
-                    if (cmin <= cmax) hitmask |= extractByte(child_bits4, j) << extractByte(bit_index4, j);
-                }
+// Ray sources/sinks.  load() must be repeatable (the world-space ray is re-read when an instance is left).
+struct QueueIO {                // the wavefront queues: SoA float4 streams
+    const float4* rayO; const float4* rayD; float4* hits; const float4* lights; float4* accucolors;
+    __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const { o4 = rayO[i]; d4 = rayD[i]; }
+    template <bool ANY> __device__ __forceinline__ void store(uint i, const LaneState& L) const {
+        if (ANY) {
+            if (L.hitId == PT_NONE) {                                         // unoccluded: kernels.h:806-809
+                const uint slot = __float_as_uint(rayD[i].w);
+                const float4 l = lights[slot];
+                float4 a = accucolors[slot];
+                a.x += l.x; a.y += l.y; a.z += l.z;
+                accucolors[slot] = a;
             }
-            ngroup.y = (hitmask & 0xFF000000u) | (ew >> 24);
-            tgroup.y = hitmask & 0x00FFFFFFu;
-        }
-        while (tgroup.y != 0u) {
-            const uint ti = 31u - __clz(tgroup.y);
-            tgroup.y &= ~(1u << ti);
-            const float4* tp = sc.wtris + (size_t)(tgroup.x + ti) * 3;
-            const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
-            float t, u, v;
-            if (triIntersect(o, d, f3(a), f3(b), f3(c), t, u, v)) {
-                const uint id = __float_as_uint(a.w);
-                if (t < tbest || (!ANY && t == tbest && found && id < hitId)) {
-                    if (ANY) return true;
-                    tbest = t; hitId = id; found = true;
-                    tcull = tbest * 1.000001f;
-                }
-            }
-        }
-        if (ngroup.y <= 0x00FFFFFFu) {
-            if (sp == 0) break;
-            ngroup = stack[--sp];
-        }
+        } else hits[i] = make_float4(__uint_as_float(L.hitType), __uint_as_float(L.hitId), __uint_as_float(L.hitInst), L.tbest);
     }
-    return found;
+};
+struct DebugIO {                // reference-format rays in, reference-format hits out (pt_debug_trace)
+    const pt_ray* rays; pt_hit* out;
+    __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const {
+        o4 = *reinterpret_cast<const float4*>(&rays[i].origin); d4 = *reinterpret_cast<const float4*>(&rays[i].direction);
+    }
+    template <bool ANY> __device__ __forceinline__ void store(uint i, const LaneState& L) const {
+        pt_hit p; p.primitive_type = L.hitType; p.primitive_id = L.hitId; p.instance_id = L.hitInst; p.t = L.tbest;
+        if (L.hitId == PT_NONE) { p.primitive_type = 0; p.instance_id = 0; }
+        else if (ANY) { p.primitive_type = 0; p.instance_id = 0; p.primitive_id = 0; }
+        else if (L.hitType != 0) p.instance_id = 0;
+        out[i] = p;
+    }
+};
+
+__device__ __forceinline__ void setModelSpaceDir(LaneState& L) {
+    const float ooeps = 8.271806125530277e-25f;   // 2^-80
+    L.idir.x = 1.0f / (fabsf(L.d.x) > ooeps ? L.d.x : copysignf(ooeps, L.d.x));
+    L.idir.y = 1.0f / (fabsf(L.d.y) > ooeps ? L.d.y : copysignf(ooeps, L.d.y));
+    L.idir.z = 1.0f / (fabsf(L.d.z) > ooeps ? L.d.z : copysignf(ooeps, L.d.z));
+    L.octinv = (L.d.x < 0.0f ? 0u : 4u) | (L.d.y < 0.0f ? 0u : 2u) | (L.d.z < 0.0f ? 0u : 1u);
 }
 
-// Top level, restating kernels.h:277-387 operation for operation (same visit order and culling as the
-// reference: for unit-scale instances the result is order independent, for scaled instances the
-// reference's mixed-space t comparison makes it order DEPENDENT, so the order is kept).
+// Start of a ray: spheres, planes, TLAS root (kernels.h:281-318).  Returns false when the ray is already finished.
 template <bool ANY>
-__device__ __forceinline__ Hit traceTop(const DScene& sc, float3 o, float3 d, float length) {
-    Hit hit; hit.type = 0; hit.inst = 0; hit.id = 0xffffffffu; hit.t = length;
-    float t, tnear, tfar;
+__device__ __forceinline__ bool beginRay(const DScene& sc, LaneState& L, const float4 o4, const float4 d4) {
+    L.o = f3(o4); L.d = f3(d4);
+    L.tbest = o4.w; L.hitId = PT_NONE; L.hitType = 0; L.hitInst = 0;
+    L.sp = 0; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.inBLAS = false; L.found = false;
+    float t;
     for (uint i = 0; i < sc.num_spheres; i++)
-        if (raySphereIntersect(o, d, sc.spheres[i], t) && t < hit.t) {
-            if (ANY) { hit.id = i; return hit; }
-            hit.id = i; hit.type = 1; hit.t = t;
+        if (raySphereIntersect(L.o, L.d, sc.spheres[i], t) && t < L.tbest) {
+            L.hitId = i; if (ANY) return false;
+            L.hitType = 1; L.tbest = t;
         }
     for (uint i = 0; i < sc.num_planes; i++)
-        if (rayPlaneIntersect(o, d, sc.planes[i], t) && t < hit.t) {
-            if (ANY) { hit.id = i; return hit; }
-            hit.id = i; hit.type = 2; hit.t = t;
+        if (rayPlaneIntersect(L.o, L.d, sc.planes[i], t) && t < L.tbest) {
+            L.hitId = i; if (ANY) return false;
+            L.hitType = 2; L.tbest = t;
         }
-    if (sc.num_instances == 0) return hit;
-    const float3 inv = rcp3(d);
-    uint stack[PT_STACK];
-    int sp = 0;
-    bool needPop = false;
-    pt_tlas_node cur = sc.tlas[0];
-    if (!(slabTestRef(o, inv, &cur.vmin.x, &cur.vmax.x, tnear) && tnear < hit.t)) return hit;
+    if (sc.num_instances == 0) return false;
+    L.idir = rcp3(L.d);
+    const pt_tlas_node root = sc.tlas[0];
+    float tnear;
+    if (!(slabTestRef(L.o, L.idir, &root.vmin.x, &root.vmax.x, tnear) && tnear < L.tbest)) return false;
+    L.curT = 0;
+    return true;
+}
+
+// One top-level step for the TLAS node L.curT (kernels.h:320-386): a leaf enters its instance
+// (transformRay, kernels.h:81-86), an inner node tests both children in the reference's order.
+__device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, uint2* stack) {
+    const pt_tlas_node cur = sc.tlas[L.curT];
+    L.curT = PT_NONE;
+    if (cur.children == 0) {
+        const pt_instance& inst = sc.instances[cur.leaf];
+        const float3 nd = normalize(matmul(inst.invTransform, L.d, 0.0f));
+        const float3 no = matmul(inst.invTransform, L.o, 1.0f);
+        L.o = no; L.d = nd;
+        setModelSpaceDir(L);
+        L.tcull = L.tbest * 1.000001f;      // slack: box distances are not computed like triangle distances
+        L.curInst = cur.leaf; L.inBLAS = true; L.found = false;
+        L.ngroup = make_uint2(sc.models[inst.model_id].rootNode, 0x80000000u);
+    } else {
+        const uint near_id = cur.children & 0xffffu, far_id = (cur.children >> 16) & 0xffffu;
+        const pt_tlas_node nn = sc.tlas[near_id];
+        const pt_tlas_node ff = sc.tlas[far_id];
+        float tnear, tfar;
+        const bool bnear = slabTestRef(L.o, L.idir, &nn.vmin.x, &nn.vmax.x, tnear) && tnear < L.tbest;
+        const bool bfar = slabTestRef(L.o, L.idir, &ff.vmin.x, &ff.vmax.x, tfar) && tfar < L.tbest;
+        if (bnear && bfar) {
+            const bool rev = tnear > tfar;
+            stack[L.sp++] = make_uint2(rev ? near_id : far_id, 0u);
+            L.curT = rev ? far_id : near_id;
+        } else if (bnear) L.curT = near_id;
+        else if (bfar) L.curT = far_id;
+    }
+}
+
+// One bottom-level step: take the nearest pending child of the node group, intersect its 8 quantised
+// child boxes (Ylitie et al. 2017), producing a new node group and a triangle group.
+__device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, uint2* stack) {
+    uint2 ngroup = L.ngroup;
+    const uint bit = 31u - __clz(ngroup.y);
+    ngroup.y &= ~(1u << bit);
+    if (ngroup.y > 0x00FFFFFFu) { stack[L.sp++] = ngroup; }
+    const uint slot = (bit - 24u) ^ L.octinv;
+    const uint rel = __popc(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
+    const float4* np = sc.nodes + (size_t)(ngroup.x + rel) * 5;
+    const float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
+    const uint ew = __float_as_uint(n0.w);
+    const float sx = __uint_as_float((ew & 0xffu) << 23), sy = __uint_as_float(((ew >> 8) & 0xffu) << 23), sz = __uint_as_float(((ew >> 16) & 0xffu) << 23);
+    const float aix = sx * L.idir.x, aiy = sy * L.idir.y, aiz = sz * L.idir.z;
+    const float aox = (n0.x - L.o.x) * L.idir.x, aoy = (n0.y - L.o.y) * L.idir.y, aoz = (n0.z - L.o.z) * L.idir.z;
+    const uint octinv4 = L.octinv * 0x01010101u;
+    const bool negx = L.d.x < 0.0f, negy = L.d.y < 0.0f, negz = L.d.z < 0.0f;
+    uint hitmask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const uint meta4 = __float_as_uint(half ? n1.w : n1.z);
+        const uint is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint inner_mask4 = signExtendS8x4(is_inner4 << 3);
+        const uint bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const uint child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint qlx = __float_as_uint(half ? n2.y : n2.x), qly = __float_as_uint(half ? n2.w : n2.z), qlz = __float_as_uint(half ? n3.y : n3.x);
+        const uint qhx = __float_as_uint(half ? n3.w : n3.z), qhy = __float_as_uint(half ? n4.y : n4.x), qhz = __float_as_uint(half ? n4.w : n4.z);
+        const uint nx = negx ? qhx : qlx, fx = negx ? qlx : qhx;
+        const uint ny = negy ? qhy : qly, fy = negy ? qly : qhy;
+        const uint nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float tnx = __fmaf_rn((float)extractByte(nx, j), aix, aox), tny = __fmaf_rn((float)extractByte(ny, j), aiy, aoy), tnz = __fmaf_rn((float)extractByte(nz, j), aiz, aoz);
+            const float tfx = __fmaf_rn((float)extractByte(fx, j), aix, aox), tfy = __fmaf_rn((float)extractByte(fy, j), aiy, aoy), tfz = __fmaf_rn((float)extractByte(fz, j), aiz, aoz);
+            const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+            const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, L.tcull));
+            if (cmin <= cmax) hitmask |= extractByte(child_bits4, j) << extractByte(bit_index4, j);
+        }
+    }
+    L.ngroup = make_uint2(__float_as_uint(n1.x), (hitmask & 0xFF000000u) | (ew >> 24));
+    L.tgroup = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
+}
+
+// Warp-cooperative flat traversal with dynamic ray fetch.  All 32 lanes must call it.  Lanes whose ray
+// terminates go idle; once enough are idle the warp claims that many new queue entries with ONE atomic
+// and the idle lanes start them, so SIMT lanes stay filled on incoherent rays.  When the queue is
+// shorter than the machine is wide, only ceil(n / warps) lanes per warp are used so the rays spread
+// over all SMs instead of serialising inside a few warps.
+// Closest hit keeps the smallest t (strict <, like kernels.h:228); among exactly equal t INSIDE one
+// instance the lowest reference triangle id wins, which makes the result independent of visit order.
+template <bool ANY, class IO>
+__device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* cursor, const IO io) {
+    const uint lane = laneId();
+    const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    const uint width = min(32u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    const uint refillAt = max(1u, width / PT_REFILL_DIV);
+    uint2 stack[PT_STACK];
+    LaneState L;
+    L.ray = PT_NONE;
+    bool exhausted = n == 0;
     while (true) {
-        if (cur.children == 0) {
-            const pt_instance& inst = sc.instances[cur.leaf];
-            const float3 nd = normalize(matmul(inst.invTransform, d, 0.0f));      // transformRay, kernels.h:81-86
-            const float3 no = matmul(inst.invTransform, o, 1.0f);
-            uint id = 0xffffffffu;
-            if (traceBLAS<ANY>(sc, sc.models[inst.model_id].rootNode, no, nd, hit.t, id)) {
-                if (ANY) { hit.id = 0; return hit; }
-                hit.id = id; hit.type = 0; hit.inst = cur.leaf;
+        const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
+        const uint nActive = __popc(activeMask);
+        if (!exhausted && nActive < width && (nActive == 0 || width - nActive >= refillAt)) {
+            const uint want = width - nActive;
+            uint base = 0;
+            if (lane == 0) base = atomicAdd(cursor, want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + want >= n) exhausted = true;
+            const uint r = __popc(~activeMask & ((1u << lane) - 1u));          // rank among the idle lanes
+            if (L.ray == PT_NONE && r < want && base + r < n) {
+                L.ray = base + r;
+                float4 o4, d4; io.load(L.ray, o4, d4);
+                if (!beginRay<ANY>(sc, L, o4, d4)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
             }
-            needPop = true;
-        } else {
-            const uint near_id = cur.children & 0xffffu, far_id = (cur.children >> 16) & 0xffffu;
-            const pt_tlas_node nn = sc.tlas[near_id];
-            const pt_tlas_node ff = sc.tlas[far_id];
-            const bool bnear = slabTestRef(o, inv, &nn.vmin.x, &nn.vmax.x, tnear) && tnear < hit.t;
-            const bool bfar = slabTestRef(o, inv, &ff.vmin.x, &ff.vmax.x, tfar) && tfar < hit.t;
-            if (bnear && bfar) {
-                const bool rev = tnear > tfar;
-                if (sp < PT_STACK) stack[sp++] = rev ? near_id : far_id;
-                cur = rev ? ff : nn;
-            } else if (bnear) cur = nn;
-            else if (bfar) cur = ff;
-            else needPop = true;
-        }
-        if (needPop) {
-            if (sp == 0) return hit;
-            cur = sc.tlas[stack[--sp]];
-            needPop = false;
+        } else if (nActive == 0) break;
+        if (L.ray != PT_NONE) {
+            if (L.tgroup.y == 0u) {                                          // node work
+                if (L.ngroup.y > 0x00FFFFFFu) blasNodeStep(sc, L, stack);
+                else if (L.curT != PT_NONE) tlasStep(sc, L, stack);
+            }
+            bool done = false;
+#pragma unroll 1
+            for (int k = 0; k < PT_TRIS_PER_ITER && L.tgroup.y != 0u; k++) {  // triangle work
+                const uint ti = 31u - __clz(L.tgroup.y);
+                L.tgroup.y &= ~(1u << ti);
+                const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
+                const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                float t, u, v;
+                if (triIntersect(L.o, L.d, f3(a), f3(b), f3(c), t, u, v)) {
+                    const uint id = __float_as_uint(a.w);
+                    if (t < L.tbest || (!ANY && t == L.tbest && L.found && id < L.hitId)) {
+                        L.tbest = t; L.hitId = id; L.hitInst = L.curInst; L.hitType = 0; L.found = true;
+                        L.tcull = t * 1.000001f;
+                        if (ANY) { done = true; break; }
+                    }
+                }
+            }
+            if (!done && L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.curT == PT_NONE) {   // pop
+                if (L.sp == 0) done = true;
+                else {
+                    const uint2 e = stack[--L.sp];
+                    if (e.y == 0u) {                                         // back in the top level: world-space ray again
+                        L.curT = e.x;
+                        if (L.inBLAS) {
+                            float4 o4, d4; io.load(L.ray, o4, d4);
+                            L.o = f3(o4); L.d = f3(d4); L.idir = rcp3(L.d); L.inBLAS = false;
+                        }
+                    } else L.ngroup = e;
+                }
+            }
+            if (done) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
     }
 }
