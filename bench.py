@@ -223,7 +223,7 @@ def gpu_arm(args):
         ext_ms, ext_n = prof["extend"]
         achieved = (pst.extend_rays * bytes_per_ext_ray) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
         tot_prof_ms = sum(v[0] for v in prof.values())
-        launches_per_step = 1 + DEPTH * 3 + 2 + 1
+        launches_per_step = sum(v[1] for v in prof.values()) / args.steps + (2 if pst.samples and False else 0)   # stage launches counted by the library (pt_get_profile)
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",

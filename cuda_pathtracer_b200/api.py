@@ -172,15 +172,15 @@ class Pathtracer:
     def reset_stats(self):
         self._ck(self.L.pt_reset_stats(self.h), "pt_reset_stats")
 
-    STAGES = ("extend", "shade", "connect", "guiding", "other")
+    STAGES = ("extend", "shade", "connect", "guiding", "other", "tail")
 
     def set_profiling(self, on):
         self._ck(self.L.pt_set_profiling(self.h, int(on)), "pt_set_profiling")
 
     def profile(self):
         """{stage: (device ms summed over launches, launches)} since set_profiling(True); call after Finish()."""
-        ms = (C.c_double * 5)()
-        n = (C.c_uint64 * 5)()
+        ms = (C.c_double * len(self.STAGES))()
+        n = (C.c_uint64 * len(self.STAGES))()
         self._ck(self.L.pt_get_profile(self.h, ms, n), "pt_get_profile")
         return {k: (ms[i], int(n[i])) for i, k in enumerate(self.STAGES)}
 

@@ -40,14 +40,15 @@ struct pt_ctx {
     uint32_t sampleIdx = 0, randIdx = 0;
     pt_allreduce_hook hook = nullptr;
     void* hookUser = nullptr;
-    int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0;
+    int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0, gridTail = 0;
+    uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch); PT_MAX_BOUNCES: never
     // per-stage timing (pt_set_profiling): CUDA event pairs around every stage launch, resolved in pt_finish
     bool prof = false;
     std::vector<cudaEvent_t> evPool;
     struct Pending { int stage; cudaEvent_t a, b; };
     std::vector<Pending> pending;
-    double profMs[PT_NUM_STAGES] = {0, 0, 0, 0, 0};
-    unsigned long long profLaunches[PT_NUM_STAGES] = {0, 0, 0, 0, 0};
+    double profMs[PT_NUM_STAGES] = {0, 0, 0, 0, 0, 0};
+    unsigned long long profLaunches[PT_NUM_STAGES] = {0, 0, 0, 0, 0, 0};
     // debug buffers
     pt_ray* dbgRays = nullptr; pt_hit* dbgHits = nullptr; uint32_t dbgCap = 0; uint* dbgCursor = nullptr;
 };
@@ -210,6 +211,11 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->gridTraceAny = ctx->numSMs * std::max(occ, 1);
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, 128, 0));
         ctx->gridShade = ctx->numSMs * std::max(occ, 1);
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_tail, 128, 0));
+        ctx->gridTail = ctx->numSMs * std::max(occ, 1);
+        if (cfg->flags & PT_FLAG_WAVEFRONT_ONLY) ctx->tailBounce = PT_MAX_BOUNCES;
+        else if ((cfg->flags >> 8) & 0xffu) ctx->tailBounce = std::max(1u, ((cfg->flags >> 8) & 0xffu) - 1u);
+        if (const char* e = getenv("PTB200_TAIL_BOUNCE")) ctx->tailBounce = std::max(1, atoi(e));      // developer knob (tools/tune.sh)
         CK(cudaStreamSynchronize(ctx->stream));
         return PT_OK;
     };
@@ -403,24 +409,34 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
         if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
         else max_bounces = should_clear ? ctx->cfg.interactive_depth + 1 : ctx->cfg.max_ray_depth;
-        for (uint32_t bounce = 0; bounce < max_bounces; bounce++) {                        // :276-290
-            const int buf = bounce & 1;
-            { StageTimer tm(ctx, PT_STAGE_EXTEND);
-              k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->q.rayO[buf], ctx->q.rayD[buf], ctx->q.cnt + CNT_EXT(bounce),
-                                                               ctx->q.cnt + CUR_EXT(bounce), ctx->q.hits, nullptr, nullptr); }
+        auto shadeParams = [&](uint32_t bounce) {
             ShadeParams P;
             P.sc = ctx->sc; P.map = map; P.tex = ctx->tex;
             P.masks = ctx->masks; P.accucolors = ctx->accucolors; P.lights = ctx->lights;
             P.sampleCache = ctx->sampleCache; P.albedo = ctx->albedo;
             P.sampleIdx = ctx->sampleIdx; P.randIdx = ctx->randIdx; P.blueFrames = ctx->cfg.blue_noise_frames;
             P.bounce = (int)bounce; P.nee = deviceNEE; P.cache = ctx->DCACHE;
-            { StageTimer tm(ctx, PT_STAGE_SHADE); k_shade<<<ctx->gridShade, 128, 0, s>>>(P, ctx->q, buf); }
+            return P;
+        };
+        const uint32_t waveBounces = std::min(max_bounces, ctx->tailBounce);
+        for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
+            const int buf = bounce & 1;
+            { StageTimer tm(ctx, PT_STAGE_EXTEND);
+              k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->q.rayO[buf], ctx->q.rayD[buf], ctx->q.cnt + CNT_EXT(bounce),
+                                                               ctx->q.cnt + CUR_EXT(bounce), ctx->q.hits, nullptr, nullptr); }
+            { StageTimer tm(ctx, PT_STAGE_SHADE); k_shade<<<ctx->gridShade, 128, 0, s>>>(shadeParams(bounce), ctx->q, buf); }
             ctx->randIdx++;                                                                // :283
             if (ctx->HNEE && deviceNEE) {                                                  // :286 (no shadow rays exist when the device _NEE is false)
                 StageTimer tm(ctx, PT_STAGE_CONNECT);
                 k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, ctx->q.shO, ctx->q.shD, ctx->q.cnt + CNT_SHADOW(bounce),
                                                                 ctx->q.cnt + CUR_CONN(bounce), nullptr, ctx->lights, ctx->accucolors);
             }
+        }
+        if (max_bounces > waveBounces) {                                                   // the same bounces, one launch (k_tail)
+            StageTimer tm(ctx, PT_STAGE_TAIL);
+            k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), ctx->q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
+                                                 ctx->q.cnt + CUR_EXT(waveBounces));
+            ctx->randIdx += max_bounces - waveBounces;                                     // :283, once per bounce
         }
         if (!should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots) {   // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING);

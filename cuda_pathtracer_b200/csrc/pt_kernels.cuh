@@ -141,6 +141,103 @@ __global__ void __launch_bounds__(128) k_shade(ShadeParams P, Queues q, int inBu
     }
 }
 
+// ---- tail bounces: one launch, one lane per PATH ----------------------------------------------------------------
+// From bounce b0 on the queues hold a few thousand rays: every wavefront launch then costs the latency of its
+// slowest ray (profiles/r1g: 30-130 us per launch for <1% of the rays, 3 launches per bounce).  k_tail takes
+// every path that is alive at bounce b0 to its end inside one launch: extend -> shade -> connect -> extend ...
+// per lane, so the launch costs the slowest PATH, not the sum over bounces of the slowest ray.  Per path the
+// order of operations (and of the float additions into accucolor) is the wavefront's, hence the reference's
+// (pathtracer.h:276-290); randIdx advances per bounce exactly as the host loop does.
+// Scratch: the path with queue index i keeps its current extension ray in ray buffer `cur`[i], writes the next
+// one to the other buffer [i] and its shadow ray to shO/shD[i] (all dead wavefront storage by now).
+__global__ void __launch_bounds__(128) k_tail(ShadeParams P, Queues q, int inBuf, int b0, int maxBounces, uint* cursor) {
+    const DScene& sc = P.sc;
+    const uint n = q.cnt[CNT_EXT(b0)];
+    const uint lane = laneId();
+    const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    const uint width = min(32u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    uint2 stack[PT_STACK];
+    LaneState L;
+    L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
+    int bounce = b0, buf = inBuf;
+    bool any = false, extPending = false, rayDone = false;
+    bool exhausted = n == 0;
+    const uint randIdx0 = P.randIdx;
+    auto loadCur = [&](float4& o4, float4& d4) {
+        if (any) { o4 = q.shO[L.ray]; d4 = q.shD[L.ray]; } else { o4 = q.rayO[buf][L.ray]; d4 = q.rayD[buf][L.ray]; }
+    };
+    while (true) {
+        // ---- F: idle lanes claim new paths ----
+        const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
+        const uint nActive = __popc(activeMask);
+        if (!exhausted && nActive < width) {
+            const uint want = width - nActive;
+            uint base = 0;
+            if (lane == 0) base = atomicAdd(cursor, want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + want >= n) exhausted = true;
+            const uint r = __popc(~activeMask & ((1u << lane) - 1u));
+            if (L.ray == PT_NONE && r < want && base + r < n) {
+                L.ray = base + r; bounce = b0; buf = inBuf; any = false; extPending = false;
+                float4 o4, d4; loadCur(o4, d4);
+                rayDone = !beginRay(sc, L, o4, d4, false);
+            }
+        } else if (nActive == 0) break;
+        // ---- C: a finished ray continues its path: shade, then the shadow ray, then the next extension ray ----
+        while (L.ray != PT_NONE && rayDone) {
+            rayDone = false;
+            bool startExt = false;
+            if (any) {
+                if (L.hitId == PT_NONE) {                                       // unoccluded: kernels.h:806-809
+                    const uint slot = __float_as_uint(q.shD[L.ray].w);
+                    const float4 l = P.lights[slot];
+                    float4 a = P.accucolors[slot];
+                    a.x += l.x; a.y += l.y; a.z += l.z;
+                    P.accucolors[slot] = a;
+                }
+                any = false;
+                startExt = extPending;
+            } else {
+                float4 o4, d4; loadCur(o4, d4);
+                const uint slot = __float_as_uint(d4.w);
+                Hit h; h.type = L.hitType; h.id = L.hitId; h.inst = L.hitInst; h.t = L.tbest;
+                ShadeParams Pb = P; Pb.bounce = bounce; Pb.randIdx = randIdx0 + (uint)(bounce - b0);
+                ShadeOut so;
+                shadeOne(Pb, f3(o4), f3(d4), slot, h, so);
+                extPending = so.pushExt && bounce + 1 < maxBounces;
+                if (so.pushExt) atomicAdd(q.cnt + CNT_EXT(bounce + 1), 1u);
+                if (extPending) {
+                    q.rayO[buf ^ 1][L.ray] = make_float4(so.ext.o.x, so.ext.o.y, so.ext.o.z, so.ext.len);
+                    q.rayD[buf ^ 1][L.ray] = make_float4(so.ext.d.x, so.ext.d.y, so.ext.d.z, __uint_as_float(slot));
+                }
+                if (so.pushShadow) {
+                    atomicAdd(q.cnt + CNT_SHADOW(bounce), 1u);
+                    const float4 so4 = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
+                    const float4 sd4 = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
+                    q.shO[L.ray] = so4; q.shD[L.ray] = sd4;
+                    any = true;
+                    rayDone = !beginRay(sc, L, so4, sd4, true);
+                } else startExt = extPending;
+            }
+            if (startExt) {
+                extPending = false; bounce++; buf ^= 1;
+                float4 o4, d4; loadCur(o4, d4);
+                rayDone = !beginRay(sc, L, o4, d4, false);
+            } else if (!any) L.ray = PT_NONE;                                    // path ended
+        }
+        // ---- T: top level ----
+        if (L.ray != PT_NONE && !hasBlasWork(L)) rayDone = tlasTrip(sc, L, stack, loadCur);
+        // ---- B: bottom level ----
+        const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
+        const uint minKeep = max(1u, (nB * PT_KEEP_NUM + PT_KEEP_DEN - 1u) / PT_KEEP_DEN);
+        while (true) {
+            const bool work = hasBlasWork(L);
+            if (__popc(__ballot_sync(0xffffffffu, work)) < minKeep) break;
+            if (work && blasTrip(sc, L, stack, any)) rayDone = true;
+        }
+    }
+}
+
 // ---- accumulate + statistics -------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* __restrict__ accucolors, float4* image,
                                                     const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces) {

@@ -14,6 +14,14 @@ __device__ __forceinline__ uint signExtendS8x4(uint x) {
     uint r; asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x)); return r;   // byte msb -> 0xFF / 0x00
 }
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+// byte j of x as a float.  Default: I2FP.F32.U32 with a byte selector (one instruction, XU pipe).  The
+// PRMT + FADD form (bits of 2^23 + b, minus 2^23; exact for 0..255) avoids the XU pipe at the price of
+// one more instruction per value; measured slower on B200 (tune run r1e), kept as a build knob.
+#if defined(PT_BYTE_PRMT)
+__device__ __forceinline__ float byteToFloat(uint x, uint j) { return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7540u + j)) - 8388608.0f; }
+#else
+__device__ __forceinline__ float byteToFloat(uint x, uint j) { return (float)((x >> (j * 8u)) & 0xffu); }
+#endif
 
 // kernels.h:120-135
 __device__ __forceinline__ bool raySphereIntersect(float3 o, float3 d, const pt_sphere& s, float& t) {
@@ -70,20 +78,24 @@ __device__ __forceinline__ bool triIntersect(float3 o, float3 d, float3 v0, floa
 }
 
 
-#define PT_STACK 40            /* unified stack: TLAS entries + BLAS node groups + postponed triangle groups */
+#define PT_STACK 40            /* unified stack: TLAS entries below the node groups of the instance being traversed */
 #define PT_NONE 0xffffffffu
 #ifndef PT_TRIS_PER_ITER
 #define PT_TRIS_PER_ITER 2     /* triangle tests a lane performs per loop trip before node work resumes */
 #endif
 #ifndef PT_REFILL_DIV
-#define PT_REFILL_DIV 4        /* fetch new rays once width/PT_REFILL_DIV lanes of the warp are idle */
+#define PT_REFILL_DIV 1        /* fetch new rays once width/PT_REFILL_DIV lanes of the warp are idle (1: when all are) */
+#endif
+#ifndef PT_KEEP_NUM
+#define PT_KEEP_NUM 1          /* the bottom-level loop runs while >= PT_KEEP_NUM/PT_KEEP_DEN of the lanes that */
+#define PT_KEEP_DEN 2          /* entered it still have bottom-level work; the others wait for the next top-level phase */
 #endif
 
-// Per-lane traversal state of the flat (single-loop) two-level traversal.  A lane is in exactly one
-// of: TLAS step pending (curT), BLAS node group pending (ngroup), triangles pending (tgroup), or
-// needs a pop.  Logical per-ray order == the reference's nested loops (kernels.h:277-387 outside,
-// one bottom-level traversal per TLAS leaf inside): TLAS entries sit below the BLAS entries of the
-// instance being traversed, so an instance is finished before the top level resumes.
+// Per-lane traversal state.  A lane is idle (ray == PT_NONE), in the top level (curT / TLAS entries
+// on the stack), or inside an instance (ngroup / tgroup / node groups above spBase on the stack).
+// Logical per-ray order == the reference's nested loops (kernels.h:277-387 outside, one bottom-level
+// traversal per TLAS leaf inside): TLAS entries sit below the BLAS entries of the instance being
+// traversed, so an instance is finished before the top level resumes.
 struct LaneState {
     float3 o, d, idir;          // ray in the CURRENT space (world in the top level, model inside an instance)
     float tbest, tcull;
@@ -93,7 +105,7 @@ struct LaneState {
     uint curInst;               // instance being traversed
     uint octinv;
     uint2 ngroup, tgroup;
-    int sp;
+    int sp, spBase;
     bool inBLAS, found;
 };
 
@@ -136,8 +148,7 @@ __device__ __forceinline__ void setModelSpaceDir(LaneState& L) {
 }
 
 // Start of a ray: spheres, planes, TLAS root (kernels.h:281-318).  Returns false when the ray is already finished.
-template <bool ANY>
-__device__ __forceinline__ bool beginRay(const DScene& sc, LaneState& L, const float4 o4, const float4 d4) {
+__device__ __forceinline__ bool beginRay(const DScene& sc, LaneState& L, const float4 o4, const float4 d4, const bool ANY) {
     L.o = f3(o4); L.d = f3(d4);
     L.tbest = o4.w; L.hitId = PT_NONE; L.hitType = 0; L.hitInst = 0;
     L.sp = 0; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.inBLAS = false; L.found = false;
@@ -173,7 +184,7 @@ __device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, uint2* 
         L.o = no; L.d = nd;
         setModelSpaceDir(L);
         L.tcull = L.tbest * 1.000001f;      // slack: box distances are not computed like triangle distances
-        L.curInst = cur.leaf; L.inBLAS = true; L.found = false;
+        L.curInst = cur.leaf; L.inBLAS = true; L.found = false; L.spBase = L.sp;
         L.ngroup = make_uint2(sc.models[inst.model_id].rootNode, 0x80000000u);
     } else {
         const uint near_id = cur.children & 0xffffu, far_id = (cur.children >> 16) & 0xffffu;
@@ -223,8 +234,8 @@ __device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, uin
         const uint nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const float tnx = __fmaf_rn((float)extractByte(nx, j), aix, aox), tny = __fmaf_rn((float)extractByte(ny, j), aiy, aoy), tnz = __fmaf_rn((float)extractByte(nz, j), aiz, aoz);
-            const float tfx = __fmaf_rn((float)extractByte(fx, j), aix, aox), tfy = __fmaf_rn((float)extractByte(fy, j), aiy, aoy), tfz = __fmaf_rn((float)extractByte(fz, j), aiz, aoz);
+            const float tnx = __fmaf_rn(byteToFloat(nx, j), aix, aox), tny = __fmaf_rn(byteToFloat(ny, j), aiy, aoy), tnz = __fmaf_rn(byteToFloat(nz, j), aiz, aoz);
+            const float tfx = __fmaf_rn(byteToFloat(fx, j), aix, aox), tfy = __fmaf_rn(byteToFloat(fy, j), aiy, aoy), tfz = __fmaf_rn(byteToFloat(fz, j), aiz, aoz);
             const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, L.tcull));
             if (cmin <= cmax) hitmask |= extractByte(child_bits4, j) << extractByte(bit_index4, j);
@@ -234,13 +245,66 @@ __device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, uin
     L.tgroup = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
 }
 
-// Warp-cooperative flat traversal with dynamic ray fetch.  All 32 lanes must call it.  Lanes whose ray
-// terminates go idle; once enough are idle the warp claims that many new queue entries with ONE atomic
-// and the idle lanes start them, so SIMT lanes stay filled on incoherent rays.  When the queue is
-// shorter than the machine is wide, only ceil(n / warps) lanes per warp are used so the rays spread
-// over all SMs instead of serialising inside a few warps.
+// Up to PT_TRIS_PER_ITER Moeller-Trumbore tests from the lane's pending triangle group.  Returns true when an
+// any-hit ray found its occluder.
+__device__ __forceinline__ bool triStep(const DScene& sc, LaneState& L, const bool ANY) {
+#pragma unroll 1
+    for (int k = 0; k < PT_TRIS_PER_ITER && L.tgroup.y != 0u; k++) {
+        const uint ti = 31u - __clz(L.tgroup.y);
+        L.tgroup.y &= ~(1u << ti);
+        const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
+        const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+        float t, u, v;
+        if (triIntersect(L.o, L.d, f3(a), f3(b), f3(c), t, u, v)) {
+            const uint id = __float_as_uint(a.w);
+            if (t < L.tbest || (!ANY && t == L.tbest && L.found && id < L.hitId)) {
+                L.tbest = t; L.hitId = id; L.hitInst = L.curInst; L.hitType = 0; L.found = true;
+                L.tcull = t * 1.000001f;
+                if (ANY) return true;
+            }
+        }
+    }
+    return false;
+}
+// Bottom-level work of one lane for one loop trip: a node step or triangle tests, then a pop if both ran dry.
+// Returns true when an any-hit ray is finished (occluded).
+__device__ __forceinline__ bool blasTrip(const DScene& sc, LaneState& L, uint2* stack, const bool ANY) {
+    if (L.tgroup.y == 0u) blasNodeStep(sc, L, stack);
+    if (triStep(sc, L, ANY)) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
+    if (L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack[--L.sp];
+    return false;
+}
+// Top-level work of a lane that is not inside an instance: TLAS steps until it enters one (returns false) or
+// the ray is finished (returns true).  reload() re-reads the world-space ray after an instance was left.
+template <class Reload>
+__device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, uint2* stack, const Reload& reload) {
+    if (L.inBLAS && L.sp > 0) {
+        float4 o4, d4; reload(o4, d4);
+        L.o = f3(o4); L.d = f3(d4); L.idir = rcp3(L.d);
+    }
+    L.inBLAS = false;
+    while (true) {
+        if (L.curT == PT_NONE) {
+            if (L.sp == 0) return true;
+            L.curT = stack[--L.sp].x;
+        }
+        tlasStep(sc, L, stack);
+        if (L.inBLAS) return false;
+    }
+}
+
+// Warp-cooperative two-phase traversal with dynamic ray fetch.  All 32 lanes must call it.
+//   F  idle lanes claim new queue entries (ONE atomic per warp) once enough of them are idle;
+//   T  lanes that are in the top level run TLAS steps until they enter an instance or finish;
+//   B  all lanes inside an instance run the bottom-level loop together; a lane that leaves its
+//      instance waits, and the loop is left once fewer than PT_KEEP_NUM/PT_KEEP_DEN of its lanes remain,
+// so every phase executes with most lanes participating (SIMT efficiency) on incoherent rays too.
+// When the queue is shorter than the machine is wide, only ceil(n / warps) lanes per warp are used so
+// the rays spread over all SMs instead of serialising inside a few warps.
 // Closest hit keeps the smallest t (strict <, like kernels.h:228); among exactly equal t INSIDE one
 // instance the lowest reference triangle id wins, which makes the result independent of visit order.
+__device__ __forceinline__ bool hasBlasWork(const LaneState& L) { return L.ray != PT_NONE && (L.tgroup.y | (L.ngroup.y & 0xFF000000u)) != 0u; }
+
 template <bool ANY, class IO>
 __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* cursor, const IO io) {
     const uint lane = laneId();
@@ -249,9 +313,10 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
     const uint refillAt = max(1u, width / PT_REFILL_DIV);
     uint2 stack[PT_STACK];
     LaneState L;
-    L.ray = PT_NONE;
+    L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     bool exhausted = n == 0;
     while (true) {
+        // ---- F: fetch ----
         const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
         const uint nActive = __popc(activeMask);
         if (!exhausted && nActive < width && (nActive == 0 || width - nActive >= refillAt)) {
@@ -264,45 +329,21 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
             if (L.ray == PT_NONE && r < want && base + r < n) {
                 L.ray = base + r;
                 float4 o4, d4; io.load(L.ray, o4, d4);
-                if (!beginRay<ANY>(sc, L, o4, d4)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+                if (!beginRay(sc, L, o4, d4, ANY)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
             }
         } else if (nActive == 0) break;
-        if (L.ray != PT_NONE) {
-            if (L.tgroup.y == 0u) {                                          // node work
-                if (L.ngroup.y > 0x00FFFFFFu) blasNodeStep(sc, L, stack);
-                else if (L.curT != PT_NONE) tlasStep(sc, L, stack);
-            }
-            bool done = false;
-#pragma unroll 1
-            for (int k = 0; k < PT_TRIS_PER_ITER && L.tgroup.y != 0u; k++) {  // triangle work
-                const uint ti = 31u - __clz(L.tgroup.y);
-                L.tgroup.y &= ~(1u << ti);
-                const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
-                const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
-                float t, u, v;
-                if (triIntersect(L.o, L.d, f3(a), f3(b), f3(c), t, u, v)) {
-                    const uint id = __float_as_uint(a.w);
-                    if (t < L.tbest || (!ANY && t == L.tbest && L.found && id < L.hitId)) {
-                        L.tbest = t; L.hitId = id; L.hitInst = L.curInst; L.hitType = 0; L.found = true;
-                        L.tcull = t * 1.000001f;
-                        if (ANY) { done = true; break; }
-                    }
-                }
-            }
-            if (!done && L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.curT == PT_NONE) {   // pop
-                if (L.sp == 0) done = true;
-                else {
-                    const uint2 e = stack[--L.sp];
-                    if (e.y == 0u) {                                         // back in the top level: world-space ray again
-                        L.curT = e.x;
-                        if (L.inBLAS) {
-                            float4 o4, d4; io.load(L.ray, o4, d4);
-                            L.o = f3(o4); L.d = f3(d4); L.idir = rcp3(L.d); L.inBLAS = false;
-                        }
-                    } else L.ngroup = e;
-                }
-            }
-            if (done) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+        // ---- T: top level ----
+        if (L.ray != PT_NONE && !hasBlasWork(L)) {
+            const uint ray = L.ray;
+            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); })) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+        }
+        // ---- B: bottom level ----
+        const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
+        const uint minKeep = max(1u, (nB * PT_KEEP_NUM + PT_KEEP_DEN - 1u) / PT_KEEP_DEN);
+        while (true) {
+            const bool work = hasBlasWork(L);
+            if (__popc(__ballot_sync(0xffffffffu, work)) < minKeep) break;
+            if (work && blasTrip(sc, L, stack, ANY)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
     }
 }

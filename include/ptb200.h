@@ -151,6 +151,11 @@ typedef struct {
     uint32_t flags;                    /* PT_FLAG_* */
 } pt_config;
 #define PT_FLAG_DEFAULT 0u
+/* Scheduling only (results are identical): bounces >= the tail bounce run as ONE per-path launch instead of
+ * three wavefront launches per bounce.  Default tail bounce: 3.  PT_FLAG_TAIL_BOUNCE(n) overrides it,
+ * PT_FLAG_WAVEFRONT_ONLY keeps every bounce in the wavefront. */
+#define PT_FLAG_WAVEFRONT_ONLY 1u
+#define PT_FLAG_TAIL_BOUNCE(n) ((((uint32_t)(n) + 1u) & 0xffu) << 8)
 
 typedef struct {                       /* device-side ray counters since the last pt_reset_stats */
     uint64_t primary_rays, extend_rays, shadow_rays, shade_calls, samples;
@@ -189,7 +194,8 @@ PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
 #define PT_STAGE_CONNECT 2
 #define PT_STAGE_GUIDING 3
 #define PT_STAGE_OTHER 4
-#define PT_NUM_STAGES 5
+#define PT_STAGE_TAIL 5     /* k_tail: extend + shade + connect of every bounce >= the tail bounce */
+#define PT_NUM_STAGES 6
 PT_API int  pt_set_profiling(pt_ctx*, int on);                         /* also resets the accumulators */
 PT_API int  pt_get_profile(pt_ctx*, double* ms /*[PT_NUM_STAGES]*/, uint64_t* launches /*[PT_NUM_STAGES]*/);
 PT_API int  pt_get_stats(pt_ctx*, pt_stats* out);
