@@ -28,7 +28,8 @@ sys.path.insert(0, ROOT)
 W, H, DEPTH = 1920, 1080, 8
 METRIC = "Mrays/s on sibenik 1080p (NEE + path guiding, depth 8)"
 WORKLOAD = "sibenik-proxy (cathedral+statue+emissive cube+2 spheres, 158k tris) 1920x1080, NEE on, guiding on, MAX_RAY_DEPTH 8"
-CPU_W, CPU_H = 480, 270      # bounded CPU sample: same scene/camera/depth at 1/16 of the pixels
+CPU_W, CPU_H = 1920, 1080    # bounded CPU sample: the same workload, a few samples (about 10-20 s on 16 cores)
+CPU_SAMPLES = 16
 
 
 def read_peaks():
@@ -148,7 +149,7 @@ def gpu_arm(args):
     stream = torch.cuda.ExternalStream(pt.stream(), device=torch.device("cuda", local))
     if world > 1:
         from cuda_pathtracer_b200.distributed import make_allreduce_hook
-        pt.set_allreduce_hook(make_allreduce_hook(torch.device("cuda", local), stream))   # NCCL sum over NVLink on the tracer's stream
+        pt.set_allreduce_hook(make_allreduce_hook(torch.device("cuda", local)))   # NCCL sum over NVLink on the stream the sample runs on
     cams = [camera_for(i, W, H) for i in range(16)]
 
     def barrier():
@@ -171,6 +172,7 @@ def gpu_arm(args):
     e0.record(stream)
     for _ in range(args.steps):
         pt.Render(cams[step % 16]); step += 1
+    pt.join()                  # renders run on the library's private streams: order them before the end event
     e1.record(stream)
     pt.Finish()
     barrier()
@@ -185,6 +187,26 @@ def gpu_arm(args):
     ms = float(tms.item())
     total_rays, ext_rays, sh_rays = (float(x) for x in rays.tolist())
     value = total_rays / (ms * 1e-3) / 1e6
+    # ---- the two phases of the reference's frame loop, separately (pathtracer.h:292: the cache trains while sampleIdx < 100) ----
+    def timed_pass(n):
+        nonlocal step
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(n):
+            pt.Render(cams[step % 16]); step += 1
+        pt.join(); b.record(stream); pt.Finish(); barrier()
+        t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / n
+    phase_steps = max(10, min(50, args.steps))
+    pt.set_guiding_frames(1 << 30)
+    training_ms = timed_pass(phase_steps)          # every frame: update buckets, all-reduce over ranks, propagate
+    pt.set_guiding_frames(0)
+    timed_pass(3)
+    steady_ms = timed_pass(phase_steps)            # cache frozen, guiding still steers the samples
+    rays_per_step = total_rays / args.steps
     # ---- per-stage device time of the same steps (separate pass: event pairs around every launch) ----
     pt.set_profiling(True)
     pt.reset_stats()
@@ -216,30 +238,38 @@ def gpu_arm(args):
     e2e_value = float(e2[0].item()) / float(e2[1].item()) / 1e6
     if rank == 0:
         peak, peak_src = read_peaks()
-        cpu_v, per_ray, cpu_s, cpu_rays = cpu_leg(arrays, os.cpu_count() or 1, 1)
+        cpu_v, per_ray, cpu_s, cpu_rays = cpu_leg(arrays, os.cpu_count() or 1, CPU_SAMPLES)
         # ALGORITHMIC bytes of one extend launch: per ray 32 (RayPacked R) + 16 (HitInfoPacked W)
         # + 64 * N_inner + 48 * N_tri, N_* counted by the CPU oracle on the reference's BVH2 for the same scene/camera/depth
         bytes_per_ext_ray = 48.0 + 64.0 * per_ray["ext_inner"] + 48.0 * per_ray["ext_tris"]
         ext_ms, ext_n = prof["extend"]
-        achieved = (pst.extend_rays * bytes_per_ext_ray) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+        # only the rays the k_trace<false> launches traced (bounces below the tail bounce); k_tail's are not in ext_ms
+        achieved = (pst.wave_extend_rays * bytes_per_ext_ray) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")      # dram__bytes_read+write per launch from the committed ncu --set full capture
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("k_trace<false>", {}).get("dram_bytes_per_launch")
         tot_prof_ms = sum(v[0] for v in prof.values())
         launches_per_step = sum(v[1] for v in prof.values()) / args.steps + (2 if pst.samples and False else 0)   # stage launches counted by the library (pt_get_profile)
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
+                "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "samples_in_flight": 4, "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
                            "cameras": "16-camera sweep inside the nave, one camera per step", "global_pixels": W * H},
                 "spp_per_s": args.steps / (ms * 1e-3), "rays_per_step": total_rays / args.steps,
+                "phases": {"note": "timed steps follow the reference frame loop from sample %d: the radiance cache trains (update + all-reduce + propagate) while sampleIdx < 100, then stays frozen" % (1 + max(args.warmup, 3)),
+                           "training_ms_per_step": training_ms, "training_mrays_s": rays_per_step / training_ms / 1e3,
+                           "steady_ms_per_step": steady_ms, "steady_mrays_s": rays_per_step / steady_ms / 1e3},
                 "clocks": sampler.summary(),
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(inst.nbytes + tlas.nbytes + 76),
                         "d2h_bytes_per_step": int(W * H * 16)},
                 "gpu_launches": int(launches_per_step * args.steps),
                 "roofline": {"bound": "hbm", "kernel": "k_trace<false> (extend)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": peak_src, "bytes_per_ray": bytes_per_ext_ray,
+                             "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": pst.wave_extend_rays * bytes_per_ext_ray / max(1, ext_n), "bytes_per_ray": bytes_per_ext_ray,
                              "avg_launch_ms": ext_ms / max(1, ext_n), "share_of_step": ext_ms / tot_prof_ms if tot_prof_ms else None,
                              "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray); HBM copy peak is the denominator"},
                 "stage_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
                 "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
-                                 "sample": "oracle/pt_oracle.cpp: 1 converge sample of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_W, CPU_H, cpu_rays, cpu_s)}}
+                                 "sample": "oracle/pt_oracle.cpp: %d converge samples of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_SAMPLES, CPU_W, CPU_H, cpu_rays, cpu_s)}}
         print(json.dumps(line), flush=True)
     pt.close()
     if world > 1:

@@ -53,6 +53,8 @@ def load_library():
     L.pt_set_allreduce_hook.argtypes = [C.c_void_p, abi.ALLREDUCE_HOOK, C.c_void_p]
     L.pt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_finish.argtypes = [C.c_void_p]
+    L.pt_join.argtypes = [C.c_void_p]
+    L.pt_set_guiding_frames.argtypes = [C.c_void_p, C.c_uint32]
     L.pt_read_image.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_read_radiance_cache.argtypes = [C.c_void_p, C.c_void_p]
     L.pt_get_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
@@ -154,6 +156,15 @@ class Pathtracer:
         out = C.c_uint64()
         self._ck(self.L.pt_texture_create(self.h, abi.ptr(rgba), rgba.shape[1], rgba.shape[0], C.byref(out)), "pt_texture_create")
         return out.value
+
+    def set_guiding_frames(self, frames):
+        """Frames during which the radiance cache trains (reference pathtracer.h:292 hard-codes 100)."""
+        self._ck(self.L.pt_set_guiding_frames(self.h, int(frames)), "pt_set_guiding_frames")
+
+    def join(self):
+        """Asynchronous: orders every Render enqueued so far before later work on stream() (renders run on
+        private streams, two samples in flight)."""
+        self._ck(self.L.pt_join(self.h), "pt_join")
 
     def set_allreduce_hook(self, fn):
         """fn(dev_ptr:int, count:int, stream:int) -> 0 on success; called once per guiding-training frame."""

@@ -14,15 +14,27 @@ using namespace ptb;
 
 static thread_local std::string g_createError;
 
+#define PT_MAX_SETS 4
 struct pt_ctx {
     pt_config cfg;
     std::string err;
     cudaStream_t stream = nullptr;
     int numSMs = 0;
     TileMap map;
-    Queues q;
-    float4 *masks = nullptr, *accucolors = nullptr, *lights = nullptr;
-    pt_sample_cache* sampleCache = nullptr;
+    // Per-sample working state.  PT_MAX_SETS sets: converge samples rotate through them on private streams, so the
+    // short-queue end of sample k (deep bounces, k_tail) overlaps the wide launches of samples k+1.. (measured on
+    // B200, sibenik 1080p: 2.46 -> 2.03 ms/sample; one eighth of the image: 0.86 -> 0.48 ms/sample).
+    struct SampleSet {
+        Queues q;
+        float4 *masks = nullptr, *accucolors = nullptr, *lights = nullptr, *albedoSample = nullptr;
+        pt_sample_cache* sampleCache = nullptr;
+        cudaStream_t stream = nullptr;
+        cudaEvent_t done = nullptr;       // recorded after the sample's accumulate
+        bool doneValid = false;
+    } set[PT_MAX_SETS];
+    int nSets = PT_MAX_SETS, cur = 0;
+    bool forked = false, prevTraining = false;
+    cudaEvent_t forkEv = nullptr;
     float4 *image = nullptr, *albedo = nullptr;
     unsigned long long* stats = nullptr;
     // scene
@@ -70,8 +82,9 @@ static cudaEvent_t getEvent(pt_ctx* ctx) {
 }
 struct StageTimer {      // records an event pair on the context's stream around one stage launch
     pt_ctx* ctx; int stage; cudaEvent_t a = nullptr, b = nullptr;
-    StageTimer(pt_ctx* c, int st) : ctx(c), stage(st) { if (ctx->prof) { a = getEvent(ctx); b = getEvent(ctx); cudaEventRecord(a, ctx->stream); } }
-    ~StageTimer() { if (a) { cudaEventRecord(b, ctx->stream); ctx->pending.push_back({stage, a, b}); } }
+    cudaStream_t s;
+    StageTimer(pt_ctx* c, int st, cudaStream_t stream) : ctx(c), stage(st), s(stream) { if (ctx->prof) { a = getEvent(ctx); b = getEvent(ctx); cudaEventRecord(a, s); } }
+    ~StageTimer() { if (a) { cudaEventRecord(b, s); ctx->pending.push_back({stage, a, b}); } }
 };
 static void resolveProfile(pt_ctx* ctx) {   // call after the stream has been synchronised
     for (auto& p : ctx->pending) {
@@ -98,6 +111,16 @@ static int devUpload(pt_ctx* ctx, T** p, const T* host, size_t n, bool sceneOwne
     return PT_OK;
 }
 
+// Work enqueued by pt_render lives on the private streams of the sample sets.  joinStreams() orders everything
+// enqueued so far before whatever comes next on the context's public stream (pt_cuda_stream()).
+static int joinStreams(pt_ctx* ctx) {
+    if (!ctx->forked) return PT_OK;
+    for (auto& S : ctx->set)
+        if (S.doneValid) { CK(cudaStreamWaitEvent(ctx->stream, S.done, 0)); S.doneValid = false; }
+    ctx->forked = false;
+    return PT_OK;
+}
+
 extern "C" {
 
 PT_API const char* pt_version(void) { return "ptb200 0.1 (sm_100a)"; }
@@ -117,15 +140,23 @@ PT_API const char* pt_last_error(const pt_ctx* ctx) { return ctx ? ctx->err.c_st
 PT_API void pt_destroy(pt_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
+    for (auto& S : ctx->set) if (S.stream) cudaStreamSynchronize(S.stream);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     resolveProfile(ctx);
     for (auto e : ctx->evPool) cudaEventDestroy(e);
     for (auto t : ctx->textures) cudaDestroyTextureObject(t);
     for (auto a : ctx->arrays) cudaFreeArray(a);
     for (void* p : ctx->sceneAllocs) cudaFree(p);
-    void* bufs[] = {ctx->q.rayO[0], ctx->q.rayO[1], ctx->q.rayD[0], ctx->q.rayD[1], ctx->q.shO, ctx->q.shD, ctx->q.hits, ctx->q.cnt,
-                    ctx->masks, ctx->accucolors, ctx->lights, ctx->sampleCache, ctx->image, ctx->albedo, ctx->stats,
-                    ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
+    for (auto& S : ctx->set) {
+        if (S.stream) cudaStreamSynchronize(S.stream);
+        void* sb[] = {S.q.rayO[0], S.q.rayO[1], S.q.rayD[0], S.q.rayD[1], S.q.shO, S.q.shD, S.q.hits, S.q.cnt,
+                      S.masks, S.accucolors, S.lights, S.albedoSample, &S == &ctx->set[0] ? S.sampleCache : nullptr};
+        for (void* p : sb) if (p) cudaFree(p);
+        if (S.done) cudaEventDestroy(S.done);
+        if (S.stream) cudaStreamDestroy(S.stream);
+    }
+    if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
+    void* bufs[] = {ctx->image, ctx->albedo, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
     for (void* p : bufs) if (p) cudaFree(p);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -169,7 +200,8 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
     }
     pt_ctx* ctx = new pt_ctx();
     ctx->cfg = *cfg;
-    memset(&ctx->q, 0, sizeof(ctx->q)); memset(&ctx->sc, 0, sizeof(ctx->sc)); memset(&ctx->tex, 0, sizeof(ctx->tex));
+    for (auto& S : ctx->set) memset(&S.q, 0, sizeof(S.q));
+    memset(&ctx->sc, 0, sizeof(ctx->sc)); memset(&ctx->tex, 0, sizeof(ctx->tex));
     ctx->tex.skyConst = make_float3(1.0f, 1.0f, 1.0f);
     auto bail = [&](int code) { g_createError = ctx->err; pt_destroy(ctx); return code; };
     auto body = [&]() -> int {
@@ -180,27 +212,40 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         m = makeTileMap(cfg);
         const size_t cap = std::max<uint32_t>(m.nSlots, 1024u);
         int r;
-        for (int i = 0; i < 2; i++) {
-            if ((r = devAlloc(ctx, &ctx->q.rayO[i], cap, false))) return r;
-            if ((r = devAlloc(ctx, &ctx->q.rayD[i], cap, false))) return r;
+        if ((cfg->flags & PT_FLAG_NO_PIPELINE) || getenv("PTB200_NO_PIPELINE")) ctx->nSets = 1;
+        else if (const char* e = getenv("PTB200_SETS")) ctx->nSets = std::min(PT_MAX_SETS, std::max(1, atoi(e)));    // developer knob
+        CK(cudaEventCreateWithFlags(&ctx->forkEv, cudaEventDisableTiming));
+        for (int k = 0; k < ctx->nSets; k++) {
+            pt_ctx::SampleSet& S = ctx->set[k];
+            CK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&S.done, cudaEventDisableTiming));
+            for (int i = 0; i < 2; i++) {
+                if ((r = devAlloc(ctx, &S.q.rayO[i], cap, false))) return r;
+                if ((r = devAlloc(ctx, &S.q.rayD[i], cap, false))) return r;
+            }
+            if ((r = devAlloc(ctx, &S.q.shO, cap, false))) return r;
+            if ((r = devAlloc(ctx, &S.q.shD, cap, false))) return r;
+            if ((r = devAlloc(ctx, &S.q.hits, cap, false))) return r;
+            if ((r = devAlloc(ctx, &S.q.cnt, (size_t)CNT_TOTAL, false))) return r;
+            if ((r = devAlloc(ctx, &S.masks, cap, false))) return r;
+            if ((r = devAlloc(ctx, &S.accucolors, cap, false))) return r;
+            if ((r = devAlloc(ctx, &S.lights, cap, false))) return r;
+            if ((r = devAlloc(ctx, &S.albedoSample, cap, false))) return r;
+            // ONE sample cache for both sets: entries a path does not rewrite (emissive hits) must stay those of the
+            // previous frame, as in the reference (kernels.h:563-576, 863-882); training frames never overlap.
+            if (k == 0) { if ((r = devAlloc(ctx, &S.sampleCache, cap * PT_MAX_CACHE_DEPTH, false))) return r; }
+            else S.sampleCache = ctx->set[0].sampleCache;
+            CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), ctx->stream));
+            CK(cudaMemsetAsync(S.lights, 0, cap * sizeof(float4), ctx->stream));
+            CK(cudaMemsetAsync(S.masks, 0, cap * sizeof(float4), ctx->stream));
+            CK(cudaMemsetAsync(S.accucolors, 0, cap * sizeof(float4), ctx->stream));
+            CK(cudaMemsetAsync(S.albedoSample, 0, cap * sizeof(float4), ctx->stream));
+            if (k == 0) CK(cudaMemsetAsync(S.sampleCache, 0, cap * PT_MAX_CACHE_DEPTH * sizeof(pt_sample_cache), ctx->stream));
         }
-        if ((r = devAlloc(ctx, &ctx->q.shO, cap, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->q.shD, cap, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->q.hits, cap, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->q.cnt, (size_t)CNT_TOTAL, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->masks, cap, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->accucolors, cap, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->lights, cap, false))) return r;
-        if ((r = devAlloc(ctx, &ctx->sampleCache, cap * PT_MAX_CACHE_DEPTH, false))) return r;
         if ((r = devAlloc(ctx, &ctx->image, (size_t)m.W * m.H, false))) return r;
         if ((r = devAlloc(ctx, &ctx->albedo, (size_t)m.W * m.H, false))) return r;
         if ((r = devAlloc(ctx, &ctx->stats, (size_t)8, false))) return r;
         if ((r = devAlloc(ctx, &ctx->dbgCursor, (size_t)1, false))) return r;
-        CK(cudaMemsetAsync(ctx->q.cnt, 0, CNT_TOTAL * sizeof(uint), ctx->stream));
-        CK(cudaMemsetAsync(ctx->lights, 0, cap * sizeof(float4), ctx->stream));
-        CK(cudaMemsetAsync(ctx->masks, 0, cap * sizeof(float4), ctx->stream));
-        CK(cudaMemsetAsync(ctx->accucolors, 0, cap * sizeof(float4), ctx->stream));
-        CK(cudaMemsetAsync(ctx->sampleCache, 0, cap * PT_MAX_CACHE_DEPTH * sizeof(pt_sample_cache), ctx->stream));
         CK(cudaMemsetAsync(ctx->image, 0, (size_t)m.W * m.H * sizeof(float4), ctx->stream));
         CK(cudaMemsetAsync(ctx->albedo, 0, (size_t)m.W * m.H * sizeof(float4), ctx->stream));
         CK(cudaMemsetAsync(ctx->stats, 0, 8 * sizeof(unsigned long long), ctx->stream));
@@ -213,6 +258,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->gridShade = ctx->numSMs * std::max(occ, 1);
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_tail, 128, 0));
         ctx->gridTail = ctx->numSMs * std::max(occ, 1);
+        if (const char* e = getenv("PTB200_TAIL_GRID")) ctx->gridTail = ctx->numSMs * std::max(1, atoi(e));   // developer knob
         if (cfg->flags & PT_FLAG_WAVEFRONT_ONLY) ctx->tailBounce = PT_MAX_BOUNCES;
         else if ((cfg->flags >> 8) & 0xffu) ctx->tailBounce = std::max(1u, ((cfg->flags >> 8) & 0xffu) - 1u);
         if (const char* e = getenv("PTB200_TAIL_BOUNCE")) ctx->tailBounce = std::max(1, atoi(e));      // developer knob (tools/tune.sh)
@@ -283,12 +329,22 @@ PT_API int pt_set_allreduce_hook(pt_ctx* ctx, pt_allreduce_hook hook, void* user
     ctx->hook = hook; ctx->hookUser = user;
     return PT_OK;
 }
+PT_API int pt_set_guiding_frames(pt_ctx* ctx, uint32_t frames) {
+    if (!ctx) return PT_ERR_INVALID;
+    ctx->cfg.guiding_frames = frames;
+    return PT_OK;
+}
 PT_API int pt_set_toggles(pt_ctx* ctx, int nee, int guiding) {
     if (!ctx) return PT_ERR_INVALID;
     ctx->HNEE = nee != 0; ctx->HCACHE = guiding != 0;
     return PT_OK;
 }
 PT_API void* pt_cuda_stream(pt_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+PT_API int pt_join(pt_ctx* ctx) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    return joinStreams(ctx);
+}
 
 static uint32_t tlasDepth(const pt_tlas_node* n, uint32_t count, uint32_t idx, uint32_t depth) {
     if (idx >= count || depth > 70) return depth;
@@ -300,6 +356,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     if (!ctx || !d) return PT_ERR_INVALID;
     if (d->num_models == 0 && d->num_instances > 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instances without models");
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaStreamSynchronize(ctx->stream));
     for (void* p : ctx->sceneAllocs) cudaFree(p);
     ctx->sceneAllocs.clear();
@@ -371,6 +428,7 @@ PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n,
     if (!ctx || !ctx->haveScene) return PT_ERR_INVALID;
     if (n != ctx->numInstancesCap || n_nodes != ctx->numTlasCap) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: counts differ from the uploaded scene");
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     if (tlasDepth(tlas, n_nodes, 0, 0) + ctx->maxWideDepth + 2 > PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: top-level BVH too deep");
     // pathtracer.h:245-246; pageable sources are staged before the call returns
     CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
@@ -386,25 +444,37 @@ static DCamera toDCamera(const pt_camera* c) {
     return d;
 }
 
-// Pathtracer::Render, pathtracer.h:224-302.  Asynchronous: only enqueues work on the context's stream.
+// Pathtracer::Render, pathtracer.h:224-302.  Asynchronous: only enqueues work.
 PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
     if (!ctx || !cam) return PT_ERR_INVALID;
     if (!ctx->haveScene) return fail(ctx, PT_ERR_INVALID, "pt_render: no scene uploaded");
     CK(cudaSetDevice(ctx->cfg.device));
-    cudaStream_t s = ctx->stream;
     const TileMap& map = ctx->map;
     const DCamera dcam = toDCamera(cam);
     const uint32_t npix = map.W * map.H;
+    // Clearing frames and profiled frames run alone on the public stream; converge samples are pipelined.
+    const bool pipelined = !should_clear && !ctx->prof && ctx->nSets >= 2;
+    if (!pipelined) { int jr = joinStreams(ctx); if (jr) return jr; }
+    else if (!ctx->forked) {
+        CK(cudaEventRecord(ctx->forkEv, ctx->stream));
+        for (int k = 0; k < ctx->nSets; k++) CK(cudaStreamWaitEvent(ctx->set[k].stream, ctx->forkEv, 0));
+        ctx->forked = true;
+    }
     if (should_clear) {
         ctx->DNEE = ctx->HNEE; ctx->DCACHE = ctx->HCACHE;                                  // :242-243
-        k_clear_image<<<(npix + 255) / 256, 256, 0, s>>>(ctx->image, ctx->albedo, npix);    // :248-249
+        k_clear_image<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(ctx->image, ctx->albedo, npix);    // :248-249
         ctx->sampleIdx = 0; ctx->randIdx = 0;                                              // :250-251
     }
     const uint32_t nsamples = should_clear ? ctx->cfg.interactive_depth : 1;               // :255
     const bool deviceNEE = ctx->DNEE && ctx->sc.num_lights > 0;                            // globals.h:23
     for (uint32_t sample = 0; sample < nsamples; sample++) {
-        CK(cudaMemsetAsync(ctx->q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                   // :265 (+ cursors)
-        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER); k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, ctx->q, ctx->masks, ctx->accucolors); }   // :258,:266
+        pt_ctx::SampleSet& S = ctx->set[pipelined ? ctx->cur : 0];
+        pt_ctx::SampleSet& other = ctx->set[pipelined ? (ctx->cur + ctx->nSets - 1) % ctx->nSets : 0];     // the previous sample's set
+        cudaStream_t s = pipelined ? S.stream : ctx->stream;
+        if (pipelined) ctx->cur = (ctx->cur + 1) % ctx->nSets;
+        const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots;   // :292
+        CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                      // :265 (+ cursors)
+        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
         uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
         if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
@@ -412,8 +482,8 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         auto shadeParams = [&](uint32_t bounce) {
             ShadeParams P;
             P.sc = ctx->sc; P.map = map; P.tex = ctx->tex;
-            P.masks = ctx->masks; P.accucolors = ctx->accucolors; P.lights = ctx->lights;
-            P.sampleCache = ctx->sampleCache; P.albedo = ctx->albedo;
+            P.masks = S.masks; P.accucolors = S.accucolors; P.lights = S.lights;
+            P.sampleCache = S.sampleCache; P.albedoSample = S.albedoSample;
             P.sampleIdx = ctx->sampleIdx; P.randIdx = ctx->randIdx; P.blueFrames = ctx->cfg.blue_noise_frames;
             P.bounce = (int)bounce; P.nee = deviceNEE; P.cache = ctx->DCACHE;
             return P;
@@ -421,33 +491,41 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         const uint32_t waveBounces = std::min(max_bounces, ctx->tailBounce);
         for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
-            { StageTimer tm(ctx, PT_STAGE_EXTEND);
-              k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, ctx->q.rayO[buf], ctx->q.rayD[buf], ctx->q.cnt + CNT_EXT(bounce),
-                                                               ctx->q.cnt + CUR_EXT(bounce), ctx->q.hits, nullptr, nullptr); }
-            { StageTimer tm(ctx, PT_STAGE_SHADE); k_shade<<<ctx->gridShade, 128, 0, s>>>(shadeParams(bounce), ctx->q, buf); }
+            { StageTimer tm(ctx, PT_STAGE_EXTEND, s);
+              k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce),
+                                                               S.q.cnt + CUR_EXT(bounce), S.q.hits, nullptr, nullptr); }
+            // the previous sample's propagate step rewrites the radiance cache (and shares the sample cache) shading uses:
+            // while the cache trains, only primary rays + the first extend overlap the previous sample
+            if (bounce == 0 && pipelined && ctx->prevTraining && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
+            { StageTimer tm(ctx, PT_STAGE_SHADE, s); k_shade<<<ctx->gridShade, 128, 0, s>>>(shadeParams(bounce), S.q, buf); }
             ctx->randIdx++;                                                                // :283
             if (ctx->HNEE && deviceNEE) {                                                  // :286 (no shadow rays exist when the device _NEE is false)
-                StageTimer tm(ctx, PT_STAGE_CONNECT);
-                k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, ctx->q.shO, ctx->q.shD, ctx->q.cnt + CNT_SHADOW(bounce),
-                                                                ctx->q.cnt + CUR_CONN(bounce), nullptr, ctx->lights, ctx->accucolors);
+                StageTimer tm(ctx, PT_STAGE_CONNECT, s);
+                k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
+                                                                S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors);
             }
         }
         if (max_bounces > waveBounces) {                                                   // the same bounces, one launch (k_tail)
-            StageTimer tm(ctx, PT_STAGE_TAIL);
-            k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), ctx->q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
-                                                 ctx->q.cnt + CUR_EXT(waveBounces));
+            StageTimer tm(ctx, PT_STAGE_TAIL, s);
+            k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
+                                                 S.q.cnt + CUR_EXT(waveBounces));
             ctx->randIdx += max_bounces - waveBounces;                                     // :283, once per bounce
         }
-        if (!should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots) {   // :292-296
-            StageTimer tm(ctx, PT_STAGE_GUIDING);
-            k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+        // image / albedo / statistics / radiance-cache updates happen in sample order
+        if (pipelined && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
+        if (training) {                                                                    // :292-296
+            StageTimer tm(ctx, PT_STAGE_GUIDING, s);
+            k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             if (ctx->hook) {
                 int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
                 if (hr) return fail(ctx, PT_ERR_INVALID, "pt_render: all-reduce hook failed");
             }
             k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
         }
-        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER); k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, ctx->accucolors, ctx->image, ctx->q.cnt, ctx->stats, max_bounces); }   // :299
+        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
+                          k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
+        if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
+        ctx->prevTraining = training;
         ctx->sampleIdx++;                                                                  // :300
     }
     CK(cudaGetLastError());
@@ -457,6 +535,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
 PT_API int pt_finish(pt_ctx* ctx) {                                                        // pathtracer.h:305-310
     if (!ctx) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaStreamSynchronize(ctx->stream));
     resolveProfile(ctx);
     return PT_OK;
@@ -464,6 +543,7 @@ PT_API int pt_finish(pt_ctx* ctx) {                                             
 
 PT_API int pt_set_profiling(pt_ctx* ctx, int on) {
     if (!ctx) return PT_ERR_INVALID;
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     ctx->prof = on != 0;
     for (int i = 0; i < PT_NUM_STAGES; i++) { ctx->profMs[i] = 0; ctx->profLaunches[i] = 0; }
     return PT_OK;
@@ -477,6 +557,7 @@ PT_API int pt_get_profile(pt_ctx* ctx, double* ms, uint64_t* launches) {
 PT_API int pt_read_image(pt_ctx* ctx, float* host_rgbw, int which) {
     if (!ctx || !host_rgbw) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaMemcpyAsync(host_rgbw, which == 0 ? ctx->image : ctx->albedo, (size_t)ctx->map.W * ctx->map.H * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return PT_OK;
@@ -485,6 +566,7 @@ PT_API int pt_read_image(pt_ctx* ctx, float* host_rgbw, int which) {
 PT_API int pt_read_radiance_cache(pt_ctx* ctx, pt_radiance_cache* out) {
     if (!ctx || !out || !ctx->haveScene) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     const uint32_t T = ctx->sc.num_triangles;
     std::vector<float> rc((size_t)T * 12), add((size_t)T * 16);
     CK(cudaMemcpyAsync(rc.data(), ctx->sc.rcRadiance, rc.size() * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
@@ -504,15 +586,18 @@ PT_API int pt_read_radiance_cache(pt_ctx* ctx, pt_radiance_cache* out) {
 PT_API int pt_get_stats(pt_ctx* ctx, pt_stats* out) {
     if (!ctx || !out) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     unsigned long long h[8];
     CK(cudaMemcpyAsync(h, ctx->stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     out->primary_rays = h[0]; out->extend_rays = h[1]; out->shadow_rays = h[2]; out->shade_calls = h[3]; out->samples = h[4];
+    out->wave_extend_rays = h[5]; out->wave_shadow_rays = h[6];
     return PT_OK;
 }
 PT_API int pt_reset_stats(pt_ctx* ctx) {
     if (!ctx) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaMemsetAsync(ctx->stats, 0, 8 * sizeof(unsigned long long), ctx->stream));
     return PT_OK;
 }
@@ -540,6 +625,7 @@ PT_API int pt_debug_primary_rays(pt_ctx* ctx, const pt_camera* cam, uint32_t ran
 static int debugTrace(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_hit, uint32_t repeats, float* out_ms, pt_hit* host_out) {
     if (!ctx || !host_rays || !ctx->haveScene) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     if (n > ctx->dbgCap) {
         if (ctx->dbgRays) cudaFree(ctx->dbgRays);
         if (ctx->dbgHits) cudaFree(ctx->dbgHits);

@@ -150,7 +150,10 @@ __global__ void __launch_bounds__(128) k_shade(ShadeParams P, Queues q, int inBu
 // (pathtracer.h:276-290); randIdx advances per bounce exactly as the host loop does.
 // Scratch: the path with queue index i keeps its current extension ray in ray buffer `cur`[i], writes the next
 // one to the other buffer [i] and its shadow ray to shO/shD[i] (all dead wavefront storage by now).
-__global__ void __launch_bounds__(128) k_tail(ShadeParams P, Queues q, int inBuf, int b0, int maxBounces, uint* cursor) {
+#ifndef PT_TAIL_MINBLOCKS
+#define PT_TAIL_MINBLOCKS 3
+#endif
+__global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, Queues q, int inBuf, int b0, int maxBounces, uint* cursor) {
     const DScene& sc = P.sc;
     const uint n = q.cnt[CNT_EXT(b0)];
     const uint lane = laneId();
@@ -239,8 +242,8 @@ __global__ void __launch_bounds__(128) k_tail(ShadeParams P, Queues q, int inBuf
 }
 
 // ---- accumulate + statistics -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* __restrict__ accucolors, float4* image,
-                                                    const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces) {
+__global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* __restrict__ accucolors, const float4* __restrict__ albedoSample,
+                                                    float4* image, float4* albedo, const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces, uint waveBounces) {
     const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint x, y;
     if (slotToPixel(map, slot, x, y)) {
@@ -248,11 +251,20 @@ __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* _
         const uint pix = x + y * map.W;
         const float4 p = image[pix];
         image[pix] = make_float4(fmaxf(0.0f, p.x) + c.x, fmaxf(0.0f, p.y) + c.y, fmaxf(0.0f, p.z) + c.z, p.w + 1.0f);
+        if ((__float_as_uint(c.w) & 0xffu) != 0u) {                                // albedoSet: kernels.h:56-62, deferred from shade
+            const float4 nv = albedoSample[slot];
+            const float4 a = albedo[pix];
+            albedo[pix] = make_float4(fmaxf(0.0f, a.x) + nv.x, fmaxf(0.0f, a.y) + nv.y, fmaxf(0.0f, a.z) + nv.z, a.w + 1.0f);
+        }
     }
     if (slot == 0) {
         unsigned long long ext = 0, sh = 0;
-        for (uint b = 0; b < maxBounces; b++) { ext += cnt[CNT_EXT(b)]; sh += cnt[CNT_SHADOW(b)]; }
-        stats[0] += cnt[CNT_EXT(0)]; stats[1] += ext; stats[2] += sh; stats[3] += ext; stats[4] += 1;
+        unsigned long long wext = 0, wsh = 0;
+        for (uint b = 0; b < maxBounces; b++) {
+            ext += cnt[CNT_EXT(b)]; sh += cnt[CNT_SHADOW(b)];
+            if (b < waveBounces) { wext += cnt[CNT_EXT(b)]; wsh += cnt[CNT_SHADOW(b)]; }
+        }
+        stats[0] += cnt[CNT_EXT(0)]; stats[1] += ext; stats[2] += sh; stats[3] += ext; stats[4] += 1; stats[5] += wext; stats[6] += wsh;
     }
 }
 __global__ void k_clear_image(float4* a, float4* b, uint n) {

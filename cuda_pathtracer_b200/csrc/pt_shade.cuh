@@ -82,9 +82,11 @@ __device__ __forceinline__ ShadeRay refractRay(float3 dir, float3 normal, float3
     return r;
 }
 
-__device__ __forceinline__ void updateAlbedo(float4* albedo, uint pix, float3 nv) {   // kernels.h:56-62
-    float4 p = albedo[pix];
-    albedo[pix] = make_float4(fmaxf(0.0f, p.x) + nv.x, fmaxf(0.0f, p.y) + nv.y, fmaxf(0.0f, p.z) + nv.z, p.w + 1.0f);
+// updateAlbedo (kernels.h:56-62) happens at most once per pixel per sample (albedoSet).  The value is parked per
+// slot and k_accumulate applies the reference's read-modify-write (max(0,old)+v, w+1) in sample order, so two
+// samples in flight (pt_api.cu) cannot race on the albedo image and the float sums keep the reference's order.
+__device__ __forceinline__ void updateAlbedo(float4* albedoSample, uint slot, float3 nv) {
+    albedoSample[slot] = make_float4(nv.x, nv.y, nv.z, 0.0f);
 }
 
 struct ShadeParams {
@@ -93,7 +95,7 @@ struct ShadeParams {
     FrameTex tex;
     float4 *masks, *accucolors, *lights;    // TraceStateSOA (types.h:470-499), indexed by local slot
     pt_sample_cache* sampleCache;           // [MAX_CACHE_DEPTH][nSlots]
-    float4* albedo;                         // full image, indexed by pixel
+    float4* albedoSample;                   // this sample's albedo contribution per local slot (applied by k_accumulate)
     uint sampleIdx, randIdx, blueFrames;
     int bounce;
     bool nee, cache;                        // device _NEE (globals.h:23) and DCACHE
@@ -105,7 +107,6 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
     const DScene& sc = P.sc;
     out.pushExt = out.pushShadow = false;
     uint x, y; slotToPixel(P.map, slot, x, y);
-    const uint pix = x + y * P.map.W;
     TraceState state;
     {
         const float4 m = P.masks[slot], a = P.accucolors[slot], l = P.lights[slot];
@@ -118,7 +119,7 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
     if (hit.id == 0xffffffffu) {                                              // kernels.h:526-538
         float3 sk = P.tex.skyConst;
         if (P.tex.sky) { float2 uv = normalToUv(rd); sk = f3(tex2D<float4>(P.tex.sky, uv.x, uv.y)); }
-        if (!state.albedoSet) { updateAlbedo(P.albedo, pix, state.mask * sk); state.albedoSet = true; }
+        if (!state.albedoSet) { updateAlbedo(P.albedoSample, slot, state.mask * sk); state.albedoSet = true; }
         state.accucolor += state.mask * sk;
     } else {
         RandState rs; rs.sampleIdx = P.sampleIdx; rs.randIdx = P.randIdx; rs.blueFrames = P.blueFrames;
@@ -152,7 +153,7 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
             writeCache = false; writeState = false;
             if (!P.nee || state.fromSpecular) {
                 state.accucolor += state.mask * emission;
-                if (!state.albedoSet) { updateAlbedo(P.albedo, pix, state.mask * emission); state.albedoSet = true; }
+                if (!state.albedoSet) { updateAlbedo(P.albedoSample, slot, state.mask * emission); state.albedoSet = true; }
                 writeState = true;
             }
         } else {
@@ -206,7 +207,7 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
                 const float3 noiseDir = sampleHemisphereCosine(secondary.d, ra, rb);
                 secondary.d = secondary.d * (1.0f - material.glossy) + material.glossy * noiseDir;
             } else {                                                          // kernels.h:662-782
-                if (!state.albedoSet) { updateAlbedo(P.albedo, pix, state.mask * diffuse); state.albedoSet = true; }
+                if (!state.albedoSet) { updateAlbedo(P.albedoSample, slot, state.mask * diffuse); state.albedoSet = true; }
                 state.fromSpecular = false;
                 if (P.nee) {                                                  // kernels.h:672-753
                     uint successIdx = 0; float valid = 0.0f;

@@ -30,10 +30,18 @@ def make_allreduce_hook(device, stream=None, group=None):
     import torch
     import torch.distributed as dist
 
-    def hook(ptr, count, _stream_handle):
+    streams = {}
+
+    def hook(ptr, count, stream_handle):
         t = wrap_float_buffer(ptr, count, device)
-        if stream is not None:
-            with torch.cuda.stream(stream):
+        st = stream
+        if st is None and stream_handle and str(device).startswith("cuda"):
+            # the library passes the stream the sample runs on (two samples alternate between two streams)
+            st = streams.get(stream_handle)
+            if st is None:
+                st = streams[stream_handle] = torch.cuda.ExternalStream(stream_handle, device=device)
+        if st is not None:
+            with torch.cuda.stream(st):
                 dist.all_reduce(t, group=group)
         else:
             dist.all_reduce(t, group=group)

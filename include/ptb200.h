@@ -155,10 +155,14 @@ typedef struct {
  * three wavefront launches per bounce.  Default tail bounce: 3.  PT_FLAG_TAIL_BOUNCE(n) overrides it,
  * PT_FLAG_WAVEFRONT_ONLY keeps every bounce in the wavefront. */
 #define PT_FLAG_WAVEFRONT_ONLY 1u
+/* Converge samples normally rotate through four working sets on private streams (samples k+1.. start while the
+ * short-queue end of sample k drains); results are identical.  This flag keeps one sample in flight. */
+#define PT_FLAG_NO_PIPELINE 2u
 #define PT_FLAG_TAIL_BOUNCE(n) ((((uint32_t)(n) + 1u) & 0xffu) << 8)
 
 typedef struct {                       /* device-side ray counters since the last pt_reset_stats */
     uint64_t primary_rays, extend_rays, shadow_rays, shade_calls, samples;
+    uint64_t wave_extend_rays, wave_shadow_rays;   /* the part of extend/shadow rays traced by the wavefront launches (the rest: k_tail) */
 } pt_stats;
 
 typedef struct pt_ctx pt_ctx;
@@ -178,6 +182,7 @@ PT_API const char* pt_last_error(const pt_ctx* ctx);                /* ctx may b
 PT_API int  pt_upload_scene(pt_ctx*, const pt_scene_desc*);         /* ~ upload half of Init() (pathtracer.h:129-190,216-220) */
 PT_API int  pt_update_instances(pt_ctx*, const pt_instance*, uint32_t n, const pt_tlas_node*, uint32_t n_nodes); /* pathtracer.h:245-246 */
 PT_API int  pt_set_toggles(pt_ctx*, int nee, int guiding);          /* HNEE / HCACHE (globals.h:19-20); takes effect on the next should_clear render (pathtracer.h:242-243) */
+PT_API int  pt_set_guiding_frames(pt_ctx*, uint32_t frames);           /* run-time value of the training window (pathtracer.h:292: sampleIdx < 100) */
 PT_API int  pt_set_skydome(pt_ctx*, const float* rgba, uint32_t w, uint32_t h);   /* ~ loadTextureHDR (use_cuda.h:202-263): rows already flipped */
 PT_API int  pt_set_sky_constant(pt_ctx*, float r, float g, float b);            /* constant sky radiance (default 1,1,1) when no HDR dome is available */
 PT_API int  pt_set_blue_noise(pt_ctx*, const float* lum, uint32_t w, uint32_t h); /* ~ loadTextureL (use_cuda.h:166-200) */
@@ -185,6 +190,7 @@ PT_API int  pt_texture_create(pt_ctx*, const float* rgba, uint32_t w, uint32_t h
 PT_API int  pt_set_allreduce_hook(pt_ctx*, pt_allreduce_hook hook, void* user);
 
 PT_API int  pt_render(pt_ctx*, const pt_camera*, int should_clear);   /* == Pathtracer::Render (pathtracer.h:224-302); asynchronous */
+PT_API int  pt_join(pt_ctx*);                                         /* asynchronous: orders every render enqueued so far before later work on pt_cuda_stream() (e.g. a timing event) */
 PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
 PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
 PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
