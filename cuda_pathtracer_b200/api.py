@@ -54,6 +54,7 @@ def load_library():
     L.pt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_finish.argtypes = [C.c_void_p]
     L.pt_join.argtypes = [C.c_void_p]
+    L.pt_write_pfm.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
     L.pt_set_guiding_frames.argtypes = [C.c_void_p, C.c_uint32]
     L.pt_read_image.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_read_radiance_cache.argtypes = [C.c_void_p, C.c_void_p]
@@ -97,13 +98,25 @@ class Pathtracer:
         return self.scene.arrays() if hasattr(self.scene, "arrays") else self.scene
 
     # -- Application interface --
-    def Init(self):
+    def Init(self, textures=None, normal_maps=None):
+        """textures / normal_maps: {material id: float4 RGBA image (h, w, 4)} -- what Scene::addModel does with the
+        MTL's map_Kd / norm entries (scene.h:218-243): the image becomes a texture object whose handle is stored in
+        the material before the scene is uploaded."""
         h = C.c_void_p()
         r = self.L.pt_create(C.byref(h), C.byref(self.cfg))
         if r < 0:
             raise PtError("pt_create failed (%d): %s" % (r, (self.L.pt_last_error(None) or b"").decode()))
         self.h = h
-        desc, keep = abi.make_scene_desc(self._arrays())
+        arrays = self._arrays()
+        if textures or normal_maps:
+            arrays = dict(arrays)
+            mats = arrays["materials"].copy()
+            for mid, img in (textures or {}).items():
+                mats[mid]["texture"] = self.create_texture(img); mats[mid]["hasTexture"] = 1
+            for mid, img in (normal_maps or {}).items():
+                mats[mid]["normal_texture"] = self.create_texture(img); mats[mid]["hasNormalMap"] = 1
+            arrays["materials"] = mats
+        desc, keep = abi.make_scene_desc(arrays)
         self._keep.append(keep)
         self.num_lights = self._ck(self.L.pt_upload_scene(self.h, C.byref(desc)), "pt_upload_scene")
         self.num_triangles = desc.num_triangles
@@ -160,6 +173,10 @@ class Pathtracer:
     def set_guiding_frames(self, frames):
         """Frames during which the radiance cache trains (reference pathtracer.h:292 hard-codes 100)."""
         self._ck(self.L.pt_set_guiding_frames(self.h, int(frames)), "pt_set_guiding_frames")
+
+    def write_pfm(self, path, which=0):
+        """Headless render-to-PFM: the display value rgb / sample count (reference main.cpp:58-62)."""
+        self._ck(self.L.pt_write_pfm(self.h, os.fsencode(path), int(which)), "pt_write_pfm")
 
     def join(self):
         """Asynchronous: orders every Render enqueued so far before later work on stream() (renders run on

@@ -563,6 +563,30 @@ PT_API int pt_read_image(pt_ctx* ctx, float* host_rgbw, int which) {
     return PT_OK;
 }
 
+// Headless stand-in for the GLFW window (north_star): the display value rgb / w (main.cpp:58-62) as a colour PFM
+// ("PF", little-endian floats, bottom row first).
+PT_API int pt_write_pfm(pt_ctx* ctx, const char* path, int which) {
+    if (!ctx || !path) return PT_ERR_INVALID;
+    const uint32_t W = ctx->map.W, H = ctx->map.H;
+    std::vector<float> img((size_t)W * H * 4);
+    int r = pt_read_image(ctx, img.data(), which);
+    if (r) return r;
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(ctx, PT_ERR_INVALID, "pt_write_pfm: cannot open the output file");
+    fprintf(f, "PF\n%u %u\n-1.0\n", W, H);
+    std::vector<float> row((size_t)W * 3);
+    for (uint32_t y = 0; y < H; y++) {
+        const float* src = img.data() + (size_t)(H - 1 - y) * W * 4;
+        for (uint32_t x = 0; x < W; x++) {
+            const float w = src[x * 4 + 3] > 0.0f ? src[x * 4 + 3] : 1.0f;
+            row[x * 3] = src[x * 4] / w; row[x * 3 + 1] = src[x * 4 + 1] / w; row[x * 3 + 2] = src[x * 4 + 2] / w;
+        }
+        fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    fclose(f);
+    return PT_OK;
+}
+
 PT_API int pt_read_radiance_cache(pt_ctx* ctx, pt_radiance_cache* out) {
     if (!ctx || !out || !ctx->haveScene) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));

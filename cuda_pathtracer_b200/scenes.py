@@ -214,6 +214,95 @@ def two_million_scene(nx=1004, ny=1005):
     return s.finalize()
 
 
+def _quads(a, b, c, d):
+    """Quads (n,3)x4 -> (2n, 9) triangles (a,b,c),(a,c,d) and (2n, 6) unit-square uvs."""
+    t = np.concatenate([np.concatenate([a, b, c], -1), np.concatenate([a, c, d], -1)])
+    n = len(a)
+    uv1 = np.tile(np.array([0, 0, 1, 0, 1, 1], np.float32), (n, 1))
+    uv2 = np.tile(np.array([0, 0, 1, 1, 0, 1], np.float32), (n, 1))
+    return t.astype(np.float32), np.concatenate([uv1, uv2])
+
+
+def voxel_terrain_soup(n=256, seed=3):
+    """Proxy for vokselia_spawn.obj / lost_empire.obj: an n x n field of voxel columns
+    (integer heights from seeded fBm) emitted as axis-aligned quads -- one top face per column, one wall per
+    height step between neighbours -- with uvs into a 16 x 16-tile atlas (tile chosen by face kind and height).
+    Returns (triangles (m, 9), uvs (m, 6)); n = 256 gives about 225k triangles."""
+    h = np.floor(6.0 * _fbm(n, n, seed, 4) + 8.0).astype(np.int64)
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    x0, z0, y = ii.ravel().astype(np.float64), jj.ravel().astype(np.float64), h.ravel().astype(np.float64)
+    P = lambda x, yy, z: np.stack([x, yy, z], -1)
+    tris, uvs, tiles = [], [], []
+    t, u = _quads(P(x0, y, z0), P(x0, y, z0 + 1), P(x0 + 1, y, z0 + 1), P(x0 + 1, y, z0))        # tops (normal +y)
+    tris.append(t); uvs.append(u); tiles.append(np.tile(np.where(y > 9, 2, np.where(y > 6, 0, 1)), 2))
+    for axis in (0, 1):                                                                          # walls between neighbours
+        ha = h[:-1, :] if axis == 0 else h[:, :-1]
+        hb = h[1:, :] if axis == 0 else h[:, 1:]
+        ia, ja = (ii[:-1, :], jj[:-1, :]) if axis == 0 else (ii[:, :-1], jj[:, :-1])
+        m = ha != hb
+        lo, hi = np.minimum(ha, hb)[m].astype(np.float64), np.maximum(ha, hb)[m].astype(np.float64)
+        a_hi = (ha > hb)[m]                                                                      # wall faces the lower column
+        i0, j0 = ia[m].astype(np.float64), ja[m].astype(np.float64)
+        if axis == 0:
+            xw = i0 + 1
+            A, B, C, D = P(xw, lo, j0), P(xw, lo, j0 + 1), P(xw, hi, j0 + 1), P(xw, hi, j0)      # normal -x ... flipped below
+        else:
+            zw = j0 + 1
+            A, B, C, D = P(i0 + 1, lo, zw), P(i0, lo, zw), P(i0, hi, zw), P(i0 + 1, hi, zw)
+        flip = a_hi if axis == 0 else a_hi
+        A2, B2, C2, D2 = np.where(flip[:, None], B, A), np.where(flip[:, None], A, B), np.where(flip[:, None], D, C), np.where(flip[:, None], C, D)
+        t, u = _quads(A2, B2, C2, D2)
+        tris.append(t); uvs.append(u); tiles.append(np.tile(np.where(hi > 9, 3, 4), 2))
+    tri = np.concatenate(tris); uv = np.concatenate(uvs); tile = np.concatenate(tiles)
+    tx, ty = (tile % 16).astype(np.float32), (tile // 16).astype(np.float32)
+    uv = uv.reshape(-1, 3, 2)
+    uv = np.stack([(tx[:, None] + 0.05 + 0.9 * uv[..., 0]) / 16.0, (ty[:, None] + 0.05 + 0.9 * uv[..., 1]) / 16.0], -1).reshape(-1, 6)
+    tri = tri.reshape(-1, 3, 3) - np.array([n / 2.0, 8.0, n / 2.0])
+    return np.ascontiguousarray(tri.reshape(-1, 9), np.float32), np.ascontiguousarray(uv, np.float32)
+
+
+def voxel_atlas(size=256, seed=5):
+    """Deterministic stand-in for vokselia_spawn.png: 16 x 16 tiles of noisy colour, float4 RGBA, a = 1
+    (the layout loadTexture produces, use_cuda.h:108-164)."""
+    rng = np.random.default_rng(seed)
+    base = np.array([[0.25, 0.6, 0.2], [0.5, 0.35, 0.2], [0.9, 0.9, 0.95], [0.5, 0.5, 0.55], [0.45, 0.3, 0.18]], np.float32)
+    img = np.ones((size, size, 4), np.float32)
+    ts = size // 16
+    for ty in range(16):
+        for tx in range(16):
+            c = base[(ty * 16 + tx) % len(base)]
+            noise = 0.75 + 0.25 * rng.random((ts, ts, 1), dtype=np.float32)
+            img[ty * ts:(ty + 1) * ts, tx * ts:(tx + 1) * ts, :3] = c[None, None, :] * noise
+    return img
+
+
+def minecraft_scene(n=256, copies=1):
+    """getMinecraftScene, sceneBuilder.h:220-239, with the voxel-terrain proxy.  The diffuse material is textured:
+    set material `scene.textured_material`'s `texture` handle (pt_texture_create / ora_add_texture of voxel_atlas())
+    and hasTexture before uploading.  The reference instantiates the model 20 times along x (sceneBuilder.h:228)."""
+    s = Scene()
+    tex_mat = s.addMaterial(material((1, 1, 1)))
+    p = _asset("vokselia_spawn.obj")
+    if p:
+        m = s.addModel(p, 1.0, (0, 0, 0), (0, 0, 0), tex_mat, True)
+    else:
+        tri, uv = voxel_terrain_soup(n, 3)
+        m = s.addModelSoup(tri, uvs=uv, material=tex_mat)
+    for c in range(copies):
+        s.addObject(m, position=(float(c * n), 0.0, 0.0))
+    s.finalize()
+    s.textured_material = tex_mat
+    return s
+
+
+def minecraft_camera(width, height, n=256):
+    """Bokeh camera of config C5: aperture 0.05, focalLength = distance to the terrain centre."""
+    eye = np.array([0.35 * n, 14.0, -0.35 * n])
+    d = np.array([0.0, 0.0, 0.0]) - eye
+    dist = float(np.linalg.norm(d))
+    return make_camera(tuple(eye), d / dist, 1.5, dist, 0.05, width, height)
+
+
 def teapot_like_scene(n=40):
     """Small single-instance diffuse scene for quick tests when teapot.obj is not at hand."""
     s = Scene()
@@ -242,4 +331,4 @@ def camera_sweep(scene_name, width, height, k=16):
     return cams
 
 
-SCENES = {"outside": outside_scene, "sibenik": sibenik_scene, "2mtris": two_million_scene}
+SCENES = {"outside": outside_scene, "sibenik": sibenik_scene, "2mtris": two_million_scene, "minecraft": minecraft_scene}

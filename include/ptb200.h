@@ -193,6 +193,7 @@ PT_API int  pt_render(pt_ctx*, const pt_camera*, int should_clear);   /* == Path
 PT_API int  pt_join(pt_ctx*);                                         /* asynchronous: orders every render enqueued so far before later work on pt_cuda_stream() (e.g. a timing event) */
 PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
 PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
+PT_API int  pt_write_pfm(pt_ctx*, const char* path, int which);        /* headless render-to-PFM (display value rgb / w, main.cpp:58-62) in place of the GLFW window */
 PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
 /* Per-stage device time, CUDA events around every stage launch on the context's stream; resolved by pt_finish. */
 #define PT_STAGE_EXTEND 0

@@ -200,3 +200,69 @@ def test_guiding_additions_shard_and_sum(sibenik_small):
     total = parts[0] + parts[1]
     assert np.array_equal(total[8:], single[8:])                      # additionCacheCount: integers, exact
     np.testing.assert_allclose(total[:8], single[:8], rtol=1e-4, atol=1e-5)
+
+
+def test_minecraft_textured_bokeh_blue_noise():
+    """Config C5 shape: textured voxel terrain (uv -> tex2D on the diffuse colour, kernels.h:586-604),
+    thin-lens bokeh camera (aperture 0.05), blue-noise seeding of the first sample, sky-lit, instanced twice."""
+    s = scenes.minecraft_scene(48, copies=2)
+    a = s.arrays()
+    atlas = scenes.voxel_atlas(128)
+    cfg = abi.default_config(192, 108, max_ray_depth=6, interactive_depth=1)
+    pt = api.Pathtracer(a, cfg).Init(textures={s.textured_material: atlas})
+    ora = OracleLib(cfg)
+    ao = dict(a); mats = a["materials"].copy()
+    mats[s.textured_material]["texture"] = ora.add_texture(atlas); mats[s.textured_material]["hasTexture"] = 1
+    ao["materials"] = mats
+    desc, keep = abi.make_scene_desc(ao)
+    ora.upload_scene(desc, keep)
+    blue = np.random.default_rng(7).random((64, 64)).astype(np.float32)
+    pt.set_blue_noise(blue); ora.set_blue_noise(blue)
+    cam = scenes.minecraft_camera(192, 108, 48)
+    assert np.float32(np.ravel(cam["aperture"])[0]) == np.float32(0.05)
+    render_both(pt, ora, cam, 1, 5, nee=True, guiding=False)
+    g, r = pt.read_image(), ora.read_image()
+    assert np.all(g[..., 3] == 6.0) and np.isfinite(g).all()
+    assert rel_rmse(g[..., :3], r[..., :3]) <= 5e-3            # bilinear texture fetches: 8-bit filter weights in the texture unit
+    assert rel_rmse(pt.read_image(1)[..., :3], ora.read_image(1)[..., :3]) <= 5e-3
+    assert len(np.unique(np.round(g[..., :3] / 6.0, 2).reshape(-1, 3), axis=0)) > 50      # the atlas colours are in the picture
+    pt.close(); ora.close()
+
+
+def test_two_million_triangle_shape_small():
+    """Config C4 shape at test size: displaced heightfield (the 2Mtris proxy, here 120 x 121 quads),
+    rotated -pi/2 about x, diffuse 0.4, sky-lit, NEE off, depth 8; traversal-bound."""
+    a = scenes.two_million_scene(120, 121).arrays()
+    cfg = abi.default_config(192, 108, max_ray_depth=8, interactive_depth=1)
+    pt, ora = make_pair(a, cfg)
+    cam = scenes.camera_sweep("2mtris", 192, 108, 16)[2]
+    render_both(pt, ora, cam, 1, 4, nee=False, guiding=False)
+    g, r = pt.read_image(), ora.read_image()
+    assert rel_rmse(g[..., :3], r[..., :3]) <= RMSE_EXACT
+    st, (ost, _) = pt.stats(), ora.stats()
+    assert st.primary_rays == ost.primary_rays and abs(int(st.extend_rays) - int(ost.extend_rays)) <= 1e-3 * ost.extend_rays
+    pt.close(); ora.close()
+
+
+def test_write_pfm_and_sample_pipelining_are_invisible(sibenik_small, tmp_path):
+    """Scheduling knobs change nothing: 4 samples in flight + k_tail vs one sample at a time, wavefront only
+    (guiding off => bit-identical); pt_write_pfm holds rgb / w."""
+    from util import read_pfm
+    cam = scenes.camera_sweep("sibenik", 192, 108, 16)[1]
+    imgs = []
+    for flags in (0, 1 | 2, (2 + 1) << 8):          # default; PT_FLAG_WAVEFRONT_ONLY|PT_FLAG_NO_PIPELINE; PT_FLAG_TAIL_BOUNCE(2)
+        cfg = abi.default_config(192, 108, max_ray_depth=8, interactive_depth=1, flags=flags)
+        pt = api.Pathtracer(sibenik_small, cfg).Init()
+        pt.HNEE, pt.HCACHE = True, False
+        pt.Render(cam, shouldClear=True)
+        for _ in range(6):
+            pt.Render(cam)
+        pt.Finish()
+        imgs.append((pt.read_image().copy(), pt.read_image(1).copy(), pt.stats().extend_rays, pt.stats().shadow_rays))
+        if flags == 0:
+            p = str(tmp_path / "o.pfm"); pt.write_pfm(p)
+            np.testing.assert_array_equal(read_pfm(p), imgs[0][0][..., :3] / imgs[0][0][..., 3:4])
+        pt.close()
+    for other in imgs[1:]:
+        assert np.array_equal(imgs[0][0], other[0]) and np.array_equal(imgs[0][1], other[1])
+        assert imgs[0][2] == other[2] and imgs[0][3] == other[3]
