@@ -237,6 +237,7 @@ def gpu_arm(args):
         e2 = torch.cat([r2, t2])
     e2e_value = float(e2[0].item()) / float(e2[1].item()) / 1e6
     if rank == 0:
+        l2_16, l2_32 = pt.measure_gather_bandwidth(32 << 20, 16), pt.measure_gather_bandwidth(32 << 20, 32)     # L2 gather ceiling
         peak, peak_src = read_peaks()
         cpu_v, per_ray, cpu_s, cpu_rays = cpu_leg(arrays, os.cpu_count() or 1, CPU_SAMPLES)
         # ALGORITHMIC bytes of one extend launch: per ray 32 (RayPacked R) + 16 (HitInfoPacked W)
@@ -266,7 +267,9 @@ def gpu_arm(args):
                 "roofline": {"bound": "hbm", "kernel": "k_trace<false> (extend)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": pst.wave_extend_rays * bytes_per_ext_ray / max(1, ext_n), "bytes_per_ray": bytes_per_ext_ray,
                              "avg_launch_ms": ext_ms / max(1, ext_n), "share_of_step": ext_ms / tot_prof_ms if tot_prof_ms else None,
-                             "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray); HBM copy peak is the denominator"},
+                             "l2_gather_peak_gbs": {"16B": l2_16, "32B": l2_32, "how": "pt_measure_gather_bandwidth: random reads over a 32 MB (L2-resident) array, best of 5"},
+                             "frac_of_l2_gather_peak": achieved / l2_32 if l2_32 else None,
+                             "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray on the reference BVH2); HBM copy peak is the stated denominator, the L2 gather rate the second ceiling; ncu (profiles/) shows the kernel instruction-issue bound (issue active ~67%, 13-26 of 32 lanes per instruction), not bandwidth bound"},
                 "stage_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
                 "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": "oracle/pt_oracle.cpp: %d converge samples of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_SAMPLES, CPU_W, CPU_H, cpu_rays, cpu_s)}}

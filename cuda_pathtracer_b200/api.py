@@ -54,6 +54,8 @@ def load_library():
     L.pt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_finish.argtypes = [C.c_void_p]
     L.pt_join.argtypes = [C.c_void_p]
+    L.pt_measure_gather_bandwidth.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(C.c_double)]
+    L.pt_postprocess.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p]
     L.pt_write_pfm.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
     L.pt_set_guiding_frames.argtypes = [C.c_void_p, C.c_uint32]
     L.pt_read_image.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
@@ -177,6 +179,25 @@ class Pathtracer:
     def write_pfm(self, path, which=0):
         """Headless render-to-PFM: the display value rgb / sample count (reference main.cpp:58-62)."""
         self._ck(self.L.pt_write_pfm(self.h, os.fsencode(path), int(which)), "pt_write_pfm")
+
+    def postprocess(self, blur=True, lum=None, albedo=None, nr_samples=None):
+        """The reference's display pass (main.cpp:316-376) headless: demodulated separable Gaussian, remodulate,
+        gamma 2, vignette.  lum/albedo: float4 images (e.g. a gathered multi-GPU framebuffer) or None for the
+        context's own accumulators.  Returns the RGBA float image the fragment shader writes."""
+        w, h = self.cfg.width, self.cfg.height
+        out = np.empty((h, w, 4), np.float32)
+        if lum is not None:
+            lum = np.ascontiguousarray(lum, np.float32); albedo = np.ascontiguousarray(albedo, np.float32)
+        if nr_samples is None:
+            nr_samples = float(self.rand_state()[0])
+        self._ck(self.L.pt_postprocess(self.h, abi.ptr(lum), abi.ptr(albedo), float(nr_samples), int(blur), abi.ptr(out)), "pt_postprocess")
+        return out
+
+    def measure_gather_bandwidth(self, array_bytes=32 << 20, access_bytes=32, repeats=5):
+        """GB/s of random 16/32-byte reads over an array (default 32 MB: L2-resident) -- the ceiling for BVH gathers."""
+        out = C.c_double()
+        self._ck(self.L.pt_measure_gather_bandwidth(self.h, int(array_bytes), int(access_bytes), int(repeats), C.byref(out)), "pt_measure_gather_bandwidth")
+        return out.value
 
     def join(self):
         """Asynchronous: orders every Render enqueued so far before later work on stream() (renders run on

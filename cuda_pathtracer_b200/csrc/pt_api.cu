@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 #include "pt_kernels.cuh"
+#include "pt_post.cuh"
 #include "wide_bvh.h"
 
 using namespace ptb;
@@ -35,7 +36,7 @@ struct pt_ctx {
     int nSets = PT_MAX_SETS, cur = 0;
     bool forked = false, prevTraining = false;
     cudaEvent_t forkEv = nullptr;
-    float4 *image = nullptr, *albedo = nullptr;
+    float4 *image = nullptr, *albedo = nullptr, *postBuf = nullptr;
     unsigned long long* stats = nullptr;
     // scene
     DScene sc;
@@ -156,7 +157,7 @@ PT_API void pt_destroy(pt_ctx* ctx) {
         if (S.stream) cudaStreamDestroy(S.stream);
     }
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
-    void* bufs[] = {ctx->image, ctx->albedo, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
+    void* bufs[] = {ctx->image, ctx->albedo, ctx->postBuf, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
     for (void* p : bufs) if (p) cudaFree(p);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -584,6 +585,68 @@ PT_API int pt_write_pfm(pt_ctx* ctx, const char* path, int which) {
         fwrite(row.data(), sizeof(float), row.size(), f);
     }
     fclose(f);
+    return PT_OK;
+}
+
+// The display post-process of src/main.cpp:316-376 (gauss_horz -> gauss_vert -> quad_fs_blurred, or quad_fs alone),
+// headless: result = the RGBA the fragment shader would write, one float4 per pixel.  lum / albedo: host float4
+// images to process (e.g. the gathered multi-GPU framebuffer) or NULL for the context's own accumulators.
+PT_API int pt_postprocess(pt_ctx* ctx, const float* lum_host, const float* albedo_host, float nr_samples, int blur, float* out_host_rgba) {
+    if (!ctx || !out_host_rgba || (lum_host == nullptr) != (albedo_host == nullptr)) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    const int W = (int)ctx->map.W, H = (int)ctx->map.H;
+    const size_t n = (size_t)W * H;
+    cudaStream_t s = ctx->stream;
+    if (!ctx->postBuf) CK(cudaMalloc((void**)&ctx->postBuf, 4 * n * sizeof(float4)));
+    float4 *tmpA = ctx->postBuf, *tmpB = ctx->postBuf + n, *inL = ctx->postBuf + 2 * n, *inA = ctx->postBuf + 3 * n;
+    const float4 *lum = ctx->image, *alb = ctx->albedo;
+    if (lum_host) {
+        CK(cudaMemcpyAsync(inL, lum_host, n * sizeof(float4), cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(inA, albedo_host, n * sizeof(float4), cudaMemcpyHostToDevice, s));
+        lum = inL; alb = inA;
+    }
+    const dim3 blk(32, 8), grd((W + 31) / 32, (H + 7) / 8);
+    if (blur) {
+        k_post_horz<<<grd, blk, 0, s>>>(lum, alb, tmpA, W, H, nr_samples);              // main.cpp:322-329
+        k_post_vert<<<grd, blk, 0, s>>>(tmpA, tmpB, W, H, nr_samples);                  // main.cpp:331-336
+        k_post_resolve<<<grd, blk, 0, s>>>(tmpB, alb, tmpA, W, H, 1);                   // main.cpp:370-376, quad_fs_blurred
+    } else k_post_resolve<<<grd, blk, 0, s>>>(lum, alb, tmpA, W, H, 0);                 // quad_fs
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_host_rgba, tmpA, n * sizeof(float4), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return PT_OK;
+}
+
+// Measured ceiling for the BVH gathers: GB/s of random `access_bytes` (16 or 32) reads over `array_bytes` of device
+// memory (<= L2 size: the L2 gather rate; larger: the HBM random-access rate).
+PT_API int pt_measure_gather_bandwidth(pt_ctx* ctx, uint64_t array_bytes, uint32_t access_bytes, uint32_t repeats, double* out_gbs) {
+    if (!ctx || !out_gbs || (access_bytes != 16 && access_bytes != 32) || array_bytes < 4096) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    uint32_t nElems = 1; while ((uint64_t)nElems * 2 * access_bytes <= array_bytes) nElems *= 2;
+    float4* data = nullptr; float* sink = nullptr;
+    CK(cudaMalloc((void**)&data, (size_t)nElems * access_bytes));
+    cudaError_t e = cudaMalloc((void**)&sink, sizeof(float));
+    if (e != cudaSuccess) { cudaFree(data); CK(e); }
+    cudaStream_t s = ctx->stream;
+    cudaMemsetAsync(data, 0, (size_t)nElems * access_bytes, s);
+    const uint32_t iters = 256, blocks = ctx->numSMs * 8, threads = 256;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (uint32_t r = 0; r < std::max(repeats, 2u) + 1; r++) {
+        cudaEventRecord(e0, s);
+        if (access_bytes == 16) k_gather_probe<1><<<blocks, threads, 0, s>>>(data, nElems, iters, sink);
+        else k_gather_probe<2><<<blocks, threads, 0, s>>>(data, nElems, iters, sink);
+        cudaEventRecord(e1, s);
+        cudaStreamSynchronize(s);
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        if (r > 0) best = std::min(best, ms);            // first pass warms the cache
+    }
+    e = cudaGetLastError();
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(data); cudaFree(sink);
+    CK(e);
+    *out_gbs = (double)blocks * threads * iters * access_bytes / (best * 1e-3) / 1e9;
     return PT_OK;
 }
 

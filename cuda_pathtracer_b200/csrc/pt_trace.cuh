@@ -88,7 +88,7 @@ __device__ __forceinline__ bool triIntersect(float3 o, float3 d, float3 v0, floa
 #endif
 #ifndef PT_KEEP_NUM
 #define PT_KEEP_NUM 1          /* the bottom-level loop runs while >= PT_KEEP_NUM/PT_KEEP_DEN of the lanes that */
-#define PT_KEEP_DEN 2          /* entered it still have bottom-level work; the others wait for the next top-level phase */
+#define PT_KEEP_DEN 32         /* entered it still have bottom-level work; the others wait for the next top-level phase */
 #endif
 
 // Per-lane traversal state.  A lane is idle (ray == PT_NONE), in the top level (curT / TLAS entries

@@ -320,8 +320,8 @@ def camera_sweep(scene_name, width, height, k=16):
             eye = (14.0 * math.cos(a), 1.5 + 1.0 * math.sin(2 * a), 4.5 * math.sin(a))
             target = (0.0, 2.0, 0.0)
         elif scene_name == "2mtris":
-            eye = (60.0 * math.cos(a), 25.0, 60.0 * math.sin(a))
-            target = (0.0, 0.0, 0.0)
+            eye = (21.0 * math.cos(a), 8.0, 21.0 * math.sin(a))      # the heightfield spans +-20 in x/z after the 0.2 scale
+            target = (0.0, -1.0, 0.0)
         else:
             eye = (18.0 * math.cos(a), 6.0, 18.0 * math.sin(a))
             target = (0.0, 0.0, 0.0)

@@ -194,6 +194,11 @@ PT_API int  pt_join(pt_ctx*);                                         /* asynchr
 PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
 PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
 PT_API int  pt_write_pfm(pt_ctx*, const char* path, int which);        /* headless render-to-PFM (display value rgb / w, main.cpp:58-62) in place of the GLFW window */
+/* Display post-process (main.cpp:46-171,316-376: demodulated separable Gaussian, remodulate, gamma 2, vignette) as CUDA
+ * kernels; host float4 in (or NULL, NULL = the context's accumulators), host float4 RGBA out. */
+PT_API int  pt_postprocess(pt_ctx*, const float* lum_host, const float* albedo_host, float nr_samples, int blur, float* out_host_rgba);
+/* Roofline helper: measured GB/s of random 16/32-byte reads over an array of `array_bytes` (L2-resident when it fits). */
+PT_API int  pt_measure_gather_bandwidth(pt_ctx*, uint64_t array_bytes, uint32_t access_bytes, uint32_t repeats, double* out_gbs);
 PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
 /* Per-stage device time, CUDA events around every stage launch on the context's stream; resolved by pt_finish. */
 #define PT_STAGE_EXTEND 0

@@ -98,6 +98,13 @@ class OracleLib:
         self._keep.append(rgba)
         return int(self.L.ora_add_texture(self.h, abi.ptr(rgba), C.c_uint32(rgba.shape[1]), C.c_uint32(rgba.shape[0])))
 
+    def postprocess(self, lum, albedo, nr_samples, blur=True):
+        """CPU restatement of the reference's display shaders (main.cpp:46-171): float4 images in, RGBA out."""
+        lum = np.ascontiguousarray(lum, np.float32); albedo = np.ascontiguousarray(albedo, np.float32)
+        out = np.empty_like(lum)
+        self.L.ora_postprocess(abi.ptr(lum), abi.ptr(albedo), C.c_int(lum.shape[1]), C.c_int(lum.shape[0]), C.c_float(nr_samples), C.c_int(int(blur)), abi.ptr(out))
+        return out
+
     def render(self, cam, should_clear):
         self.L.ora_render(self.h, abi.ptr(cam), C.c_int(int(should_clear)))
 

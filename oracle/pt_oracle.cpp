@@ -981,3 +981,53 @@ ORA_API int ora_plane_intersect(const float* ray6, const float* n, float d, floa
 ORA_API int ora_slab(const float* origin, const float* invdir, const float* box6, float* tmin) {
     return slabTest(mk3(origin[0], origin[1], origin[2]), mk3(invdir[0], invdir[1], invdir[2]), box6, box6 + 3, *tmin) ? 1 : 0;
 }
+
+// ---- display post-process: CPU restatement of the reference's GLSL (src/main.cpp:46-171), chained as main.cpp:316-376.
+// lum / albedo: float4 per pixel (rgb sums, w = counts).  blur != 0: gauss_horz (:111-141) -> gauss_vert (:143-171) ->
+// quad_fs_blurred (:76-109); blur == 0: quad_fs (:46-74).  The shaders' hard-coded 640/480 bounds are W/H.
+// Parity UNPINNED: the GLSL cannot run on this box (no graphics stack); checked by review against the shader source.
+ORA_API void ora_postprocess(const float* lum, const float* albedo, int W, int H, float nrSamples, int blur, float* out) {
+    const size_t n = (size_t)W * H;
+    std::vector<float> horz(n * 4), vert(n * 4);
+    const float spread = std::max(0.7f, nrSamples / 200.0f);
+    auto gauss = [&](int i) { return expf(-(float)(i * i) * 0.5f * spread) / sqrtf(2.0f * 3.1415926f); };
+    const float* src = lum;
+    if (blur) {
+        for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+            float sum = 0.0f, cs[3] = {0, 0, 0};
+            for (int i = -3; i < 4; i++) {
+                if (x + i < 0 || x + i >= W) continue;
+                const float* l = lum + ((size_t)y * W + x + i) * 4; const float* a = albedo + ((size_t)y * W + x + i) * 4;
+                const float g = gauss(i);
+                for (int k = 0; k < 3; k++) cs[k] = cs[k] + ((l[k] / std::max(a[k], 0.001f)) * nrSamples) * g;
+                sum += g;
+            }
+            float* d = &horz[((size_t)y * W + x) * 4];
+            d[0] = cs[0] / sum; d[1] = cs[1] / sum; d[2] = cs[2] / sum; d[3] = nrSamples;
+        }
+        for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+            float sum = 0.0f, cs[3] = {0, 0, 0};
+            for (int i = -4; i < 4; i++) {
+                if (y + i < 0 || y + i >= H) continue;
+                const float* l = &horz[((size_t)(y + i) * W + x) * 4];
+                const float g = gauss(i);
+                for (int k = 0; k < 3; k++) cs[k] = cs[k] + l[k] * g;
+                sum += g;
+            }
+            float* d = &vert[((size_t)y * W + x) * 4];
+            d[0] = cs[0] / sum; d[1] = cs[1] / sum; d[2] = cs[2] / sum; d[3] = nrSamples;
+        }
+        src = vert.data();
+    }
+    for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+        const float u = ((float)x + 0.5f) / (float)W - 0.5f, v = ((float)y + 0.5f) / (float)H - 0.5f;
+        const float* l = src + ((size_t)y * W + x) * 4; const float* a = albedo + ((size_t)y * W + x) * 4;
+        const float vig = 1.0f - (u * u + v * v);
+        for (int k = 0; k < 3; k++) {
+            float c = l[k] / l[3];
+            if (blur) c = c * (a[k] / a[3]);
+            out[((size_t)y * W + x) * 4 + k] = powf(c, 1.0f / 2.0f) * vig;
+        }
+        out[((size_t)y * W + x) * 4 + 3] = vig;
+    }
+}

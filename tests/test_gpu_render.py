@@ -266,3 +266,26 @@ def test_write_pfm_and_sample_pipelining_are_invisible(sibenik_small, tmp_path):
     for other in imgs[1:]:
         assert np.array_equal(imgs[0][0], other[0]) and np.array_equal(imgs[0][1], other[1])
         assert imgs[0][2] == other[2] and imgs[0][3] == other[3]
+
+
+@pytest.mark.parametrize("blur", [True, False])
+def test_display_postprocess_matches_shader_restatement(sibenik_small, blur):
+    """gauss_horz / gauss_vert / quad_fs(_blurred) (main.cpp:46-171) as CUDA kernels vs the CPU
+    restatement of the same shader source on the same accumulators; tolerance 1e-5 relative (expf/powf ulps)."""
+    cfg = abi.default_config(192, 108, max_ray_depth=4, interactive_depth=1)
+    pt = api.Pathtracer(sibenik_small, cfg).Init()
+    cam = scenes.camera_sweep("sibenik", 192, 108, 16)[2]
+    pt.Render(cam, shouldClear=True)
+    for _ in range(7):
+        pt.Render(cam)
+    pt.Finish()
+    lum, alb = pt.read_image(0), pt.read_image(1)
+    got = pt.postprocess(blur=blur)
+    ora = OracleLib(cfg)
+    want = ora.postprocess(lum, alb, 8.0, blur)
+    assert pt.rand_state()[0] == 8
+    ok = np.isfinite(want)
+    assert ok.mean() > 0.99 and np.array_equal(np.isfinite(got), ok)
+    np.testing.assert_allclose(got[ok], want[ok], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(pt.postprocess(blur=blur, lum=lum, albedo=alb, nr_samples=8.0)[ok], got[ok], rtol=0, atol=0)   # host-image path
+    pt.close(); ora.close()
