@@ -409,6 +409,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     if ((r = devUpload(ctx, &ds, d->spheres, d->num_spheres, true))) return r;
     if ((r = devUpload(ctx, &dp, d->planes, d->num_planes, true))) return r;
     if ((r = devUpload(ctx, &dli, lights.data(), lights.size(), true))) return r;
+    if ((r = devAlloc(ctx, &sc.lightTab, lights.size() * PT_LIGHT_STRIDE, true))) return r;
     if ((r = devAlloc(ctx, &sc.rcRadiance, (size_t)d->num_triangles * 3, true))) return r;
     if ((r = devAlloc(ctx, &sc.rcAdditions, (size_t)d->num_triangles * 16, true))) return r;
     sc.nodes = dn; sc.wtris = dt; sc.vertices = dv; sc.vertexData = dd; sc.materials = dm; sc.instances = di; sc.tlas = dl;
@@ -420,6 +421,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
         k_rc_init<<<(d->num_triangles + 255) / 256, 256, 0, ctx->stream>>>(sc.rcRadiance, sc.rcAdditions, d->num_triangles);   // pathtracer.h:220
         CK(cudaGetLastError());
     }
+    if (sc.num_lights) { k_prepare_lights<<<(sc.num_lights + 127) / 128, 128, 0, ctx->stream>>>(sc); CK(cudaGetLastError()); }
     CK(cudaStreamSynchronize(ctx->stream));      // host vectors above go out of scope
     ctx->haveScene = true;
     return (int)lights.size();
@@ -434,6 +436,7 @@ PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n,
     // pathtracer.h:245-246; pageable sources are staged before the call returns
     CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync((void*)ctx->sc.tlas, tlas, n_nodes * sizeof(pt_tlas_node), cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->sc.num_lights) { k_prepare_lights<<<(ctx->sc.num_lights + 127) / 128, 128, 0, ctx->stream>>>(ctx->sc); CK(cudaGetLastError()); }   // per-light NEE terms follow the instance transforms
     return PT_OK;
 }
 

@@ -97,6 +97,7 @@ struct DScene {
     const pt_sphere* spheres;
     const pt_plane* planes;
     const pt_triangle_light* lights;
+    float4* lightTab;           // 6 x float4 per light, everything NEE needs that depends on the light only (k_prepare_lights)
     float4* rcRadiance;         // 3 x float4 per triangle: radianceCache[8], radianceTotal, pad[3]
     float* rcAdditions;         // SoA [16][num_triangles]: additionCache[8] then additionCacheCount[8]
     uint num_triangles, num_instances, num_spheres, num_planes, num_lights;

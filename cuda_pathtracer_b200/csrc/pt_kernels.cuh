@@ -110,8 +110,16 @@ __global__ void __launch_bounds__(128) k_trace_debug(DScene sc, const pt_ray* __
     traceLoop<ANY>(sc, n, cursor, io);
 }
 
+__global__ void k_prepare_lights(DScene sc) {
+    const uint i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < sc.num_lights) prepareLight(sc, i);
+}
+
 // ---- shade ----------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_shade(ShadeParams P, Queues q, int inBuf) {
+#ifndef PT_SHADE_MINBLOCKS
+#define PT_SHADE_MINBLOCKS 8
+#endif
+__global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P, Queues q, int inBuf) {
     const uint n = q.cnt[CNT_EXT(P.bounce)];
     const uint warpsTotal = (gridDim.x * blockDim.x) >> 5;
     const uint warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;

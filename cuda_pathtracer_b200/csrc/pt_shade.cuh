@@ -16,6 +16,40 @@ struct FrameTex {
 
 struct TraceState { float3 mask, accucolor, light; bool fromSpecular, albedoSet; };   // types.h:461-468
 
+// Per-light terms of next event estimation (kernels.h:676-716) depend on the light only, not on the shading point:
+// they are computed once per scene / instance update with the SAME expressions the reference evaluates per ray
+// (bit-identical values), PT_LIGHT_STRIDE float4 per light:
+//   [0] centroid (world)  [1] normalize(T * normal)  [2] v0  [3] v1-v0  [4] v2-v0  [5] cross/|cross|, |cross|  [6] emission
+#define PT_LIGHT_STRIDE 8
+__device__ __forceinline__ void prepareLight(const DScene& sc, uint i) {
+    const pt_triangle_light light = sc.lights[i];
+    const pt_triangle_v lv = sc.vertices[light.triangle_index];
+    const pt_instance& li = sc.instances[light.instance_index];
+    const pt_mat4x3& T = li.transform;
+    float3 centroid = (f3(lv.v0.x, lv.v0.y, lv.v0.z) + f3(lv.v1.x, lv.v1.y, lv.v1.z) + f3(lv.v2.x, lv.v2.y, lv.v2.z)) / 3.0f;
+    centroid = matmul(T, centroid, 1.0f);
+    const pt_float3 ln = sc.vertexData[light.triangle_index].normal;
+    const float3 lightNormal = normalize(matmul(T, f3(ln.x, ln.y, ln.z), 0.0f));
+    const float3 v0 = matmul(T, f3(lv.v0.x, lv.v0.y, lv.v0.z), 1.0f);
+    const float3 v1 = matmul(T, f3(lv.v1.x, lv.v1.y, lv.v1.z), 1.0f);
+    const float3 v2 = matmul(T, f3(lv.v2.x, lv.v2.y, lv.v2.z), 1.0f);
+    const float3 v0v1 = v1 - v0, v0v2 = v2 - v0;
+    const float3 cr = cross(v0v1, v0v2);
+    const float crLength = length(cr);
+    const float3 n2 = cr / crLength;
+    const uint mid = li.material_id == 0xffffffffu ? sc.vertexData[light.triangle_index].material : li.material_id;
+    const pt_float3 em = sc.materials[mid].emission;
+    float4* o = sc.lightTab + (size_t)i * PT_LIGHT_STRIDE;
+    o[0] = make_float4(centroid.x, centroid.y, centroid.z, 0.0f);
+    o[1] = make_float4(lightNormal.x, lightNormal.y, lightNormal.z, 0.0f);
+    o[2] = make_float4(v0.x, v0.y, v0.z, 0.0f);
+    o[3] = make_float4(v0v1.x, v0v1.y, v0v1.z, 0.0f);
+    o[4] = make_float4(v0v2.x, v0v2.y, v0v2.z, 0.0f);
+    o[5] = make_float4(n2.x, n2.y, n2.z, crLength);
+    o[6] = make_float4(em.x, em.y, em.z, 0.0f);
+    o[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
 // kernels.h:31-36
 __device__ __forceinline__ float2 normalToUv(float3 n) {
     return make_float2(atan2f(n.x, n.z) / (2.0f * PT_PI), -acosf(n.y) / PT_PI);
@@ -211,28 +245,19 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
                 state.fromSpecular = false;
                 if (P.nee) {                                                  // kernels.h:672-753
                     uint successIdx = 0; float valid = 0.0f;
-                    for (uint k = 0; k < 4; k++) {
+                    for (uint k = 0; k < 4; k++) {                            // kernels.h:676-690; per-light terms come from k_prepare_lights
                         const uint lightSource = uint(rnd(rs) * sc.num_lights) % sc.num_lights;
-                        const pt_triangle_light light = sc.lights[lightSource];
-                        const pt_triangle_v lv = sc.vertices[light.triangle_index];
-                        const pt_mat4x3& lt = sc.instances[light.instance_index].transform;
-                        float3 centroid = (f3(lv.v0.x, lv.v0.y, lv.v0.z) + f3(lv.v1.x, lv.v1.y, lv.v1.z) + f3(lv.v2.x, lv.v2.y, lv.v2.z)) / 3.0f;
-                        centroid = matmul(lt, centroid, 1.0f);
-                        const pt_float3 ln = sc.vertexData[light.triangle_index].normal;
-                        const float3 lightNormal = normalize(matmul(lt, f3(ln.x, ln.y, ln.z), 0.0f));
+                        const float3 centroid = f3(sc.lightTab[lightSource * PT_LIGHT_STRIDE]);
+                        const float3 lightNormal = f3(sc.lightTab[lightSource * PT_LIGHT_STRIDE + 1]);
                         const float3 fromLight = normalize(intersectionPos - centroid);
                         if (dot(lightNormal, fromLight) > 0) { valid += 1.0f; successIdx = lightSource; }
                     }
                     if (valid > 0) {
-                        const pt_triangle_light light = sc.lights[successIdx];
-                        const pt_triangle_v lv = sc.vertices[light.triangle_index];
-                        const pt_instance& li = sc.instances[light.instance_index];
-                        const float3 v0 = matmul(li.transform, f3(lv.v0.x, lv.v0.y, lv.v0.z), 1.0f);
-                        const float3 v1 = matmul(li.transform, f3(lv.v1.x, lv.v1.y, lv.v1.z), 1.0f);
-                        const float3 v2 = matmul(li.transform, f3(lv.v2.x, lv.v2.y, lv.v2.z), 1.0f);
-                        const float3 v0v1 = v1 - v0, v0v2 = v2 - v0;
-                        const float3 cr = cross(v0v1, v0v2);
-                        const float crLength = length(cr);
+                        const float4* lt = sc.lightTab + successIdx * PT_LIGHT_STRIDE;
+                        const float3 v0 = f3(lt[2]), v0v1 = f3(lt[3]), v0v2 = f3(lt[4]);
+                        const float4 ln4 = lt[5];
+                        const float3 lightNormal = f3(ln4);                   // cr / crLength
+                        const float crLength = ln4.w;
                         float u = rnd(rs), v = rnd(rs);
                         if (u + v > 1.0f) { u = 1.0f - u; v = 1.0f - v; }
                         const float3 samplePoint = v0 + u * v0v1 + v * v0v2;
@@ -240,12 +265,10 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
                         const float shadowLength = length(shadowDir);
                         const float invShadowLength = 1.0f / shadowLength;
                         shadowDir *= invShadowLength;
-                        const float3 lightNormal = cr / crLength;
                         const float NL = dot(colliderNormal, -shadowDir);
                         const float LNL = dot(lightNormal, shadowDir);
                         if (NL > 0 && dot(-shadowDir, surfaceNormal) > 0 && LNL > 0) {
-                            const uint mid = li.material_id == 0xffffffffu ? sc.vertexData[light.triangle_index].material : li.material_id;
-                            const pt_float3 em = sc.materials[mid].emission;
+                            const float4 em = lt[6];
                             const float A = 0.5f * crLength;
                             const float SA = LNL * A * invShadowLength * invShadowLength;
                             state.light = state.mask * (NL * SA * sc.num_lights * BRDF * f3(em.x, em.y, em.z) * (valid / 4.0f));
