@@ -179,6 +179,7 @@ def gpu_arm(args):
     sampler.stop_flag = True
     ms = e0.elapsed_time(e1)
     st = pt.stats()
+    timed_launches = int(st.kernel_launches)
     rays = torch.tensor([st.extend_rays + st.shadow_rays, st.extend_rays, st.shadow_rays], dtype=torch.float64, device="cuda")
     tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -251,7 +252,6 @@ def gpu_arm(args):
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("k_trace<false>", {}).get("dram_bytes_per_launch")
         tot_prof_ms = sum(v[0] for v in prof.values())
-        launches_per_step = sum(v[1] for v in prof.values()) / args.steps + (2 if pst.samples and False else 0)   # stage launches counted by the library (pt_get_profile)
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "samples_in_flight": 4, "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
@@ -263,7 +263,7 @@ def gpu_arm(args):
                 "clocks": sampler.summary(),
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(inst.nbytes + tlas.nbytes + 76),
                         "d2h_bytes_per_step": int(W * H * 16)},
-                "gpu_launches": int(launches_per_step * args.steps),
+                "gpu_launches": timed_launches,
                 "roofline": {"bound": "hbm", "kernel": "k_trace<false> (extend)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": pst.wave_extend_rays * bytes_per_ext_ray / max(1, ext_n), "bytes_per_ray": bytes_per_ext_ray,
                              "avg_launch_ms": ext_ms / max(1, ext_n), "share_of_step": ext_ms / tot_prof_ms if tot_prof_ms else None,

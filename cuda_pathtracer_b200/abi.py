@@ -65,7 +65,7 @@ class Config(C.Structure):             # pt_config
 class Stats(C.Structure):              # pt_stats
     _fields_ = [("primary_rays", C.c_uint64), ("extend_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("shade_calls", C.c_uint64), ("samples", C.c_uint64),
-                ("wave_extend_rays", C.c_uint64), ("wave_shadow_rays", C.c_uint64)]
+                ("wave_extend_rays", C.c_uint64), ("wave_shadow_rays", C.c_uint64), ("kernel_launches", C.c_uint64)]
 
 
 ALLREDUCE_HOOK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)

@@ -51,6 +51,7 @@ struct pt_ctx {
     bool HNEE = true, HCACHE = true;      // pathtracer.h:213-214
     bool DNEE = false, DCACHE = false;    // __constant__ copies, synced on shouldClear (pathtracer.h:242-243)
     uint32_t sampleIdx = 0, randIdx = 0;
+    unsigned long long launches = 0;      // kernels launched by pt_render since the last pt_reset_stats
     pt_allreduce_hook hook = nullptr;
     void* hookUser = nullptr;
     int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0, gridTail = 0;
@@ -466,7 +467,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
     }
     if (should_clear) {
         ctx->DNEE = ctx->HNEE; ctx->DCACHE = ctx->HCACHE;                                  // :242-243
-        k_clear_image<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(ctx->image, ctx->albedo, npix);    // :248-249
+        ctx->launches++, k_clear_image<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(ctx->image, ctx->albedo, npix);    // :248-249
         ctx->sampleIdx = 0; ctx->randIdx = 0;                                              // :250-251
     }
     const uint32_t nsamples = should_clear ? ctx->cfg.interactive_depth : 1;               // :255
@@ -478,7 +479,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         if (pipelined) ctx->cur = (ctx->cur + 1) % ctx->nSets;
         const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots;   // :292
         CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                      // :265 (+ cursors)
-        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
+        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); ctx->launches++, k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
         uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
         if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
@@ -493,25 +494,34 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             return P;
         };
         const uint32_t waveBounces = std::min(max_bounces, ctx->tailBounce);
+        const bool connects = ctx->HNEE && deviceNEE;                                      // :286 (no shadow rays exist when the device _NEE is false)
+        const bool fuse = connects && !ctx->prof;                                          // connect(b) rides in the launch of extend(b+1)
+        auto launchConnect = [&](uint32_t bounce) {
+            StageTimer tm(ctx, PT_STAGE_CONNECT, s);
+            ctx->launches++, k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
+                                                            S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors);
+        };
         for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
-            { StageTimer tm(ctx, PT_STAGE_EXTEND, s);
-              k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce),
-                                                               S.q.cnt + CUR_EXT(bounce), S.q.hits, nullptr, nullptr); }
+            if (fuse && bounce > 0) {
+                StageTimer tm(ctx, PT_STAGE_EXTEND, s);
+                ctx->launches++, k_trace_pair<<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce), S.q.cnt + CUR_EXT(bounce), S.q.hits,
+                                                               S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce - 1), S.q.cnt + CUR_CONN(bounce - 1), S.lights, S.accucolors);
+            } else {
+                StageTimer tm(ctx, PT_STAGE_EXTEND, s);
+                ctx->launches++, k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce),
+                                                                 S.q.cnt + CUR_EXT(bounce), S.q.hits, nullptr, nullptr);
+            }
             // the previous sample's propagate step rewrites the radiance cache (and shares the sample cache) shading uses:
             // while the cache trains, only primary rays + the first extend overlap the previous sample
             if (bounce == 0 && pipelined && ctx->prevTraining && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
-            { StageTimer tm(ctx, PT_STAGE_SHADE, s); k_shade<<<ctx->gridShade, 128, 0, s>>>(shadeParams(bounce), S.q, buf); }
+            { StageTimer tm(ctx, PT_STAGE_SHADE, s); ctx->launches++, k_shade<<<ctx->gridShade, 128, 0, s>>>(shadeParams(bounce), S.q, buf); }
             ctx->randIdx++;                                                                // :283
-            if (ctx->HNEE && deviceNEE) {                                                  // :286 (no shadow rays exist when the device _NEE is false)
-                StageTimer tm(ctx, PT_STAGE_CONNECT, s);
-                k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
-                                                                S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors);
-            }
+            if (connects && (!fuse || bounce + 1 == waveBounces)) launchConnect(bounce);
         }
         if (max_bounces > waveBounces) {                                                   // the same bounces, one launch (k_tail)
             StageTimer tm(ctx, PT_STAGE_TAIL, s);
-            k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
+            ctx->launches++, k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
                                                  S.q.cnt + CUR_EXT(waveBounces));
             ctx->randIdx += max_bounces - waveBounces;                                     // :283, once per bounce
         }
@@ -519,15 +529,15 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         if (pipelined && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
         if (training) {                                                                    // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING, s);
-            k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            ctx->launches++, k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             if (ctx->hook) {
                 int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
                 if (hr) return fail(ctx, PT_ERR_INVALID, "pt_render: all-reduce hook failed");
             }
-            k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            ctx->launches++, k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
         }
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
-                          k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
+                          ctx->launches++, k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
         if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
         ctx->prevTraining = training;
         ctx->sampleIdx++;                                                                  // :300
@@ -681,7 +691,7 @@ PT_API int pt_get_stats(pt_ctx* ctx, pt_stats* out) {
     CK(cudaMemcpyAsync(h, ctx->stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     out->primary_rays = h[0]; out->extend_rays = h[1]; out->shadow_rays = h[2]; out->shade_calls = h[3]; out->samples = h[4];
-    out->wave_extend_rays = h[5]; out->wave_shadow_rays = h[6];
+    out->wave_extend_rays = h[5]; out->wave_shadow_rays = h[6]; out->kernel_launches = ctx->launches;
     return PT_OK;
 }
 PT_API int pt_reset_stats(pt_ctx* ctx) {
@@ -689,6 +699,7 @@ PT_API int pt_reset_stats(pt_ctx* ctx) {
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaMemsetAsync(ctx->stats, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    ctx->launches = 0;
     return PT_OK;
 }
 PT_API int pt_get_rand_state(pt_ctx* ctx, uint32_t* sampleIdx, uint32_t* randIdx) {

@@ -103,6 +103,21 @@ __global__ void __launch_bounds__(128) k_trace(DScene sc, const float4* __restri
     traceLoop<ANY>(sc, *count, cursor, io);
 }
 
+// extend(b+1) and connect(b) in ONE launch: both queues exist once shade(b) has run and neither kernel touches what the
+// other writes (hits vs accucolors), so the dependent-launch chain per bounce is shade -> trace instead of
+// shade -> connect -> extend.  Warps drain the extension queue first, then the shadow queue fills the gaps its
+// stragglers leave.  (The per-stage profiling pass launches them separately to time them apart.)
+__global__ void __launch_bounds__(128, 8) k_trace_pair(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+                                                    const uint* __restrict__ extCount, uint* extCursor, float4* __restrict__ hits,
+                                                    const float4* __restrict__ shO, const float4* __restrict__ shD,
+                                                    const uint* __restrict__ shCount, uint* shCursor,
+                                                    const float4* __restrict__ lights, float4* accucolors) {
+    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr;
+    traceLoop<false>(sc, *extCount, extCursor, e);
+    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors;
+    traceLoop<true>(sc, *shCount, shCursor, c);
+}
+
 // stage-parity hook: reference-format rays in, reference-format hits out (pt_debug_trace)
 template <bool ANY>
 __global__ void __launch_bounds__(128) k_trace_debug(DScene sc, const pt_ray* __restrict__ rays, uint n, uint* cursor, pt_hit* __restrict__ out) {

@@ -163,6 +163,7 @@ typedef struct {
 typedef struct {                       /* device-side ray counters since the last pt_reset_stats */
     uint64_t primary_rays, extend_rays, shadow_rays, shade_calls, samples;
     uint64_t wave_extend_rays, wave_shadow_rays;   /* the part of extend/shadow rays traced by the wavefront launches (the rest: k_tail) */
+    uint64_t kernel_launches;                      /* kernels pt_render launched (host-side count) */
 } pt_stats;
 
 typedef struct pt_ctx pt_ctx;

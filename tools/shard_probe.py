@@ -22,3 +22,12 @@ pt.join(); e1.record(stream); pt.Finish()
 ms = e0.elapsed_time(e1); st = pt.stats()
 print("world %d: %.3f ms/sample, %.1f Mrays/s on this rank (x%d = %.1f)" % (world, ms / steps, (st.extend_rays + st.shadow_rays) / ms / 1e3, world, world * (st.extend_rays + st.shadow_rays) / ms / 1e3))
 pt.close()
+# per-stage device time of one sample at this shard size (serialised, event pairs around every launch)
+pt = api.Pathtracer(arrays, cfg).Init()
+pt.Render(cams[0], shouldClear=True)
+for i in range(110): pt.Render(cams[i % 16])
+pt.Finish(); pt.set_profiling(True)
+for i in range(50): pt.Render(cams[i % 16])
+pt.Finish()
+print("  stage us/sample:", {k: round(1e3 * v[0] / 50, 1) for k, v in pt.profile().items()}, "launches/sample", sum(v[1] for v in pt.profile().values()) / 50)
+pt.close()
