@@ -218,7 +218,8 @@ def gpu_arm(args):
     pst = pt.stats()
     pt.set_profiling(False)
     # ---- end to end through the public API with host buffers ----
-    img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
+    # every rank ships its own tiles (1/N of the framebuffer, slot order); one rank alone ships the whole image
+    img = torch.empty((H, W, 4) if world == 1 else (pt.num_slots(), 4), dtype=torch.float32, pin_memory=True).numpy()
     inst, tlas = arrays["instances"], arrays["topBvh"]
     pt.reset_stats()
     barrier()
@@ -227,7 +228,10 @@ def gpu_arm(args):
         pt.update_instances(inst, tlas)            # host -> device: instances + TLAS (camera rides in the launch parameters)
         pt.Render(cams[step % 16]); step += 1
         pt.Finish()
-        pt.read_image(0, out=img)                   # device -> host: the accumulated float4 image
+        if world == 1:
+            pt.read_image(0, out=img)               # device -> host: the accumulated float4 image
+        else:
+            pt.read_tiles(0, out=img)               # device -> host: this rank's tiles of it
     barrier()
     e2e_s = time.perf_counter() - t0
     est = pt.stats()
@@ -262,7 +266,7 @@ def gpu_arm(args):
                            "steady_ms_per_step": steady_ms, "steady_mrays_s": rays_per_step / steady_ms / 1e3},
                 "clocks": sampler.summary(),
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(inst.nbytes + tlas.nbytes + 76),
-                        "d2h_bytes_per_step": int(W * H * 16)},
+                        "d2h_bytes_per_step": int(img.nbytes) * world},
                 "gpu_launches": timed_launches,
                 "roofline": {"bound": "hbm", "kernel": "k_trace<false> (extend)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": pst.wave_extend_rays * bytes_per_ext_ray / max(1, ext_n), "bytes_per_ray": bytes_per_ext_ray,

@@ -54,6 +54,9 @@ def load_library():
     L.pt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_finish.argtypes = [C.c_void_p]
     L.pt_join.argtypes = [C.c_void_p]
+    L.pt_read_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    L.pt_tile_num_slots.argtypes = [C.POINTER(abi.Config)]
+    L.pt_tile_num_slots.restype = C.c_uint32
     L.pt_measure_gather_bandwidth.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(C.c_double)]
     L.pt_postprocess.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p]
     L.pt_write_pfm.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
@@ -198,6 +201,17 @@ class Pathtracer:
         out = C.c_double()
         self._ck(self.L.pt_measure_gather_bandwidth(self.h, int(array_bytes), int(access_bytes), int(repeats), C.byref(out)), "pt_measure_gather_bandwidth")
         return out.value
+
+    def num_slots(self):
+        return int(self.L.pt_tile_num_slots(C.byref(self.cfg)))
+
+    def read_tiles(self, which=0, out=None):
+        """This rank's pixels only, (num_slots, 4) float32 in slot order (see tile_pixels()): with N ranks each
+        moves 1/N of the framebuffer."""
+        if out is None:
+            out = np.empty((self.num_slots(), 4), np.float32)
+        self._ck(self.L.pt_read_tiles(self.h, abi.ptr(out), int(which)), "pt_read_tiles")
+        return out
 
     def join(self):
         """Asynchronous: orders every Render enqueued so far before later work on stream() (renders run on

@@ -15,7 +15,7 @@ using namespace ptb;
 
 static thread_local std::string g_createError;
 
-#define PT_MAX_SETS 4
+#define PT_MAX_SETS 8
 struct pt_ctx {
     pt_config cfg;
     std::string err;
@@ -33,10 +33,10 @@ struct pt_ctx {
         cudaEvent_t done = nullptr;       // recorded after the sample's accumulate
         bool doneValid = false;
     } set[PT_MAX_SETS];
-    int nSets = PT_MAX_SETS, cur = 0;
+    int nSets = 4, cur = 0;
     bool forked = false, prevTraining = false;
     cudaEvent_t forkEv = nullptr;
-    float4 *image = nullptr, *albedo = nullptr, *postBuf = nullptr;
+    float4 *image = nullptr, *albedo = nullptr, *postBuf = nullptr, *packBuf = nullptr;
     unsigned long long* stats = nullptr;
     // scene
     DScene sc;
@@ -158,7 +158,7 @@ PT_API void pt_destroy(pt_ctx* ctx) {
         if (S.stream) cudaStreamDestroy(S.stream);
     }
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
-    void* bufs[] = {ctx->image, ctx->albedo, ctx->postBuf, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
+    void* bufs[] = {ctx->image, ctx->albedo, ctx->postBuf, ctx->packBuf, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
     for (void* p : bufs) if (p) cudaFree(p);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -214,6 +214,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         m = makeTileMap(cfg);
         const size_t cap = std::max<uint32_t>(m.nSlots, 1024u);
         int r;
+        ctx->nSets = m.nSlots <= 600000u ? 8 : 4;        // small shards (multi-GPU) are latency bound per launch: more samples in flight
         if ((cfg->flags & PT_FLAG_NO_PIPELINE) || getenv("PTB200_NO_PIPELINE")) ctx->nSets = 1;
         else if (const char* e = getenv("PTB200_SETS")) ctx->nSets = std::min(PT_MAX_SETS, std::max(1, atoi(e)));    // developer knob
         CK(cudaEventCreateWithFlags(&ctx->forkEv, cudaEventDisableTiming));
@@ -478,6 +479,11 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         cudaStream_t s = pipelined ? S.stream : ctx->stream;
         if (pipelined) ctx->cur = (ctx->cur + 1) % ctx->nSets;
         const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots;   // :292
+        // Short queues: a sample that runs alone (clearing / profiled / cache-training frames) spreads its rays over all
+        // warps (latency); samples that overlap others keep their warps full (throughput: 0.41 -> 0.32 ms/sample on a
+        // 1/8-image shard), the other samples in flight fill the machine.
+        ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
+        if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->sc.minWidth = (uint)std::max(1, std::min(32, atoi(e)));   // developer knob
         CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                      // :265 (+ cursors)
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); ctx->launches++, k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
@@ -573,6 +579,22 @@ PT_API int pt_read_image(pt_ctx* ctx, float* host_rgbw, int which) {
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaMemcpyAsync(host_rgbw, which == 0 ? ctx->image : ctx->albedo, (size_t)ctx->map.W * ctx->map.H * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+// This rank's share of the image only: nSlots float4 in slot order (pt_tile_slot_to_pixel maps a slot to its pixel).
+// With N ranks every rank moves 1/N of the framebuffer instead of a full-size image that is zero outside its tiles.
+PT_API int pt_read_tiles(pt_ctx* ctx, float* host_rgbw_slots, int which) {
+    if (!ctx || !host_rgbw_slots) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    const uint32_t n = ctx->map.nSlots;
+    if (n == 0) return PT_OK;
+    if (!ctx->packBuf) CK(cudaMalloc((void**)&ctx->packBuf, (size_t)n * sizeof(float4)));
+    k_pack_tiles<<<n / 256, 256, 0, ctx->stream>>>(ctx->map, which == 0 ? ctx->image : ctx->albedo, ctx->packBuf);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(host_rgbw_slots, ctx->packBuf, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return PT_OK;
 }

@@ -101,6 +101,7 @@ struct DScene {
     float4* rcRadiance;         // 3 x float4 per triangle: radianceCache[8], radianceTotal, pad[3]
     float* rcAdditions;         // SoA [16][num_triangles]: additionCache[8] then additionCacheCount[8]
     uint num_triangles, num_instances, num_spheres, num_planes, num_lights;
+    uint minWidth;              // scheduling: least number of rays a warp claims from a short queue (1..32)
 };
 
 struct DCamera { float3 eye, viewDir, lt, u, v; float d, focalLength, aperture; };

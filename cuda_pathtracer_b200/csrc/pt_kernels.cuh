@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
     const uint n = q.cnt[CNT_EXT(b0)];
     const uint lane = laneId();
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
-    const uint width = min(32u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    const uint width = min(32u, max(max(1u, sc.minWidth), (n + totalWarps - 1u) / totalWarps));
     uint2 stack[PT_STACK];
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
@@ -289,6 +289,12 @@ __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* _
         }
         stats[0] += cnt[CNT_EXT(0)]; stats[1] += ext; stats[2] += sh; stats[3] += ext; stats[4] += 1; stats[5] += wext; stats[6] += wsh;
     }
+}
+// this rank's pixels in slot order (the tile partition): what a rank ships to the host / to rank 0
+__global__ void __launch_bounds__(256) k_pack_tiles(TileMap map, const float4* __restrict__ image, float4* out) {
+    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint x, y;
+    out[slot] = slotToPixel(map, slot, x, y) ? image[x + y * map.W] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 __global__ void k_clear_image(float4* a, float4* b, uint n) {
     const uint i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -309,7 +309,7 @@ template <bool ANY, class IO>
 __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* cursor, const IO io) {
     const uint lane = laneId();
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
-    const uint width = min(32u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    const uint width = min(32u, max(max(1u, sc.minWidth), (n + totalWarps - 1u) / totalWarps));
     const uint refillAt = max(1u, width / PT_REFILL_DIV);
     uint2 stack[PT_STACK];
     LaneState L;

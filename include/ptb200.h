@@ -194,6 +194,7 @@ PT_API int  pt_render(pt_ctx*, const pt_camera*, int should_clear);   /* == Path
 PT_API int  pt_join(pt_ctx*);                                         /* asynchronous: orders every render enqueued so far before later work on pt_cuda_stream() (e.g. a timing event) */
 PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
 PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
+PT_API int  pt_read_tiles(pt_ctx*, float* host_rgbw_slots, int which);  /* this rank's pixels only: pt_tile_num_slots() float4 in slot order (multi-GPU: 1/N of the image per rank) */
 PT_API int  pt_write_pfm(pt_ctx*, const char* path, int which);        /* headless render-to-PFM (display value rgb / w, main.cpp:58-62) in place of the GLFW window */
 /* Display post-process (main.cpp:46-171,316-376: demodulated separable Gaussian, remodulate, gamma 2, vignette) as CUDA
  * kernels; host float4 in (or NULL, NULL = the context's accumulators), host float4 RGBA out. */

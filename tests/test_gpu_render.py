@@ -170,6 +170,28 @@ def test_tile_sharded_ranks_reproduce_single_gpu_image(sibenik_small):
         assert sum(p[2].extend_rays for p in parts) == st1.extend_rays and sum(p[2].shadow_rays for p in parts) == st1.shadow_rays
 
 
+def test_read_tiles_is_the_ranks_share_of_the_image(sibenik_small):
+    """pt_read_tiles: slot-ordered pixels of one rank == the rank's full-size image at pt_tile_slot_to_pixel positions."""
+    import ctypes as C
+    cfg = abi.default_config(200, 120, max_ray_depth=3, interactive_depth=1, rank=1, world_size=3)
+    pt = api.Pathtracer(sibenik_small, cfg).Init()
+    cam = scenes.camera_sweep("sibenik", 200, 120, 16)[4]
+    pt.Render(cam, shouldClear=True); pt.Render(cam); pt.Finish()
+    full, tiles = pt.read_image(), pt.read_tiles()
+    assert tiles.shape == (pt.num_slots(), 4)
+    x, y = C.c_uint32(), C.c_uint32()
+    inside = 0
+    for slot in range(0, pt.num_slots(), 7):
+        r = pt.L.pt_tile_slot_to_pixel(C.byref(cfg), slot, C.byref(x), C.byref(y))
+        if r == 1:
+            inside += 1
+            assert np.array_equal(tiles[slot], full[y.value, x.value])
+        else:
+            assert not tiles[slot].any()
+    assert inside > 100 and full[..., 3].sum() == tiles[..., 3].sum()
+    pt.close()
+
+
 def test_guiding_additions_shard_and_sum(sibenik_small):
     """The all-reduce payload: per-rank radiance-cache additions of a tile-sharded frame, summed over ranks, equal
     the single-rank additions of the same frame (counts exactly, energies up to float-atomic order).  The hook is
