@@ -105,6 +105,28 @@ def cpu_leg(scene_arrays, threads, samples=1):
 
 
 
+def reference_gpu_leg(rays_per_sample, frames=40):
+    """The reference's OWN device path (src/pathtracer.h + kernels.h, unmodified, built for sm_100a with the reference's
+    flags, oracle/_ref/refgpu_shipped_1920x1080x8) on this GPU: the same scene/camera/depth, NEE + guiding, 100 training
+    frames then `frames` timed converge samples with one Finish per frame as src/main.cpp:308-319 does."""
+    import tempfile
+    from oracle import refgpu
+    exe = refgpu.binary_path("shipped", W, H, DEPTH)
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/refgpu_shipped_%dx%dx%d not built (needs /root/reference at build time)" % (W, H, DEPTH)}
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            sp = refgpu.sibenik_spec(tmp)
+            cam = camera_for(0, W, H)
+            sp.camera = (tuple(float(x) for x in np.ravel(cam["eye"])[:3]), tuple(float(x) for x in np.ravel(cam["viewDir"])[:3]), 1.5, 5.0, 0.01)
+            blue = (np.random.default_rng(3).random((64, 64)) > 0.5).astype(np.uint8) * 255
+            _, _, ms, _ = refgpu.run_reference(exe, sp, tmp, W, H, 1, 100, True, True, blue, timed_frames=frames, timeout=900)
+        return {"ms_per_sample": ms, "samples_per_s": 1e3 / ms, "mrays_s": rays_per_sample / ms / 1e3, "timed_samples": frames,
+                "what": "reference src/pathtracer.h + src/kernels.h unmodified, nvcc --use_fast_math -O3 (CMakeLists.txt:21-25) for sm_100a, GL interop -> plain cudaArray; camera 0 of the sweep; Mrays/s uses this run's rays per sample"}
+    except Exception as e:                       # a baseline leg must never take the bench line down
+        return {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:300])}
+
+
 def reference_arm(args):
     """--impl reference: the CPU implementation of the path (the oracle port of the reference's kernels,
     kind "port": the reference has no CPU build of kernel_shade/connect) on all host cores."""
@@ -243,6 +265,7 @@ def gpu_arm(args):
     e2e_value = float(e2[0].item()) / float(e2[1].item()) / 1e6
     if rank == 0:
         l2_16, l2_32 = pt.measure_gather_bandwidth(32 << 20, 16), pt.measure_gather_bandwidth(32 << 20, 32)     # L2 gather ceiling
+        ref_gpu = reference_gpu_leg(total_rays / args.steps)
         peak, peak_src = read_peaks()
         cpu_v, per_ray, cpu_s, cpu_rays = cpu_leg(arrays, os.cpu_count() or 1, CPU_SAMPLES)
         # ALGORITHMIC bytes of one extend launch: per ray 32 (RayPacked R) + 16 (HitInfoPacked W)
@@ -275,6 +298,7 @@ def gpu_arm(args):
                              "frac_of_l2_gather_peak": achieved / l2_32 if l2_32 else None,
                              "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray on the reference BVH2); HBM copy peak is the stated denominator, the L2 gather rate the second ceiling; ncu (profiles/) shows the kernel instruction-issue bound (issue active ~67%, 13-26 of 32 lanes per instruction), not bandwidth bound"},
                 "stage_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
+                "reference_on_this_gpu": ref_gpu,
                 "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": "oracle/pt_oracle.cpp: %d converge samples of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_SAMPLES, CPU_W, CPU_H, cpu_rays, cpu_s)}}
         print(json.dumps(line), flush=True)

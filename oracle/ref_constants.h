@@ -15,6 +15,9 @@
 #define NR_PIXELS (WINDOW_WIDTH * WINDOW_HEIGHT)
 #define EPS 0.001f
 #define PI 3.14159265358979323846f
-#define MAX_RAY_DEPTH 32
+#ifndef REF_DEPTH
+#define REF_DEPTH 32
+#endif
+#define MAX_RAY_DEPTH REF_DEPTH
 #define MAX_CACHE_DEPTH 3
 #endif
