@@ -77,3 +77,35 @@ def test_frame_loop_matches_reference_device_kernels(tmp_path, nee, cache, frame
     assert err <= tol
     assert close > 0.995          # measured on B200: 0.9999 / 0.9998 / 0.9992 (rel RMSE 4e-6 / 4e-4 / 3e-4)
     assert abs(float(a.mean()) / float(b.mean()) - 1.0) < 0.01                                       # same energy
+
+
+BIN_FULL = refgpu.binary_path("exact", 1920, 1080, 8)
+
+
+@pytest.mark.skipif(not os.path.exists(BIN_FULL), reason="oracle/_ref/refgpu_exact_1920x1080x8 not built")
+@pytest.mark.parametrize("cache,frames,tol", [(False, 6, 2e-3), (True, 12, 1e-2)])
+def test_full_size_bench_workload_matches_reference_device_kernels(tmp_path, cache, frames, tol):
+    """BASELINE.json configs[2] at FULL size (sibenik-proxy 158k triangles + spheres + emissive cube, 1920x1080, depth 8,
+    NEE on): product (4 samples in flight, k_trace_pair, k_tail) vs the reference's device kernels, same seeds."""
+    sp = refgpu.sibenik_spec(str(tmp_path))
+    cam0 = scenes.camera_sweep("sibenik", 1920, 1080, 16)[0]
+    sp.camera = (tuple(float(x) for x in np.ravel(cam0["eye"])[:3]), tuple(float(x) for x in np.ravel(cam0["viewDir"])[:3]), 1.5, 5.0, 0.01)
+    blue = (np.random.default_rng(3).random((64, 64)) > 0.5).astype(np.uint8) * 255
+    lum_r, alb_r, _, _ = refgpu.run_reference(BIN_FULL, sp, str(tmp_path), 1920, 1080, 1, frames, True, cache, blue)
+    cfg = abi.default_config(1920, 1080, max_ray_depth=8, interactive_depth=1)
+    pt = api.Pathtracer(sp.build_ours(), cfg).Init()
+    pt.set_skydome(np.ones((32, 64, 4), np.float32)); pt.set_blue_noise((blue // 255).astype(np.float32))
+    pt.HNEE, pt.HCACHE = True, cache
+    cam = sp.camera_ours(1920, 1080)
+    pt.Render(cam, shouldClear=True)
+    for _ in range(frames):
+        pt.Render(cam)
+    pt.Finish()
+    lum_g = pt.read_image(); st = pt.stats()
+    pt.close()
+    assert np.array_equal(lum_r[..., 3], lum_g[..., 3]) and st.samples == frames + 1 and st.primary_rays == (frames + 1) * 1920 * 1080
+    a, b = lum_g[..., :3] / lum_g[..., 3:4], lum_r[..., :3] / lum_r[..., 3:4]
+    err = rel_rmse(a, b)
+    close = np.mean(np.all(np.abs(a - b) <= 1e-4 * (1.0 + np.abs(b)), axis=-1))
+    print("full size cache=%s: rel RMSE %.4g, pixels equal to 1e-4: %.5f" % (cache, err, close))
+    assert err <= tol and close > 0.99
