@@ -10,6 +10,6 @@ python bench.py --steps 100 --warmup 5 > gpurun_out/${TAG}_bench.json 2> gpurun_
 python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu list exit $?"
-ncu --set full --clock-control none --import-source on -k "regex:k_trace|k_tail" -s 23 -c 7 -o gpurun_out/${TAG}_trace -f python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k "regex:k_trace|k_tail" -s 17 -c 5 -o gpurun_out/${TAG}_trace -f python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu2.log 2>&1
 echo "ncu full exit $?"
 ls -la gpurun_out

@@ -10,7 +10,7 @@ for v in "" "$@"; do
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
-        d=json.loads(l); print(json.dumps({k:d[k] for k in ('value','ms_per_step','stage_ms_per_step')})); print(json.dumps(d['e2e']), d['roofline']['frac'])
+        d=json.loads(l); print(json.dumps({k:d[k] for k in ('value','ms_per_step','stage_ms_per_step')})); print('steady', d['phases']['steady_mrays_s'], 'e2e', d['e2e']['value'])
     else: print(l.rstrip()[:300])
 " | tee -a gpurun_out/${TAG}_tune.log
 done
