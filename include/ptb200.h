@@ -151,9 +151,10 @@ typedef struct {
     uint32_t flags;                    /* PT_FLAG_* */
 } pt_config;
 #define PT_FLAG_DEFAULT 0u
-/* Scheduling only (results are identical): bounces >= the tail bounce run as ONE per-path launch instead of
- * three wavefront launches per bounce.  Default tail bounce: 3.  PT_FLAG_TAIL_BOUNCE(n) overrides it,
- * PT_FLAG_WAVEFRONT_ONLY keeps every bounce in the wavefront. */
+/* Scheduling only (results are identical): in a sample that runs alone (clearing, cache-training frames) bounces >= the
+ * tail bounce (default 3) run as ONE per-path launch instead of wavefront launches per bounce; samples that overlap
+ * others stay wavefront.  PT_FLAG_TAIL_BOUNCE(n) forces the per-path launch from bounce n for every sample,
+ * PT_FLAG_WAVEFRONT_ONLY keeps every bounce of every sample in the wavefront. */
 #define PT_FLAG_WAVEFRONT_ONLY 1u
 /* Converge samples normally rotate through four working sets on private streams (samples k+1.. start while the
  * short-queue end of sample k drains); results are identical.  This flag keeps one sample in flight. */
