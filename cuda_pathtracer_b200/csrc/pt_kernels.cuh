@@ -38,6 +38,24 @@ __device__ __forceinline__ uint warpAppend(bool pred, uint* counter) {
     return base + __popc(m & ((1u << laneId()) - 1u));
 }
 
+// One atomic per BLOCK (<= 8 warps): warps take consecutive ranges in warp order.  Must be called by every thread of the
+// block; `sm` = 9 uints of shared memory, reusable after the call returns.
+__device__ __forceinline__ uint blockAppend(bool pred, uint* counter, uint* sm) {
+    const uint m = __ballot_sync(0xffffffffu, pred);
+    const uint w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (laneId() == 0) sm[w] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint total = 0;
+        for (uint i = 0; i < nw; i++) { const uint c = sm[i]; sm[i] = total; total += c; }
+        sm[8] = total ? atomicAdd(counter, total) : 0u;
+    }
+    __syncthreads();
+    const uint idx = sm[8] + sm[w] + __popc(m & ((1u << laneId()) - 1u));
+    __syncthreads();
+    return idx;
+}
+
 // ---- primary rays: types.h:641-658 (Camera::getRay), 669-676 (distort) ----------------------------------
 __device__ __forceinline__ float3 camDistort(const DCamera& c, float3 p) {
     float3 center = c.eye + c.d * c.viewDir;
@@ -74,7 +92,9 @@ __global__ void __launch_bounds__(256) k_primary(DCamera cam, TileMap map, uint 
         uint seed = getSeed(x, y, randIdx, map.W);
         camGetRay(cam, x, y, seed, map.W, map.H, o, d);
     }
-    const uint idx = warpAppend(valid, q.cnt + CNT_EXT(0));
+    // one atomic per 256-thread block: 65k same-address atomics per 1080p frame were this kernel's critical path
+    __shared__ uint sm[9];
+    const uint idx = blockAppend(valid, q.cnt + CNT_EXT(0), sm);
     if (valid) {
         q.rayO[0][idx] = make_float4(o.x, o.y, o.z, 9999999.0f);
         q.rayD[0][idx] = make_float4(d.x, d.y, d.z, __uint_as_float(slot));
@@ -136,13 +156,12 @@ __global__ void k_prepare_lights(DScene sc) {
 #endif
 __global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P, Queues q, int inBuf) {
     const uint n = q.cnt[CNT_EXT(P.bounce)];
-    const uint warpsTotal = (gridDim.x * blockDim.x) >> 5;
-    const uint warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint lane = laneId();
     const float4* rayO = q.rayO[inBuf]; const float4* rayD = q.rayD[inBuf];
     float4* outO = q.rayO[inBuf ^ 1]; float4* outD = q.rayD[inBuf ^ 1];
-    for (uint base = warp * 32u; base < n; base += warpsTotal * 32u) {
-        const uint i = base + lane;
+    __shared__ uint sm[9];
+    const uint nRound = (n + blockDim.x - 1u) / blockDim.x * blockDim.x;          // block-uniform trip count (blockAppend synchronises)
+    for (uint base = blockIdx.x * blockDim.x; base < nRound; base += gridDim.x * blockDim.x) {
+        const uint i = base + threadIdx.x;
         ShadeOut so; so.pushExt = so.pushShadow = false;
         uint slot = 0;
         if (i < n) {
@@ -151,12 +170,12 @@ __global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P
             Hit h; h.type = __float_as_uint(h4.x); h.id = __float_as_uint(h4.y); h.inst = __float_as_uint(h4.z); h.t = h4.w;
             shadeOne(P, f3(o4), f3(d4), slot, h, so);
         }
-        const uint si = warpAppend(so.pushShadow, q.cnt + CNT_SHADOW(P.bounce));
+        const uint si = blockAppend(so.pushShadow, q.cnt + CNT_SHADOW(P.bounce), sm);
         if (so.pushShadow) {
             q.shO[si] = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
             q.shD[si] = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
         }
-        const uint ei = warpAppend(so.pushExt, q.cnt + CNT_EXT(P.bounce + 1));
+        const uint ei = blockAppend(so.pushExt, q.cnt + CNT_EXT(P.bounce + 1), sm);
         if (so.pushExt) {
             outO[ei] = make_float4(so.ext.o.x, so.ext.o.y, so.ext.o.z, so.ext.len);
             outD[ei] = make_float4(so.ext.d.x, so.ext.d.y, so.ext.d.z, __uint_as_float(slot));
