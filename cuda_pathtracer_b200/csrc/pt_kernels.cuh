@@ -115,8 +115,11 @@ __global__ void k_primary_debug(DCamera cam, uint W, uint H, uint randIdx, pt_ra
 // ---- extend / connect ---------------------------------------------------------------------------------------
 // Persistent warps running the flat two-level traversal with dynamic ray fetch (pt_trace.cuh traceLoop).
 // count/cursor are device-side: the host never reads queue sizes (reference README.md:201).
+#ifndef PT_TRACE_MINBLOCKS
+#define PT_TRACE_MINBLOCKS 8
+#endif
 template <bool ANY>
-__global__ void __launch_bounds__(128) k_trace(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+__global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
                                                const float4* __restrict__ lights, float4* accucolors) {
     QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors;
@@ -127,7 +130,7 @@ __global__ void __launch_bounds__(128) k_trace(DScene sc, const float4* __restri
 // other writes (hits vs accucolors), so the dependent-launch chain per bounce is shade -> trace instead of
 // shade -> connect -> extend.  Warps drain the extension queue first, then the shadow queue fills the gaps its
 // stragglers leave.  (The per-stage profiling pass launches them separately to time them apart.)
-__global__ void __launch_bounds__(128, 8) k_trace_pair(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+__global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                                                     const uint* __restrict__ extCount, uint* extCursor, float4* __restrict__ hits,
                                                     const float4* __restrict__ shO, const float4* __restrict__ shD,
                                                     const uint* __restrict__ shCount, uint* shCursor,
