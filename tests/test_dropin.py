@@ -69,3 +69,42 @@ def test_reference_host_code_renders_through_the_adapter(tmp_path):
     err = float(np.sqrt(np.mean((img.astype(np.float64) - ref) ** 2)) / np.sqrt(np.mean(ref.astype(np.float64) ** 2)))
     assert err <= 2e-2, err
     ora.close()
+
+
+EXAMPLE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "examples", "render_pfm")
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(EXAMPLE), reason="examples/render_pfm not built")
+def test_cpp_only_headless_render_to_pfm(tmp_path):
+    """examples/render_pfm.cpp: the C ABI from plain C++ (pts_* scene code + pt_* render path), PFM out; the same scene
+    through the Python mirror must give the identical picture (guiding off would be bit-exact; it is on by default,
+    so float atomics leave ~1e-9)."""
+    from cuda_pathtracer_b200 import api
+    obj = _mesh(tmp_path)
+    out = str(tmp_path / "cpp.pfm")
+    r = subprocess.run([EXAMPLE, obj, out, "160", "120", "5", "8", "1", "0"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    img = read_pfm(out)
+    s = Scene()
+    white = s.addMaterial(material((0.7, 0.7, 0.7)))
+    lamp = s.addMaterial(material((1, 1, 1), emission=(12, 12, 12)))
+    m = s.addModel(obj, 1.0, (0, 0, 0), (0, 0, 0), white, False)
+    s.addObject(m)
+    s.addObject(m, material=lamp, position=(0, 7, 0), scale=(0.3, 0.3, 0.3))
+    s.addPlane((0, -1, 0), -3, white)
+    cfg = abi.default_config(160, 120, max_ray_depth=8, interactive_depth=1)
+    pt = api.Pathtracer(s.finalize(), cfg).Init()
+    eye = np.array([1.0, 3.0, -8.0]); d = np.array([0.0, 1.0, 0.0]) - eye
+    cam = make_camera(tuple(eye), d / np.float32(np.sqrt(np.float32(d @ d))), 1.5, 5.0, 0.01, 160, 120)
+    pt.Render(cam, shouldClear=True)
+    for _ in range(5):
+        pt.Render(cam)
+    pt.Finish()
+    ref = pt.read_image(); ref = ref[..., :3] / ref[..., 3:4]
+    pt.close()
+    err = float(np.sqrt(np.mean((img.astype(np.float64) - ref) ** 2)) / np.sqrt(np.mean(ref.astype(np.float64) ** 2)))
+    assert err < 1e-3, err
+    # and with the display pass
+    r = subprocess.run([EXAMPLE, obj, out, "160", "120", "5", "8", "1", "1"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and np.isfinite(read_pfm(out)).mean() > 0.99
