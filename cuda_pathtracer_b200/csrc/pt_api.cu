@@ -31,7 +31,8 @@ struct pt_ctx {
         pt_sample_cache* sampleCache = nullptr;
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;       // recorded after the sample's accumulate
-        bool doneValid = false;
+        cudaEvent_t tailStart = nullptr;  // recorded right before the sample's k_tail launch
+        bool doneValid = false, tailValid = false;
     } set[PT_MAX_SETS];
     int nSets = 4, cur = 0;
     bool forked = false, prevTraining = false;
@@ -118,8 +119,10 @@ static int devUpload(pt_ctx* ctx, T** p, const T* host, size_t n, bool sceneOwne
 // enqueued so far before whatever comes next on the context's public stream (pt_cuda_stream()).
 static int joinStreams(pt_ctx* ctx) {
     if (!ctx->forked) return PT_OK;
-    for (auto& S : ctx->set)
+    for (auto& S : ctx->set) {
         if (S.doneValid) { CK(cudaStreamWaitEvent(ctx->stream, S.done, 0)); S.doneValid = false; }
+        S.tailValid = false;
+    }
     ctx->forked = false;
     return PT_OK;
 }
@@ -156,6 +159,7 @@ PT_API void pt_destroy(pt_ctx* ctx) {
                       S.masks, S.accucolors, S.lights, S.albedoSample, &S == &ctx->set[0] ? S.sampleCache : nullptr};
         for (void* p : sb) if (p) cudaFree(p);
         if (S.done) cudaEventDestroy(S.done);
+        if (S.tailStart) cudaEventDestroy(S.tailStart);
         if (S.stream) cudaStreamDestroy(S.stream);
     }
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
@@ -223,6 +227,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
             pt_ctx::SampleSet& S = ctx->set[k];
             CK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
             CK(cudaEventCreateWithFlags(&S.done, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&S.tailStart, cudaEventDisableTiming));
             for (int i = 0; i < 2; i++) {
                 if ((r = devAlloc(ctx, &S.q.rayO[i], cap, false))) return r;
                 if ((r = devAlloc(ctx, &S.q.rayD[i], cap, false))) return r;
@@ -485,6 +490,10 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // 1/8-image shard), the other samples in flight fill the machine.
         ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
         if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->sc.minWidth = (uint)std::max(1, std::min(32, atoi(e)));   // developer knob
+        // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
+        // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
+        // of competing with the previous sample's wide launches.
+        if (pipelined && (training || ctx->prevTraining) && other.tailValid && !getenv("PTB200_NO_TAIL_WAIT")) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
         CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                      // :265 (+ cursors)
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); ctx->launches++, k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
@@ -531,7 +540,9 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             ctx->randIdx++;                                                                // :283
             if (connects && (!fuse || bounce + 1 == waveBounces)) launchConnect(bounce);
         }
+        S.tailValid = false;
         if (max_bounces > waveBounces) {                                                   // the same bounces, one launch (k_tail)
+            if (pipelined) { CK(cudaEventRecord(S.tailStart, s)); S.tailValid = true; }
             StageTimer tm(ctx, PT_STAGE_TAIL, s);
             ctx->launches++, k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
                                                  S.q.cnt + CUR_EXT(waveBounces));
