@@ -44,6 +44,8 @@ def load_library():
     L.pt_destroy.argtypes = [C.c_void_p]
     L.pt_destroy.restype = None
     L.pt_upload_scene.argtypes = [C.c_void_p, C.POINTER(abi.SceneDesc)]
+    L.pt_build_bvh.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
+    L.pt_build_bvh_last_error.restype = C.c_char_p
     L.pt_update_instances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
     L.pt_set_toggles.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.pt_set_skydome.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -290,3 +292,24 @@ class Pathtracer:
             self.close()
         except Exception:
             pass
+
+
+def build_bvh(triangles, tri_offset=0, device=0):
+    """createBVHBinned (reference src/bvhBuilder.h:35-274) on the GPU: `triangles` = abi.TRIANGLE_V records (or an (n, 9)
+    float array).  Returns (nodes [abi.BVH_NODE], order [uint32: input index per output position], device_ms, levels).
+    The caller permutes its TriangleV / TriangleD arrays with `order` (permuteTriangles, bvhBuilder.h:17-27)."""
+    L = load_library()
+    if not (isinstance(triangles, np.ndarray) and triangles.dtype == abi.TRIANGLE_V):
+        v = np.ascontiguousarray(triangles, np.float32).reshape(-1, 9)
+        t = np.zeros(len(v), abi.TRIANGLE_V)
+        t["v0"], t["v1"], t["v2"] = v[:, 0:3], v[:, 3:6], v[:, 6:9]
+        triangles = t
+    triangles = np.ascontiguousarray(triangles)
+    n = len(triangles)
+    nodes = np.zeros(max(1, 2 * n - 1), abi.BVH_NODE)
+    order = np.zeros(n, np.uint32)
+    used, levels, ms = C.c_uint32(), C.c_uint32(), C.c_float()
+    r = L.pt_build_bvh(int(device), abi.ptr(triangles), n, int(tri_offset), abi.ptr(nodes), C.byref(used), abi.ptr(order), C.byref(ms), C.byref(levels))
+    if r != 0:
+        raise PtError("pt_build_bvh failed (%d): %s" % (r, (L.pt_build_bvh_last_error() or b"").decode()))
+    return nodes[:used.value].copy(), order, ms.value, levels.value

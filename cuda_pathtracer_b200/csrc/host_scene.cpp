@@ -311,6 +311,7 @@ struct SceneImpl {
     std::vector<pt_plane> planes;
     std::string err;
     double lastBuildMs = 0;
+    int buildDevice = -1;       // >= 0: BVH2 built by pt_build_bvh on that GPU
     bool finalized = false;
 };
 
@@ -321,7 +322,19 @@ int finishModel(SceneImpl& s, uint start, uint n) {
     pt_model m; memset(&m, 0, sizeof(m));
     m.triangleStart = start; m.nrTriangles = n;
     const double t0 = nowMs();
-    s.bvhs.push_back(buildBinnedSAH(s.verts.data() + start, s.vdata.data() + start, n, start));
+    if (s.buildDevice >= 0) {
+        std::vector<pt_bvh_node> nodes(n ? 2 * (size_t)n - 1 : 1);
+        std::vector<uint> order(n);
+        uint used = 0;
+        const int r = pt_build_bvh(s.buildDevice, s.verts.data() + start, n, start, nodes.data(), &used, order.data(), nullptr, nullptr);
+        if (r != PT_OK) { s.err = std::string("device BVH build failed: ") + pt_build_bvh_last_error(); s.verts.resize(start); s.vdata.resize(start); return r; }
+        std::vector<pt_triangle_v> tv2(s.verts.begin() + start, s.verts.end()); std::vector<pt_triangle_d> td2(s.vdata.begin() + start, s.vdata.end());
+        for (uint i = 0; i < n; i++) { s.verts[start + i] = tv2[order[i]]; s.vdata[start + i] = td2[order[i]]; }    // permuteTriangles, bvhBuilder.h:17-27
+        nodes.resize(used);
+        s.bvhs.push_back(std::move(nodes));
+    } else {
+        s.bvhs.push_back(buildBinnedSAH(s.verts.data() + start, s.vdata.data() + start, n, start));
+    }
     s.lastBuildMs = nowMs() - t0;
     m.nrBvhNodes = (uint)s.bvhs.back().size();
     s.models.push_back(m);
@@ -571,6 +584,7 @@ PT_API pts_scene* pts_scene_new(void) { return new pts_scene(); }
 PT_API void pts_scene_free(pts_scene* h) { delete h; }
 PT_API const char* pts_last_error(const pts_scene* h) { return h ? h->s.err.c_str() : ""; }
 PT_API double pts_last_build_ms(const pts_scene* h) { return h ? h->s.lastBuildMs : 0.0; }
+PT_API void pts_set_build_device(pts_scene* h, int device) { if (h) h->s.buildDevice = device; }
 
 PT_API uint32_t pts_add_material(pts_scene* h, const pt_material* m) {      // Scene::addMaterial, scene.h:140-144
     h->s.materials.push_back(*m); h->s.texNames.push_back(""); h->s.normalTexNames.push_back("");

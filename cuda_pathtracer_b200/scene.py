@@ -27,6 +27,8 @@ def _bind(L):
     L.pts_last_error.argtypes = [C.c_void_p]
     L.pts_last_build_ms.restype = C.c_double
     L.pts_last_build_ms.argtypes = [C.c_void_p]
+    L.pts_set_build_device.argtypes = [C.c_void_p, C.c_int]
+    L.pts_set_build_device.restype = None
     L.pts_add_material.argtypes = [C.c_void_p, C.c_void_p]
     L.pts_add_material.restype = C.c_uint32
     L.pts_set_material.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
@@ -127,6 +129,11 @@ class Scene:
 
     def update(self):
         self._ck(self.L.pts_update(self.h), "pts_update")
+
+    def set_build_device(self, device):
+        """device >= 0: models added from now on get their BVH2 from pt_build_bvh on that GPU; -1: host builder."""
+        self.L.pts_set_build_device(self.h, int(device))
+        return self
 
     def last_build_ms(self):
         return float(self.L.pts_last_build_ms(self.h))

@@ -203,6 +203,15 @@ PT_API int  pt_postprocess(pt_ctx*, const float* lum_host, const float* albedo_h
 /* Roofline helper: measured GB/s of random 16/32-byte reads over an array of `array_bytes` (L2-resident when it fits). */
 PT_API int  pt_measure_gather_bandwidth(pt_ctx*, uint64_t array_bytes, uint32_t access_bytes, uint32_t repeats, double* out_gbs);
 PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
+/* createBVHBinned (bvhBuilder.h:35-274: 16-bin SAH, leaf <= 4 triangles, two-pointer partition, pre-order node ids) built
+ * on the device, level by level; same nodes, same triangle order and same node numbering as the reference's host build
+ * (a box may differ in the SIGN of a zero coordinate).  tris: n host TriangleV records; nodes: room for max(1, 2n-1);
+ * order[i] = input index of the triangle that ends up at position i (apply it to the TriangleV / TriangleD arrays ==
+ * permuteTriangles, bvhBuilder.h:17-27).  device_ms (optional): device time of the build without the copies;
+ * levels (optional): tree levels processed.  No CPU fallback: PT_ERR_NO_DEVICE without a GPU. */
+PT_API int  pt_build_bvh(int device, const pt_triangle_v* tris, uint32_t n, uint32_t tri_offset, pt_bvh_node* nodes, uint32_t* n_nodes,
+                         uint32_t* order, float* device_ms, uint32_t* levels);
+PT_API const char* pt_build_bvh_last_error(void);
 /* Per-stage device time, CUDA events around every stage launch on the context's stream; resolved by pt_finish. */
 #define PT_STAGE_EXTEND 0
 #define PT_STAGE_SHADE 1

@@ -19,6 +19,9 @@ PT_API pts_scene* pts_scene_new(void);
 PT_API void pts_scene_free(pts_scene*);
 PT_API const char* pts_last_error(const pts_scene*);
 PT_API double pts_last_build_ms(const pts_scene*);                /* wall time of the last BVH2 build */
+/* Where models added from now on get their BVH2 built: device >= 0 -> pt_build_bvh on that GPU (same tree),
+ * -1 (default) -> the host builder.  A failed device build fails the add_model call; it never falls back silently. */
+PT_API void pts_set_build_device(pts_scene*, int device);
 
 PT_API uint32_t pts_add_material(pts_scene*, const pt_material*);  /* Scene::addMaterial, scene.h:140-144 */
 PT_API int pts_set_material(pts_scene*, uint32_t idx, const pt_material*);

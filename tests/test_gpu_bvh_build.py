@@ -1,0 +1,119 @@
+"""Device BVH2 build (pt_build_bvh) against the host builder, which the CPU suite pins against the
+reference's createBVHBinned (tests/test_cpu_host_scene.py): same nodes, same triangle order, same node numbering.
+Integer fields are compared bit for bit; box floats by value (a zero may differ in sign, see bvh_build.cu)."""
+import numpy as np
+import pytest
+
+from cuda_pathtracer_b200 import abi, api, scenes
+from cuda_pathtracer_b200.scene import Scene, material
+
+pytestmark = pytest.mark.gpu
+
+
+def host_and_device(verts):
+    out = []
+    for dev in (-1, 0):
+        s = Scene().set_build_device(dev)
+        s.addMaterial(material())
+        s.addModelSoup(verts)
+        s.addObject(0)
+        s.finalize()
+        out.append((s.arrays(), s.last_build_ms()))
+    return out
+
+
+def assert_same_tree(h, d):
+    hb, db = h["bvh"][0], d["bvh"][0]
+    assert len(hb) == len(db), (len(hb), len(db))
+    for f in ("first", "count"):
+        bad = np.nonzero(hb[f] != db[f])[0]
+        assert len(bad) == 0, "%s differs at node %d of %d: host %s device %s" % (f, bad[0], len(hb), hb[bad[0]], db[bad[0]])
+    for f in ("vmin", "vmax"):
+        bad = np.nonzero((hb[f] != db[f]).any(axis=1))[0]
+        assert len(bad) == 0, "%s differs at node %d: host %s device %s" % (f, bad[0], hb[bad[0]], db[bad[0]])
+    for f in ("v0", "v1", "v2"):
+        bad = np.nonzero((h["vertices"][f] != d["vertices"][f]).any(axis=1))[0]
+        assert len(bad) == 0, "triangle order differs first at position %d of %d" % (bad[0], len(h["vertices"]))
+    for f in h["vertexData"].dtype.names:                       # field by field: the structs carry padding bytes
+        assert h["vertexData"][f].tobytes() == d["vertexData"][f].tobytes(), f
+    assert np.array_equal(h["models"]["nrBvhNodes"], d["models"]["nrBvhNodes"])
+    for f in h["topBvh"].dtype.names:
+        assert np.array_equal(h["topBvh"][f], d["topBvh"][f]), f
+
+
+def _random_soup(n, spread, size, seed=11):
+    rng = np.random.default_rng(seed)
+    return (rng.random((n, 1, 3), np.float32) * spread + (rng.random((n, 3, 3), np.float32) - 0.5) * size).reshape(-1, 9)
+
+
+def _coplanar_grid():                      # coplanar, many SAH ties, zero coordinates
+    g = np.stack(np.meshgrid(np.arange(64, dtype=np.float32), np.arange(64, dtype=np.float32), indexing="ij"), -1).reshape(-1, 2)
+    flat = np.zeros((len(g), 9), np.float32)
+    flat[:, 0], flat[:, 2] = g[:, 0], g[:, 1]
+    flat[:, 3], flat[:, 5] = g[:, 0] + 1, g[:, 1]
+    flat[:, 6], flat[:, 8] = g[:, 0], g[:, 1] + 1
+    return flat
+
+
+SOUPS = {
+    "random-soup-20k": lambda: _random_soup(20000, 10, 1.0),
+    "cathedral": scenes.cathedral_soup,
+    "statue": scenes.statue_soup,
+    "cube": scenes.cube_soup,
+    "heightfield-200x201": lambda: scenes.heightfield_soup(200, 201),
+    "voxel-terrain-64": lambda: scenes.voxel_terrain_soup(64)[0],
+    "identical-x40": lambda: np.tile(np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32), (40, 1)),     # centroid extent 0: one big leaf
+    "coplanar-grid-4096": _coplanar_grid,
+    "random-soup-300k": lambda: _random_soup(300000, 50, 0.3),
+}
+for _n in (1, 2, 4, 5, 6, 9, 17):
+    SOUPS["tiny-%d" % _n] = (lambda n: (lambda: _random_soup(n, 4, 1.0, seed=n)))(_n)
+
+
+@pytest.mark.parametrize("name", list(SOUPS))
+def test_device_build_equals_host_build(name):
+    verts = np.ascontiguousarray(SOUPS[name](), np.float32).reshape(-1, 9)
+    (h, hms), (d, dms) = host_and_device(verts)
+    assert_same_tree(h, d)
+
+
+def test_raw_entry_point_order_and_offsets():
+    """pt_build_bvh itself: `order` is a permutation, leaves tile [offset, offset+n) in order, inner nodes point at adjacent
+    children handed out in pre-order (bvhBuilder.h:222-223)."""
+    v = scenes.statue_soup().reshape(-1, 9)
+    nodes, order, ms, levels = api.build_bvh(v, tri_offset=1000)
+    n = len(v)
+    assert sorted(order.tolist()) == list(range(n)) and levels > 3 and ms > 0
+    leaves = nodes[nodes["count"] > 0]
+    assert int(leaves["count"].sum()) == n and int(leaves["first"].min()) == 1000 and int((leaves["first"] + leaves["count"]).max()) == 1000 + n
+    inner = nodes[nodes["count"] == 0]
+    assert len(nodes) == 2 * len(inner) + 1
+    assert np.array_equal(np.sort(inner["first"]), 1 + 2 * np.arange(len(inner), dtype=np.uint32))
+    # every triangle of a leaf lies inside the leaf's box
+    t = np.zeros(n, abi.TRIANGLE_V); t["v0"], t["v1"], t["v2"] = v[:, 0:3], v[:, 3:6], v[:, 6:9]
+    t = t[order]
+    for leaf in leaves[:: max(1, len(leaves) // 200)]:
+        tri = t[leaf["first"] - 1000: leaf["first"] - 1000 + leaf["count"]]
+        pts = np.concatenate([tri["v0"], tri["v1"], tri["v2"]])
+        assert (pts >= leaf["vmin"]).all() and (pts <= leaf["vmax"]).all()
+
+
+def test_render_with_device_built_scene_is_bit_identical():
+    """The whole path on a device-built tree: same image as with the host-built tree."""
+    imgs = []
+    for dev in (-1, 0):
+        s = Scene().set_build_device(dev)
+        s.addMaterial(material(diffuse=(0.7, 0.6, 0.5)))
+        s.addModelSoup(scenes.statue_soup())
+        s.addObject(0)
+        s.finalize()
+        cfg = abi.default_config(160, 120, max_ray_depth=4, interactive_depth=1)
+        pt = api.Pathtracer(s.arrays(), cfg).Init()
+        cam = scenes.camera_sweep("sibenik", 160, 120, 4)[0]
+        pt.Render(cam, shouldClear=True)
+        for _ in range(4):
+            pt.Render(cam)
+        pt.Finish()
+        imgs.append(pt.read_image())
+        pt.close()
+    assert imgs[0].tobytes() == imgs[1].tobytes()
