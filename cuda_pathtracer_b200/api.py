@@ -46,6 +46,7 @@ def load_library():
     L.pt_upload_scene.argtypes = [C.c_void_p, C.POINTER(abi.SceneDesc)]
     L.pt_build_bvh.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
     L.pt_build_bvh_last_error.restype = C.c_char_p
+    L.pt_debug_read_wide_bvh.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint32)]
     L.pt_update_instances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
     L.pt_set_toggles.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.pt_set_skydome.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -206,6 +207,14 @@ class Pathtracer:
 
     def num_slots(self):
         return int(self.L.pt_tile_num_slots(C.byref(self.cfg)))
+
+    def debug_read_wide_bvh(self):
+        """(nodes [n, 20] uint32, triangle records [m, 12] uint32) of the 8-wide BVH as it sits on the device."""
+        nn, nt = C.c_uint32(), C.c_uint32()
+        self._ck(self.L.pt_debug_read_wide_bvh(self.h, None, C.byref(nn), None, C.byref(nt)), "pt_debug_read_wide_bvh")
+        nodes, tris = np.zeros((nn.value, 20), np.uint32), np.zeros((nt.value, 12), np.uint32)
+        self._ck(self.L.pt_debug_read_wide_bvh(self.h, abi.ptr(nodes), None, abi.ptr(tris), None), "pt_debug_read_wide_bvh")
+        return nodes, tris
 
     def read_tiles(self, which=0, out=None):
         """This rank's pixels only, (num_slots, 4) float32 in slot order (see tile_pixels()): with N ranks each

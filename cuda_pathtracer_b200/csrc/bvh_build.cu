@@ -320,10 +320,20 @@ __global__ void k_emit(uint total, Nodes N, const uint* newId, uint triOffset, f
 thread_local char g_buildErr[512] = "";
 #define BCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { snprintf(g_buildErr, sizeof g_buildErr, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); rc = e_ == cudaErrorMemoryAllocation ? PT_ERR_OOM : PT_ERR_CUDA; goto done; } } while (0)
 
-struct DevMem {                 // everything freed on every exit path
-    void* p[32]; int n = 0;
-    template <typename T> cudaError_t get(T** out, size_t count) { cudaError_t e = cudaMalloc((void**)out, std::max<size_t>(count, 1) * sizeof(T)); if (e == cudaSuccess) p[n++] = *out; return e; }
-    ~DevMem() { for (int i = 0; i < n; i++) cudaFree(p[i]); }
+struct DevMem {                 // one device allocation carved into 256-byte aligned pieces; freed on every exit path
+    struct Want { void** out; size_t bytes; };
+    Want want[40]; int n = 0; void* base = nullptr;
+    template <typename T> void add(T** out, size_t count) { want[n++] = Want{(void**)out, (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~(size_t)255}; }
+    cudaError_t commit() {
+        size_t total = 0;
+        for (int i = 0; i < n; i++) total += want[i].bytes;
+        const cudaError_t e = cudaMalloc(&base, total);
+        if (e != cudaSuccess) return e;
+        size_t off = 0;
+        for (int i = 0; i < n; i++) { *want[i].out = (char*)base + off; off += want[i].bytes; }
+        return cudaSuccess;
+    }
+    ~DevMem() { if (base) cudaFree(base); }
 };
 
 }  // namespace
@@ -358,16 +368,17 @@ PT_API int pt_build_bvh(int device, const pt_triangle_v* tris, uint32_t n, uint3
     BCK(cudaSetDevice(device));
     BCK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     BCK(cudaEventCreate(&e0)); BCK(cudaEventCreate(&e1));
-    BCK(mem.get(&dTv, 3 * (size_t)n)); BCK(mem.get(&cen, n)); BCK(mem.get(&tbLo, n)); BCK(mem.get(&tbHi, n)); BCK(mem.get(&out, 2 * (size_t)cap));
-    BCK(mem.get(&ord, n)); BCK(mem.get(&posNode, n)); BCK(mem.get(&rootKeys, 6)); BCK(mem.get(&counter, 1)); BCK(mem.get(&scratch, (size_t)maxSlots * BB_SCRATCH));
-    BCK(mem.get(&listL, n)); BCK(mem.get(&vals, cap)); BCK(mem.get(&valsSorted, cap)); BCK(mem.get(&newId, cap)); BCK(mem.get(&binOf, n));
-    BCK(mem.get(&flags, (size_t)n + 1)); BCK(mem.get(&scan, (size_t)n + 1)); BCK(mem.get(&keys, cap)); BCK(mem.get(&keysSorted, cap));
-    BCK(mem.get(&N.start, cap)); BCK(mem.get(&N.count, cap)); BCK(mem.get(&N.child, cap)); BCK(mem.get(&N.state, cap)); BCK(mem.get(&N.left, cap));
-    BCK(mem.get(&N.axis, cap)); BCK(mem.get(&N.bmin, cap)); BCK(mem.get(&N.binFac, cap)); BCK(mem.get(&N.split, cap)); BCK(mem.get(&N.lo, cap)); BCK(mem.get(&N.hi, cap));
+    mem.add(&dTv, 3 * (size_t)n); mem.add(&cen, n); mem.add(&tbLo, n); mem.add(&tbHi, n); mem.add(&out, 2 * (size_t)cap);
+    mem.add(&ord, n); mem.add(&posNode, n); mem.add(&rootKeys, 6); mem.add(&counter, 1); mem.add(&scratch, (size_t)maxSlots * BB_SCRATCH);
+    mem.add(&listL, n); mem.add(&vals, cap); mem.add(&valsSorted, cap); mem.add(&newId, cap); mem.add(&binOf, n);
+    mem.add(&flags, (size_t)n + 1); mem.add(&scan, (size_t)n + 1); mem.add(&keys, cap); mem.add(&keysSorted, cap);
+    mem.add(&N.start, cap); mem.add(&N.count, cap); mem.add(&N.child, cap); mem.add(&N.state, cap); mem.add(&N.left, cap);
+    mem.add(&N.axis, cap); mem.add(&N.bmin, cap); mem.add(&N.binFac, cap); mem.add(&N.split, cap); mem.add(&N.lo, cap); mem.add(&N.hi, cap);
+    flags = scan = keys = keysSorted = nullptr; vals = valsSorted = nullptr;      // cub only sizes its temporary storage in these calls
     BCK(cub::DeviceScan::ExclusiveSum(nullptr, tmpScan, flags, scan, (int)(n + 1), st));
     BCK(cub::DeviceRadixSort::SortPairs(nullptr, tmpSort, keys, keysSorted, vals, valsSorted, (int)cap, 0, 64, st));
     tmpBytes = std::max(tmpScan, tmpSort);
-    { unsigned char* t8; BCK(mem.get(&t8, tmpBytes)); tmp = t8; }
+    { unsigned char* t8 = nullptr; mem.add(&t8, tmpBytes); BCK(mem.commit()); tmp = t8; }
     if (n) BCK(cudaMemcpyAsync(dTv, tris, (size_t)n * sizeof(pt_triangle_v), cudaMemcpyHostToDevice, st));
     BCK(cudaMemcpyAsync(rootKeys, hostRootKeys, sizeof hostRootKeys, cudaMemcpyHostToDevice, st));
     BCK(cudaEventRecord(e0, st));

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <chrono>
 #include "pt_kernels.cuh"
 #include "pt_post.cuh"
 #include "wide_bvh.h"
@@ -43,7 +44,7 @@ struct pt_ctx {
     DScene sc;
     bool haveScene = false;
     std::vector<void*> sceneAllocs;
-    uint32_t numInstancesCap = 0, numTlasCap = 0, maxWideDepth = 0;
+    uint32_t numInstancesCap = 0, numTlasCap = 0, maxWideDepth = 0, numWideNodes = 0, numWideTris = 0;
     // textures
     FrameTex tex;
     std::vector<cudaArray_t> arrays;
@@ -364,8 +365,24 @@ static uint32_t tlasDepth(const pt_tlas_node* n, uint32_t count, uint32_t idx, u
     return std::max(tlasDepth(n, count, n[idx].children & 0xffffu, depth + 1), tlasDepth(n, count, (n[idx].children >> 16) & 0xffffu, depth + 1));
 }
 
+// Test hook: the wide BVH as it sits on the device (80-byte nodes, 48-byte triangle records).  NULL pointers: sizes only.
+PT_API int pt_debug_read_wide_bvh(pt_ctx* ctx, void* nodes, uint32_t* n_nodes, void* tris, uint32_t* n_tris) {
+    if (!ctx || !ctx->haveScene) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (n_nodes) *n_nodes = ctx->numWideNodes;
+    if (n_tris) *n_tris = ctx->numWideTris;
+    if (nodes && ctx->numWideNodes) CK(cudaMemcpy(nodes, ctx->sc.nodes, (size_t)ctx->numWideNodes * sizeof(WideNode), cudaMemcpyDeviceToHost));
+    if (tris && ctx->numWideTris) CK(cudaMemcpy(tris, ctx->sc.wtris, (size_t)ctx->numWideTris * sizeof(WideTri), cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+static double wallMs() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     if (!ctx || !d) return PT_ERR_INVALID;
+    const bool timing = getenv("PTB200_TIMING") != nullptr;          // developer knob: phase wall times on stderr
+    double tPhase = wallMs();
+    auto phase = [&](const char* what) { if (timing) { cudaStreamSynchronize(ctx->stream); const double t = wallMs(); fprintf(stderr, "[pt_upload_scene] %-28s %8.2f ms\n", what, t - tPhase); tPhase = t; } };
     if (d->num_models == 0 && d->num_instances > 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instances without models");
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
@@ -375,18 +392,62 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     ctx->haveScene = false;
     DScene& sc = ctx->sc;
     memset(&sc, 0, sizeof(sc));
-    // wide BVH per model (host), one node array / one triangle-record array for the whole scene
+    // Wide BVH per model, one node array / one triangle-record array for the whole scene.  Built on the device from
+    // the uploaded BVH2 (wide_bvh_device.cu); PT_FLAG_HOST_WIDE_BVH / PTB200_HOST_WIDE_BVH selects the host converter
+    // (wide_bvh.cpp), which produces the same bytes and is what the device converter is tested against.
     std::vector<WideNode> nodes; std::vector<WideTri> wtris; std::vector<DModel> models(d->num_models);
     uint32_t maxWide = 0;
-    for (uint32_t m = 0; m < d->num_models; m++) {
-        const pt_model& pm = d->models[m];
-        if (!pm.bvh || pm.nrBvhNodes == 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: model without BVH");
-        WideBuildStats st;
-        models[m].rootNode = buildWideBVH(pm.bvh, pm.nrBvhNodes, d->vertices, nodes, wtris, &st);
-        models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;
-        maxWide = std::max(maxWide, st.max_depth);
-        if (st.tris != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
+    const bool hostWide = (ctx->cfg.flags & PT_FLAG_HOST_WIDE_BVH) || getenv("PTB200_HOST_WIDE_BVH");
+    float4 *dn = nullptr, *dt = nullptr; pt_triangle_v* dv = nullptr;
+    int r;
+    for (uint32_t m = 0; m < d->num_models; m++)
+        if (!d->models[m].bvh || d->models[m].nrBvhNodes == 0) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: model without BVH");
+    if ((r = devUpload(ctx, &dv, d->vertices, d->num_triangles, true))) return r;
+    phase("vertices H2D");
+    ctx->numWideNodes = ctx->numWideTris = 0;
+    if (hostWide) {
+        for (uint32_t m = 0; m < d->num_models; m++) {
+            const pt_model& pm = d->models[m];
+            WideBuildStats st;
+            models[m].rootNode = buildWideBVH(pm.bvh, pm.nrBvhNodes, d->vertices, nodes, wtris, &st);
+            models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;
+            maxWide = std::max(maxWide, st.max_depth);
+            if (st.tris != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
+        }
+        if ((r = devUpload(ctx, (WideNode**)&dn, nodes.data(), nodes.size(), true))) return r;
+        if ((r = devUpload(ctx, (WideTri**)&dt, wtris.data(), wtris.size(), true))) return r;
+        ctx->numWideNodes = (uint32_t)nodes.size(); ctx->numWideTris = (uint32_t)wtris.size();
+    } else {
+        size_t nodeCap = 0, maxBound = 0, maxBvh2 = 0, triCap = 0;
+        for (uint32_t m = 0; m < d->num_models; m++) {
+            const size_t b = wideNodeBound(d->models[m].nrBvhNodes, d->models[m].nrTriangles);
+            nodeCap += b; maxBound = std::max(maxBound, b); maxBvh2 = std::max<size_t>(maxBvh2, d->models[m].nrBvhNodes); triCap += d->models[m].nrTriangles;
+        }
+        const size_t tmpBytes = wideScanTempBytes(maxBound + 1);
+        struct Scratch { std::vector<void*> p; ~Scratch() { for (void* q : p) cudaFree(q); } } scratch;
+        auto scratchAlloc = [&](void** out, size_t bytes) { cudaError_t e = cudaMalloc(out, std::max<size_t>(bytes, 256)); if (e == cudaSuccess) scratch.p.push_back(*out); return e; };
+        void *tmpNodes, *refs, *counts, *scan, *tmp, *dBvh2;
+        CK(scratchAlloc(&tmpNodes, nodeCap * sizeof(WideNode))); CK(scratchAlloc(&refs, maxBound * 8)); CK(scratchAlloc(&counts, (maxBound + 1) * 8));
+        CK(scratchAlloc(&scan, (maxBound + 1) * 8)); CK(scratchAlloc(&tmp, tmpBytes)); CK(scratchAlloc(&dBvh2, maxBvh2 * sizeof(pt_bvh_node)));
+        if ((r = devAlloc(ctx, (WideTri**)&dt, triCap, true))) return r;
+        uint32_t nodeCursor = 0, triCursor = 0;
+        for (uint32_t m = 0; m < d->num_models; m++) {
+            const pt_model& pm = d->models[m];
+            CK(cudaMemcpyAsync(dBvh2, pm.bvh, (size_t)pm.nrBvhNodes * sizeof(pt_bvh_node), cudaMemcpyHostToDevice, ctx->stream));
+            uint32_t nUsed = 0, tUsed = 0, depth = 0; const char* err = "";
+            r = buildWideBVHDevice(ctx->stream, (const pt_bvh_node*)dBvh2, pm.nrBvhNodes, dv, (WideNode*)tmpNodes, nodeCursor, (WideTri*)dt, triCursor,
+                                   refs, counts, scan, tmp, tmpBytes, &nUsed, &tUsed, &depth, &err);
+            if (r) return fail(ctx, r, err);
+            if (tUsed != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
+            models[m].rootNode = nodeCursor; models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;
+            nodeCursor += nUsed; triCursor += tUsed; maxWide = std::max(maxWide, depth);
+        }
+        if ((r = devAlloc(ctx, (WideNode**)&dn, nodeCursor, true))) return r;
+        CK(cudaMemcpyAsync(dn, tmpNodes, (size_t)nodeCursor * sizeof(WideNode), cudaMemcpyDeviceToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->numWideNodes = nodeCursor; ctx->numWideTris = triCursor;
     }
+    phase(hostWide ? "wide BVH (host) + H2D" : "wide BVH (device)");
     for (uint32_t i = 0; i < d->num_instances; i++)
         if (d->instances[i].model_id >= d->num_models) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instance model_id out of range");
     // unified traversal stack: TLAS entries below the node groups of the instance being traversed
@@ -406,12 +467,9 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
             lights.push_back(pt_triangle_light{t, i});
         }
     }
-    int r;
-    float4 *dn, *dt; pt_triangle_v* dv; pt_triangle_d* dd; pt_material* dm; pt_instance* di; pt_tlas_node* dl; DModel* dmo;
+    phase("light scan (host)");
+    pt_triangle_d* dd; pt_material* dm; pt_instance* di; pt_tlas_node* dl; DModel* dmo;
     pt_sphere* ds; pt_plane* dp; pt_triangle_light* dli;
-    if ((r = devUpload(ctx, (WideNode**)&dn, nodes.data(), nodes.size(), true))) return r;
-    if ((r = devUpload(ctx, (WideTri**)&dt, wtris.data(), wtris.size(), true))) return r;
-    if ((r = devUpload(ctx, &dv, d->vertices, d->num_triangles, true))) return r;
     if ((r = devUpload(ctx, &dd, d->vertexData, d->num_triangles, true))) return r;
     if ((r = devUpload(ctx, &dm, d->materials, d->num_materials, true))) return r;
     if ((r = devUpload(ctx, &di, d->instances, d->num_instances, true))) return r;
@@ -423,6 +481,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     if ((r = devAlloc(ctx, &sc.lightTab, lights.size() * PT_LIGHT_STRIDE, true))) return r;
     if ((r = devAlloc(ctx, &sc.rcRadiance, (size_t)d->num_triangles * 3, true))) return r;
     if ((r = devAlloc(ctx, &sc.rcAdditions, (size_t)d->num_triangles * 16, true))) return r;
+    phase("other H2D + allocations");
     sc.nodes = dn; sc.wtris = dt; sc.vertices = dv; sc.vertexData = dd; sc.materials = dm; sc.instances = di; sc.tlas = dl;
     sc.models = dmo; sc.spheres = ds; sc.planes = dp; sc.lights = dli;
     sc.num_triangles = d->num_triangles; sc.num_instances = d->num_instances; sc.num_spheres = d->num_spheres;
@@ -434,6 +493,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     }
     if (sc.num_lights) { k_prepare_lights<<<(sc.num_lights + 127) / 128, 128, 0, ctx->stream>>>(sc); CK(cudaGetLastError()); }
     CK(cudaStreamSynchronize(ctx->stream));      // host vectors above go out of scope
+    phase("cache init + light table");
     ctx->haveScene = true;
     return (int)lights.size();
 }

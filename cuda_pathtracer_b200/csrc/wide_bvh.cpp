@@ -128,7 +128,9 @@ uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangl
         uint32_t ebyte[3]; float scale[3];
         for (int a = 0; a < 3; a++) {
             float ext = r.box.hi[a] - r.box.lo[a];
-            int e = ext > 0.0f ? (int)std::ceil(std::log2(ext / 255.0f)) : -126;
+            // e = ceil(log2(ext / 255)), from the float's own exponent (exact; the device converter does the same)
+            int e = -126;
+            if (ext > 0.0f) { int ex; const float m = std::frexp(ext / 255.0f, &ex); e = m == 0.5f ? ex - 1 : ex; }
             e = std::max(-126, std::min(127, e));
             // make sure ceil((hi-lo)/2^e) <= 255 despite rounding
             while (e < 127 && std::ceil(ext / std::ldexp(1.0f, e)) > 255.0f) e++;

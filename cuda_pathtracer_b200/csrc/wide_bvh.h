@@ -35,5 +35,15 @@ struct WideBuildStats { uint32_t nodes, leaves, tris, max_depth; double sah_cost
 uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangle_v* triangles /* global array */,
                       std::vector<WideNode>& nodes, std::vector<WideTri>& tris, WideBuildStats* stats);
 
+
+// The same conversion on the device (wide_bvh_device.cu); byte-identical output.  Pointers are device pointers.
+size_t wideNodeBound(uint32_t n_bvh2, uint32_t n_tris);
+size_t wideScanTempBytes(size_t maxItems);
+#ifdef __CUDACC__
+int buildWideBVHDevice(cudaStream_t st, const pt_bvh_node* d_bvh2, uint32_t n_bvh2, const pt_triangle_v* d_tris, WideNode* d_nodes, uint32_t nodeBase,
+                       WideTri* d_wtris, uint32_t triBase, void* refsScratch, void* countsScratch, void* scanScratch, void* tmp, size_t tmpBytes,
+                       uint32_t* nodesUsed, uint32_t* trisUsed, uint32_t* maxDepth, const char** err);
+#endif
+
 }  // namespace ptb
 #endif

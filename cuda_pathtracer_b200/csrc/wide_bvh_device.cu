@@ -1,0 +1,221 @@
+// wide_bvh_device.cu -- BVH2 -> 8-wide compressed BVH on the device ("output feeds the
+// wide-BVH converter directly").  Same node format, same collapse / slot / quantisation rules and the same
+// breadth-first numbering as the host converter in wide_bvh.cpp, so the two produce byte-identical arrays
+// (tests/test_gpu_bvh_build.py compares them).  One thread builds one wide node; a level of wide nodes is one
+// launch pair (count, then emit) with a prefix sum in between that hands out child-node and triangle-record
+// indices in the host converter's queue order.  Compiled with -fmad=false like the rest of the library.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <algorithm>
+#include <cub/device/device_scan.cuh>
+#include "wide_bvh.h"
+
+namespace ptb {
+namespace {
+
+typedef unsigned int uint;
+typedef unsigned long long u64;
+#define WB_THREADS 128
+
+// A node of the temporary binary tree of wide_bvh.cpp, by reference: b == 0 -> BVH2 node a; b > 0 -> the triangle
+// range [a, a + b) of a BVH2 leaf that was cut down to <= 3 triangles per leaf.
+struct TRef { uint a, b; };
+struct TInfo {
+    float lo[3], hi[3];
+    TRef self, left, right;
+    uint first, count;
+    bool internal;
+};
+
+__device__ __forceinline__ float stdmin(float a, float b) { return (b < a) ? b : a; }     // std::min / std::max operand rules
+__device__ __forceinline__ float stdmax(float a, float b) { return (a < b) ? b : a; }
+
+__device__ void rangeBounds(const pt_triangle_v* tris, uint first, uint count, float* lo, float* hi) {
+    for (int a = 0; a < 3; a++) { lo[a] = 3.0e38f; hi[a] = -3.0e38f; }
+    for (uint i = first; i < first + count; i++) {
+        const float* p = &tris[i].v0.x;                                                     // v0, v1, v2 are contiguous
+        for (int v = 0; v < 3; v++)
+            for (int a = 0; a < 3; a++) { lo[a] = stdmin(lo[a], p[3 * v + a]); hi[a] = stdmax(hi[a], p[3 * v + a]); }
+    }
+}
+
+__device__ void loadRef(const float4* bvh2, const pt_triangle_v* tris, TRef r, TInfo& t) {
+    t.self = r;
+    if (r.b == 0) {
+        const float4 lo = bvh2[2 * (size_t)r.a], hi = bvh2[2 * (size_t)r.a + 1];
+        t.lo[0] = lo.x; t.lo[1] = lo.y; t.lo[2] = lo.z; t.hi[0] = hi.x; t.hi[1] = hi.y; t.hi[2] = hi.z;
+        t.first = __float_as_uint(lo.w); t.count = __float_as_uint(hi.w);
+        if (t.count == 0) { t.internal = true; t.left = TRef{t.first, 0}; t.right = TRef{t.first + 1, 0}; return; }
+    } else {
+        t.first = r.a; t.count = r.b;
+        rangeBounds(tris, r.a, r.b, t.lo, t.hi);
+    }
+    t.internal = t.count > 3;
+    if (t.internal) { const uint lc = t.count / 2; t.left = TRef{t.first, lc}; t.right = TRef{t.first + lc, t.count - lc}; }
+}
+
+__device__ __forceinline__ float boxArea(const TInfo& t) {
+    const float x = t.hi[0] - t.lo[0], y = t.hi[1] - t.lo[1], z = t.hi[2] - t.lo[2];
+    return (x < 0 || y < 0 || z < 0) ? 0.0f : 2.0f * (x * y + x * z + y * z);
+}
+
+// collapse + slot assignment of one wide node (wide_bvh.cpp "collapse" and "assign children to slots")
+struct Collapsed { TInfo root; TInfo ch[8]; int childIn[8]; int nch; };
+
+__device__ void collapse(const float4* bvh2, const pt_triangle_v* tris, TRef ref, Collapsed& c) {
+    loadRef(bvh2, tris, ref, c.root);
+    c.nch = 0;
+    if (!c.root.internal) c.ch[c.nch++] = c.root;                      // degenerate model: the root itself is a leaf
+    else { loadRef(bvh2, tris, c.root.left, c.ch[0]); loadRef(bvh2, tris, c.root.right, c.ch[1]); c.nch = 2; }
+    while (c.nch < 8) {
+        int best = -1; float bestArea = -1.0f;
+        for (int i = 0; i < c.nch; i++)
+            if (c.ch[i].internal) { const float a = boxArea(c.ch[i]); if (a > bestArea) { bestArea = a; best = i; } }
+        if (best < 0) break;
+        const TRef l = c.ch[best].left, r = c.ch[best].right;
+        loadRef(bvh2, tris, l, c.ch[best]); loadRef(bvh2, tris, r, c.ch[c.nch++]);
+    }
+    float ctr[3];
+    for (int a = 0; a < 3; a++) ctr[a] = 0.5f * (c.root.lo[a] + c.root.hi[a]);
+    float cost[8][8];
+    for (int i = 0; i < c.nch; i++) {
+        float d[3];
+        for (int a = 0; a < 3; a++) d[a] = 0.5f * (c.ch[i].lo[a] + c.ch[i].hi[a]) - ctr[a];
+        for (int s = 0; s < 8; s++) {
+            const float sx = (s & 4) ? 1.0f : -1.0f, sy = (s & 2) ? 1.0f : -1.0f, sz = (s & 1) ? 1.0f : -1.0f;
+            cost[i][s] = d[0] * sx + d[1] * sy + d[2] * sz;
+        }
+    }
+    int slotOf[8];
+    for (int i = 0; i < 8; i++) { slotOf[i] = -1; c.childIn[i] = -1; }
+    for (int k = 0; k < c.nch; k++) {
+        int bi = -1, bs = -1; float bc = -3.0e38f;
+        for (int i = 0; i < c.nch; i++) if (slotOf[i] < 0)
+            for (int s = 0; s < 8; s++) if (c.childIn[s] < 0 && cost[i][s] > bc) { bc = cost[i][s]; bi = i; bs = s; }
+        slotOf[bi] = bs; c.childIn[bs] = bi;
+    }
+}
+
+// pass 1 of a level: how many internal children / leaf triangles each wide node will emit
+__global__ void __launch_bounds__(WB_THREADS) k_wide_count(const float4* bvh2, const pt_triangle_v* tris, const TRef* refs, uint levelBegin, uint levelSize, u64* counts) {
+    const uint i = blockIdx.x * WB_THREADS + threadIdx.x;
+    if (i > levelSize) return;
+    if (i == levelSize) { counts[i] = 0; return; }
+    Collapsed c;
+    collapse(bvh2, tris, refs[levelBegin + i], c);
+    uint nInternal = 0, nTris = 0;
+    for (int s = 0; s < 8; s++) {
+        if (c.childIn[s] < 0) continue;
+        const TInfo& cn = c.ch[c.childIn[s]];
+        if (cn.internal) nInternal++; else nTris += cn.count;
+    }
+    counts[i] = ((u64)nInternal << 32) | nTris;
+}
+
+// pass 2: write the node, its triangle records and the references of its internal children
+__global__ void __launch_bounds__(WB_THREADS) k_wide_emit(const float4* bvh2, const pt_triangle_v* tris, TRef* refs, uint levelBegin, uint levelSize, const u64* scan,
+                                                           uint nodeBase, uint triCursor, WideNode* nodes, WideTri* wtris) {
+    const uint i = blockIdx.x * WB_THREADS + threadIdx.x;
+    if (i >= levelSize) return;
+    Collapsed c;
+    collapse(bvh2, tris, refs[levelBegin + i], c);
+    const TInfo& r = c.root;
+    uint ebyte[3]; float scale[3];
+    for (int a = 0; a < 3; a++) {                                                           // quantisation frame
+        const float ext = r.hi[a] - r.lo[a];
+        int e = -126;
+        if (ext > 0.0f) { int ex; const float m = frexpf(ext / 255.0f, &ex); e = m == 0.5f ? ex - 1 : ex; }
+        e = max(-126, min(127, e));
+        while (e < 127 && ceilf(ext / __uint_as_float((uint)(e + 127) << 23)) > 255.0f) e++;
+        ebyte[a] = (uint)(e + 127);
+        scale[a] = __uint_as_float((uint)(e + 127) << 23);                                  // ldexp(1, e), e >= -126
+    }
+    uint w[20];
+    for (int k = 0; k < 20; k++) w[k] = 0;
+    unsigned char* bytes = (unsigned char*)w;
+    const uint nextLevelBegin = levelBegin + levelSize;                                     // local index of the first node of the next level
+    const uint childLocal = nextLevelBegin + (uint)(scan[i] >> 32);
+    const uint triBase = triCursor + (uint)(scan[i] & 0xffffffffull);
+    uint imask = 0, nInternal = 0, triOffset = 0;
+    for (int s = 0; s < 8; s++) {
+        if (c.childIn[s] < 0) continue;
+        const TInfo& cn = c.ch[c.childIn[s]];
+        unsigned char meta;
+        if (cn.internal) {
+            imask |= 1u << s; meta = (unsigned char)(0x20 | (24 + s));
+            refs[childLocal + nInternal] = cn.self;
+            nInternal++;
+        } else {
+            const unsigned char unary[4] = {0, 1, 3, 7};
+            meta = (unsigned char)((unary[cn.count] << 5) | triOffset);
+            for (uint t = cn.first; t < cn.first + cn.count; t++) {
+                const pt_triangle_v tv = tris[t];
+                WideTri wt;
+                wt.v0[0] = tv.v0.x; wt.v0[1] = tv.v0.y; wt.v0[2] = tv.v0.z; wt.id = t;
+                wt.e1[0] = tv.v1.x - tv.v0.x; wt.e1[1] = tv.v1.y - tv.v0.y; wt.e1[2] = tv.v1.z - tv.v0.z; wt.pad1 = 0;   // kernels.h:171
+                wt.e2[0] = tv.v2.x - tv.v0.x; wt.e2[1] = tv.v2.y - tv.v0.y; wt.e2[2] = tv.v2.z - tv.v0.z; wt.pad2 = 0;   // kernels.h:172
+                wtris[triBase + triOffset + (t - cn.first)] = wt;
+            }
+            triOffset += cn.count;
+        }
+        bytes[24 + s] = meta;
+        for (int a = 0; a < 3; a++) {
+            float qlo = floorf((cn.lo[a] - r.lo[a]) / scale[a]);
+            float qhi = ceilf((cn.hi[a] - r.lo[a]) / scale[a]);
+            while (qlo > 0.0f && r.lo[a] + qlo * scale[a] > cn.lo[a]) qlo -= 1.0f;
+            while (qhi < 255.0f && r.lo[a] + qhi * scale[a] < cn.hi[a]) qhi += 1.0f;
+            qlo = stdmax(0.0f, stdmin(255.0f, qlo)); qhi = stdmax(0.0f, stdmin(255.0f, qhi));
+            bytes[32 + a * 8 + s] = (unsigned char)qlo;
+            bytes[56 + a * 8 + s] = (unsigned char)qhi;
+        }
+    }
+    w[0] = __float_as_uint(r.lo[0]); w[1] = __float_as_uint(r.lo[1]); w[2] = __float_as_uint(r.lo[2]);
+    w[3] = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
+    w[4] = nodeBase + childLocal; w[5] = triBase;
+    uint4* dst = (uint4*)(nodes + nodeBase + levelBegin + i);
+    for (int k = 0; k < 5; k++) dst[k] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+}
+
+}  // namespace
+
+// Upper bound on the wide nodes of one model: every wide node is an internal node of the temporary binary tree.
+size_t wideNodeBound(uint32_t n_bvh2, uint32_t n_tris) { return (size_t)(n_bvh2 / 2) + n_tris + 2; }
+
+// Appends one model's wide BVH to device arrays.  d_bvh2 / d_tris are device pointers (d_tris = the scene's whole
+// TriangleV array in reference order); nodes are written at nodes[nodeBase ...], triangle records at wtris[triBase ...].
+// `refs` (wideNodeBound entries of 8 bytes), `counts` and `scan` (wideNodeBound + 1 u64 each) and `tmp` are scratch.
+int buildWideBVHDevice(cudaStream_t st, const pt_bvh_node* d_bvh2, uint32_t n_bvh2, const pt_triangle_v* d_tris, WideNode* d_nodes, uint32_t nodeBase,
+                       WideTri* d_wtris, uint32_t triBase, void* refsScratch, void* countsScratch, void* scanScratch, void* tmp, size_t tmpBytes,
+                       uint32_t* nodesUsed, uint32_t* trisUsed, uint32_t* maxDepth, const char** err) {
+    (void)n_bvh2;
+    TRef* refs = (TRef*)refsScratch; u64* counts = (u64*)countsScratch; u64* scan = (u64*)scanScratch;
+    const TRef root{0, 0};
+    cudaError_t e;
+#define WCK(call) do { e = (call); if (e != cudaSuccess) { *err = cudaGetErrorString(e); return PT_ERR_CUDA; } } while (0)
+    WCK(cudaMemcpyAsync(refs, &root, sizeof root, cudaMemcpyHostToDevice, st));
+    uint levelBegin = 0, levelSize = 1, triCursor = triBase, depth = 0;
+    while (levelSize) {
+        const uint grid1 = (levelSize + 1 + WB_THREADS - 1) / WB_THREADS, grid = (levelSize + WB_THREADS - 1) / WB_THREADS;
+        k_wide_count<<<grid1, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, refs, levelBegin, levelSize, counts);
+        size_t need = tmpBytes;
+        WCK(cub::DeviceScan::ExclusiveSum(tmp, need, counts, scan, (int)(levelSize + 1), st));
+        k_wide_emit<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, refs, levelBegin, levelSize, scan, nodeBase, triCursor, d_nodes, d_wtris);
+        u64 totals = 0;
+        WCK(cudaMemcpyAsync(&totals, scan + levelSize, sizeof totals, cudaMemcpyDeviceToHost, st));
+        WCK(cudaStreamSynchronize(st));
+        levelBegin += levelSize; levelSize = (uint)(totals >> 32); triCursor += (uint)(totals & 0xffffffffull); depth++;
+    }
+    WCK(cudaGetLastError());
+#undef WCK
+    *nodesUsed = levelBegin; *trisUsed = triCursor - triBase; *maxDepth = depth;
+    return PT_OK;
+}
+
+size_t wideScanTempBytes(size_t maxItems) {
+    size_t bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, bytes, (u64*)nullptr, (u64*)nullptr, (int)maxItems);
+    return bytes;
+}
+
+}  // namespace ptb

@@ -160,6 +160,9 @@ typedef struct {
  * short-queue end of sample k drains); results are identical.  This flag keeps one sample in flight. */
 #define PT_FLAG_NO_PIPELINE 2u
 #define PT_FLAG_TAIL_BOUNCE(n) ((((uint32_t)(n) + 1u) & 0xffu) << 8)
+/* pt_upload_scene converts the BVH2 to the 8-wide layout on the device; this flag selects the host converter instead
+ * (same bytes; kept as the checker of the device converter). */
+#define PT_FLAG_HOST_WIDE_BVH 4u
 
 typedef struct {                       /* device-side ray counters since the last pt_reset_stats */
     uint64_t primary_rays, extend_rays, shadow_rays, shade_calls, samples;
@@ -212,6 +215,8 @@ PT_API int  pt_read_radiance_cache(pt_ctx*, pt_radiance_cache* host_out);
 PT_API int  pt_build_bvh(int device, const pt_triangle_v* tris, uint32_t n, uint32_t tri_offset, pt_bvh_node* nodes, uint32_t* n_nodes,
                          uint32_t* order, float* device_ms, uint32_t* levels);
 PT_API const char* pt_build_bvh_last_error(void);
+/* Test hook: the 8-wide BVH as it sits on the device (80-byte nodes, 48-byte triangle records); NULL pointers: sizes only. */
+PT_API int  pt_debug_read_wide_bvh(pt_ctx*, void* nodes, uint32_t* n_nodes, void* tris, uint32_t* n_tris);
 /* Per-stage device time, CUDA events around every stage launch on the context's stream; resolved by pt_finish. */
 #define PT_STAGE_EXTEND 0
 #define PT_STAGE_SHADE 1

@@ -117,3 +117,31 @@ def test_render_with_device_built_scene_is_bit_identical():
         imgs.append(pt.read_image())
         pt.close()
     assert imgs[0].tobytes() == imgs[1].tobytes()
+
+
+WIDE_CASES = ["cube", "statue", "cathedral", "identical-x40", "coplanar-grid-4096", "tiny-1", "tiny-4", "tiny-5", "tiny-17", "heightfield-200x201", "random-soup-300k"]
+
+
+@pytest.mark.parametrize("name", WIDE_CASES)
+def test_device_wide_bvh_equals_host_converter(name):
+    """BVH2 -> 8-wide conversion on the device (default of pt_upload_scene) against the host converter
+    (PT_FLAG_HOST_WIDE_BVH): byte-identical node and triangle-record arrays."""
+    verts = np.ascontiguousarray(SOUPS[name](), np.float32).reshape(-1, 9)
+    s = Scene()
+    s.addMaterial(material())
+    s.addModelSoup(verts)
+    s.addModelSoup(scenes.cube_soup())                      # a second model: node / triangle bases are absolute
+    s.addObject(0)
+    s.addObject(1, position=(3, 0, 0))
+    s.finalize()
+    out = []
+    for flags in (abi.FLAG_HOST_WIDE_BVH, 0):
+        pt = api.Pathtracer(s.arrays(), abi.default_config(64, 64, max_ray_depth=2, interactive_depth=1, flags=flags)).Init()
+        out.append(pt.debug_read_wide_bvh())
+        pt.close()
+    (hn, ht), (dn, dt) = out
+    assert hn.shape == dn.shape and ht.shape == dt.shape, (hn.shape, dn.shape, ht.shape, dt.shape)
+    bad = np.nonzero((hn != dn).any(axis=1))[0]
+    assert len(bad) == 0, "wide node %d of %d differs: host %s device %s" % (bad[0], len(hn), hn[bad[0]], dn[bad[0]])
+    bad = np.nonzero((ht != dt).any(axis=1))[0]
+    assert len(bad) == 0, "triangle record %d of %d differs" % (bad[0], len(ht))

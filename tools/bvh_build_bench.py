@@ -17,9 +17,18 @@ for name, make in (("statue 20k", scenes.statue_soup), ("cathedral 138k", scenes
         best = (ms, wall, levels, len(nodes)) if best is None or ms < best[0] else best
     s = Scene(); s.addMaterial(material()); t0 = time.perf_counter(); s.addModelSoup(v); host_wall = (time.perf_counter() - t0) * 1e3
     host_ms = s.last_build_ms()
-    same = len(s.arrays()["bvh"][0]) == best[3]
+    s.addObject(0); s.finalize()
+    arrays = s.arrays()
+    same = len(arrays["bvh"][0]) == best[3]
+    from cuda_pathtracer_b200 import abi
+    up = {}
+    for label, flags in (("warm-up", 0), ("device_wide_bvh", 0), ("host_wide_bvh", abi.FLAG_HOST_WIDE_BVH)):
+        pt = api.Pathtracer(arrays, abi.default_config(64, 64, max_ray_depth=2, interactive_depth=1, flags=flags))
+        t0 = time.perf_counter(); pt.Init(); up[label] = (time.perf_counter() - t0) * 1e3
+        pt.close()
     rows.append({"mesh": name, "triangles": len(v), "nodes": best[3], "levels": best[2], "device_build_ms": round(best[0], 3), "device_call_wall_ms_incl_copies_and_alloc": round(best[1], 2),
-                 "host_build_ms": round(host_ms, 1), "speedup_vs_host_builder": round(host_ms / best[0], 1), "same_node_count": bool(same)})
+                 "host_build_ms": round(host_ms, 1), "speedup_vs_host_builder": round(host_ms / best[0], 1), "same_node_count": bool(same),
+                 "upload_scene_wall_ms_device_wide_bvh": round(up["device_wide_bvh"], 1), "upload_scene_wall_ms_host_wide_bvh": round(up["host_wide_bvh"], 1)})
     print(rows[-1], flush=True)
 if len(sys.argv) > 1:
-    json.dump({"what": "binned-SAH BVH2 build, device (pt_build_bvh) vs host builder (host_scene.cpp, 1 thread); identical trees (tests/test_gpu_bvh_build.py)", "rows": rows}, open(sys.argv[1], "w"), indent=1)
+    json.dump({"what": "binned-SAH BVH2 build, device (pt_build_bvh) vs host builder (host_scene.cpp, 1 thread), and pt_upload_scene with the BVH2 -> 8-wide conversion on the device vs on the host; identical outputs (tests/test_gpu_bvh_build.py)", "rows": rows}, open(sys.argv[1], "w"), indent=1)
