@@ -48,6 +48,8 @@ def load_library():
     L.pt_build_bvh_last_error.restype = C.c_char_p
     L.pt_debug_read_wide_bvh.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint32)]
     L.pt_update_instances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+    L.pt_update_instances_device_tlas.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    L.pt_debug_read_tlas.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
     L.pt_set_toggles.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.pt_set_skydome.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
     L.pt_set_sky_constant.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float]
@@ -141,7 +143,10 @@ class Pathtracer:
             if len(a["instances"]):
                 inst = np.ascontiguousarray(a["instances"])
                 tlas = np.ascontiguousarray(a["topBvh"])
-                self._ck(self.L.pt_update_instances(self.h, abi.ptr(inst), len(inst), abi.ptr(tlas), len(tlas)), "pt_update_instances")
+                if getattr(self, "DEVICE_TLAS", False):      # top-level BVH rebuilt on the device from the instance matrices
+                    self._ck(self.L.pt_update_instances_device_tlas(self.h, abi.ptr(inst), len(inst)), "pt_update_instances_device_tlas")
+                else:
+                    self._ck(self.L.pt_update_instances(self.h, abi.ptr(inst), len(inst), abi.ptr(tlas), len(tlas)), "pt_update_instances")
         cam = np.ascontiguousarray(camera)
         self._ck(self.L.pt_render(self.h, abi.ptr(cam), int(bool(shouldClear))), "pt_render")
 
@@ -207,6 +212,16 @@ class Pathtracer:
 
     def num_slots(self):
         return int(self.L.pt_tile_num_slots(C.byref(self.cfg)))
+
+    def update_instances_device_tlas(self, instances):
+        """Scene::update's instance upload with BuildTopLevelBVH (scene.h:81-118) run on the device."""
+        inst = np.ascontiguousarray(instances)
+        self._ck(self.L.pt_update_instances_device_tlas(self.h, abi.ptr(inst), len(inst)), "pt_update_instances_device_tlas")
+
+    def debug_read_tlas(self):
+        out = np.zeros(len(self._arrays()["topBvh"]), abi.TLAS_NODE)
+        self._ck(self.L.pt_debug_read_tlas(self.h, abi.ptr(out), len(out)), "pt_debug_read_tlas")
+        return out
 
     def debug_read_wide_bvh(self):
         """(nodes [n, 20] uint32, triangle records [m, 12] uint32) of the 8-wide BVH as it sits on the device."""

@@ -45,6 +45,8 @@ struct pt_ctx {
     bool haveScene = false;
     std::vector<void*> sceneAllocs;
     uint32_t numInstancesCap = 0, numTlasCap = 0, maxWideDepth = 0, numWideNodes = 0, numWideTris = 0;
+    uint32_t numModels = 0;
+    float4* modelBox = nullptr; unsigned char* tlasAlive = nullptr; uint32_t* tlasDepth = nullptr;   // device top-level BVH build (k_build_tlas)
     // textures
     FrameTex tex;
     std::vector<cudaArray_t> arrays;
@@ -475,6 +477,17 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     if ((r = devUpload(ctx, &di, d->instances, d->num_instances, true))) return r;
     if ((r = devUpload(ctx, &dl, d->topBvh, d->num_tlas_nodes, true))) return r;
     if ((r = devUpload(ctx, &dmo, models.data(), models.size(), true))) return r;
+    {   // what the device top-level BVH build needs: every model's BVH2 root box (scene.h:88-90)
+        std::vector<float4> boxes(2 * (size_t)d->num_models);
+        for (uint32_t m = 0; m < d->num_models; m++) {
+            const pt_bvh_node& rn = d->models[m].bvh[0];
+            boxes[2 * m] = make_float4(rn.vmin.x, rn.vmin.y, rn.vmin.z, 0.f); boxes[2 * m + 1] = make_float4(rn.vmax.x, rn.vmax.y, rn.vmax.z, 0.f);
+        }
+        if ((r = devUpload(ctx, &ctx->modelBox, boxes.data(), boxes.size(), true))) return r;
+        CK(cudaStreamSynchronize(ctx->stream));
+        if ((r = devAlloc(ctx, &ctx->tlasAlive, (size_t)d->num_tlas_nodes + 4, true))) return r;
+        if ((r = devAlloc(ctx, &ctx->tlasDepth, (size_t)d->num_tlas_nodes + 4, true))) return r;
+    }
     if ((r = devUpload(ctx, &ds, d->spheres, d->num_spheres, true))) return r;
     if ((r = devUpload(ctx, &dp, d->planes, d->num_planes, true))) return r;
     if ((r = devUpload(ctx, &dli, lights.data(), lights.size(), true))) return r;
@@ -486,7 +499,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     sc.models = dmo; sc.spheres = ds; sc.planes = dp; sc.lights = dli;
     sc.num_triangles = d->num_triangles; sc.num_instances = d->num_instances; sc.num_spheres = d->num_spheres;
     sc.num_planes = d->num_planes; sc.num_lights = (uint)lights.size();
-    ctx->numInstancesCap = d->num_instances; ctx->numTlasCap = d->num_tlas_nodes;
+    ctx->numInstancesCap = d->num_instances; ctx->numTlasCap = d->num_tlas_nodes; ctx->numModels = d->num_models;
     if (d->num_triangles) {
         k_rc_init<<<(d->num_triangles + 255) / 256, 256, 0, ctx->stream>>>(sc.rcRadiance, sc.rcAdditions, d->num_triangles);   // pathtracer.h:220
         CK(cudaGetLastError());
@@ -508,6 +521,38 @@ PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n,
     CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync((void*)ctx->sc.tlas, tlas, n_nodes * sizeof(pt_tlas_node), cudaMemcpyHostToDevice, ctx->stream));
     if (ctx->sc.num_lights) { k_prepare_lights<<<(ctx->sc.num_lights + 127) / 128, 128, 0, ctx->stream>>>(ctx->sc); CK(cudaGetLastError()); }   // per-light NEE terms follow the instance transforms
+    return PT_OK;
+}
+
+// Scene::update's instance half on the host, its BuildTopLevelBVH half (scene.h:81-118) on the device: the caller hands
+// over the instance matrices only; the top-level BVH is rebuilt in stream order by k_build_tlas (no host work, no
+// synchronisation unless the tree could outgrow the traversal stack).
+PT_API int pt_update_instances_device_tlas(pt_ctx* ctx, const pt_instance* inst, uint32_t n) {
+    if (!ctx || !ctx->haveScene || !inst) return PT_ERR_INVALID;
+    if (n == 0 || n != ctx->numInstancesCap || 2 * n - 1 != ctx->numTlasCap) return fail(ctx, PT_ERR_INVALID, "pt_update_instances_device_tlas: counts differ from the uploaded scene");
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    for (uint32_t i = 0; i < n; i++) if (inst[i].model_id * 2 + 1 >= ctx->numModels * 2) return fail(ctx, PT_ERR_INVALID, "pt_update_instances_device_tlas: instance model_id out of range");
+    CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
+    k_build_tlas<<<1, 256, 0, ctx->stream>>>(ctx->sc.instances, ctx->sc.models, ctx->modelBox, n, (pt_tlas_node*)ctx->sc.tlas, ctx->tlasAlive, ctx->tlasDepth, ctx->tlasDepth + ctx->numTlasCap);
+    CK(cudaGetLastError());
+    if (n - 1 + ctx->maxWideDepth + 2 > PT_STACK) {          // a chain of n leaves is n-1 deep: only then the depth has to be looked at
+        uint32_t depth = 0;
+        CK(cudaMemcpyAsync(&depth, ctx->tlasDepth + ctx->numTlasCap, sizeof depth, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (depth + ctx->maxWideDepth + 2 > PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances_device_tlas: top-level BVH too deep");
+    }
+    if (ctx->sc.num_lights) { k_prepare_lights<<<(ctx->sc.num_lights + 127) / 128, 128, 0, ctx->stream>>>(ctx->sc); CK(cudaGetLastError()); }
+    return PT_OK;
+}
+
+// Test hook: the top-level BVH as it sits on the device.
+PT_API int pt_debug_read_tlas(pt_ctx* ctx, pt_tlas_node* out, uint32_t n_nodes) {
+    if (!ctx || !ctx->haveScene || !out || n_nodes != ctx->numTlasCap) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    CK(cudaMemcpyAsync(out, ctx->sc.tlas, (size_t)n_nodes * sizeof(pt_tlas_node), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     return PT_OK;
 }
 

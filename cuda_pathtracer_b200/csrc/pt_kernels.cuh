@@ -327,6 +327,108 @@ __global__ void k_clear_image(float4* a, float4* b, uint n) {
 // Layout: rcRadiance = 3 x float4 per triangle {radianceCache[0..3]}{radianceCache[4..7]}{radianceTotal,-,-,-};
 // rcAdditions = SoA planes [16][T] (additionCache[8] | additionCacheCount[8]) -- one contiguous buffer,
 // which is what the multi-GPU all-reduce sums.
+// ---- top-level BVH on the device: BuildTopLevelBVH / FindBestMatch / transformBox (scene.h:27-118) ------------------
+// One block.  Same agglomerative clustering as the reference's host code, node for node: leaves sit at 2n-2-i, the walk
+// A -> bestMatch(A) -> ... merges a pair when the relation is mutual, new nodes take the next lower index.  The best
+// match is the first minimum in ascending node order (the reference iterates a std::map with a strict <), found here
+// as the lexicographic minimum of (merged area, node index) over the block.
+struct TlasBox { float lo[3], hi[3]; };
+__device__ __forceinline__ TlasBox tlasLoadBox(const pt_tlas_node* n) {
+    TlasBox b; b.lo[0] = n->vmin.x; b.lo[1] = n->vmin.y; b.lo[2] = n->vmin.z; b.hi[0] = n->vmax.x; b.hi[1] = n->vmax.y; b.hi[2] = n->vmax.z; return b;
+}
+__device__ __forceinline__ float tlasMergedArea(const TlasBox& a, const TlasBox& o) {
+    float lo[3], hi[3];
+    for (int k = 0; k < 3; k++) { lo[k] = fminf(a.lo[k], o.lo[k]); hi[k] = fmaxf(a.hi[k], o.hi[k]); }
+    const float lx = hi[0] - lo[0], ly = hi[1] - lo[1], lz = hi[2] - lo[2];
+    return 2 * lx * ly + 2 * lx * lz + 2 * ly * lz;                                          // Box::getSurfaceArea, types.h:154-161
+}
+__device__ uint tlasBestMatch(const pt_tlas_node* dest, const unsigned char* alive, uint lowest, uint total, uint node, float* sArea, uint* sIdx) {
+    const TlasBox nb = tlasLoadBox(dest + node);
+    float best = 3.402823466e+38f; uint bi = 0xffffffffu;
+    for (uint i = lowest + threadIdx.x; i < total; i += blockDim.x) {
+        if (!alive[i] || i == node) continue;
+        const float a = tlasMergedArea(nb, tlasLoadBox(dest + i));
+        if (a < best) { best = a; bi = i; }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        const float oa = __shfl_down_sync(0xffffffffu, best, off); const uint oi = __shfl_down_sync(0xffffffffu, bi, off);
+        if (oi != 0xffffffffu && (bi == 0xffffffffu || oa < best || (oa == best && oi < bi))) { best = oa; bi = oi; }
+    }
+    __syncthreads();                                                                         // previous readers of sArea / sIdx are done
+    if ((threadIdx.x & 31) == 0) { sArea[threadIdx.x >> 5] = best; sIdx[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    best = sArea[0]; bi = sIdx[0];
+    for (uint w = 1; w < blockDim.x / 32; w++) {
+        const float oa = sArea[w]; const uint oi = sIdx[w];
+        if (oi != 0xffffffffu && (bi == 0xffffffffu || oa < best || (oa == best && oi < bi))) { best = oa; bi = oi; }
+    }
+    return bi == 0xffffffffu ? node : bi;
+}
+__global__ void __launch_bounds__(256) k_build_tlas(const pt_instance* inst, const DModel* models, const float4* modelBox, uint n, pt_tlas_node* dest,
+                                                   unsigned char* alive, uint* depthScratch, uint* maxDepthOut) {
+    __shared__ float sArea[8]; __shared__ uint sIdx[8];
+    const uint total = 2 * n - 1;
+    for (uint i = threadIdx.x; i < total; i += blockDim.x) alive[i] = 0;
+    __syncthreads();
+    for (uint i = threadIdx.x; i < n; i += blockDim.x) {                                     // leaves: transformBox of the model's root box, scene.h:27-52
+        const float4 lo = modelBox[2 * inst[i].model_id], hi = modelBox[2 * inst[i].model_id + 1];
+        const float blo[3] = {lo.x, lo.y, lo.z}, bhi[3] = {hi.x, hi.y, hi.z};
+        const float d[3] = {bhi[0] - blo[0], bhi[1] - blo[1], bhi[2] - blo[2]};
+        float pts[8][3];
+        for (int a = 0; a < 3; a++) { pts[0][a] = blo[a]; pts[4][a] = bhi[a]; }
+        for (int k = 0; k < 3; k++) for (int a = 0; a < 3; a++) {
+            pts[1 + k][a] = blo[a] + (a == k ? d[a] : 0.0f);
+            pts[5 + k][a] = bhi[a] - (a == k ? d[a] : 0.0f);
+        }
+        const pt_mat4x3 t = inst[i].transform;
+        float rlo[3] = {9999999, 9999999, 9999999}, rhi[3] = {-9999999, -9999999, -9999999};  // Box::insideOut, types.h:170-176
+        for (int p = 0; p < 8; p++) {
+            const float wp[3] = {pts[p][0] * t.r1.x + pts[p][1] * t.r1.y + pts[p][2] * t.r1.z + 1.0f * t.r1.w,
+                                 pts[p][0] * t.r2.x + pts[p][1] * t.r2.y + pts[p][2] * t.r2.z + 1.0f * t.r2.w,
+                                 pts[p][0] * t.r3.x + pts[p][1] * t.r3.y + pts[p][2] * t.r3.z + 1.0f * t.r3.w};
+            for (int a = 0; a < 3; a++) { rlo[a] = fminf(wp[a], rlo[a]); rhi[a] = fmaxf(wp[a], rhi[a]); }
+        }
+        pt_tlas_node nd;
+        nd.vmin = pt_float3{rlo[0], rlo[1], rlo[2]}; nd.vmax = pt_float3{rhi[0], rhi[1], rhi[2]}; nd.children = 0; nd.leaf = i;
+        dest[total - 1 - i] = nd; alive[total - 1 - i] = 1;
+    }
+    __syncthreads();
+    uint nodeCount = n - 1, live = n;
+    uint A = n - 1;                                                                          // list.begin(): the lowest live index
+    uint B = live > 1 ? tlasBestMatch(dest, alive, nodeCount, total, A, sArea, sIdx) : A;
+    while (live > 1) {
+        const uint Cc = tlasBestMatch(dest, alive, nodeCount, total, B, sArea, sIdx);
+        if (A == Cc) {
+            const uint idx = --nodeCount;
+            if (threadIdx.x == 0) {
+                const TlasBox a = tlasLoadBox(dest + A), b = tlasLoadBox(dest + B);
+                float lo[3] = {9999999, 9999999, 9999999}, hi[3] = {-9999999, -9999999, -9999999};                      // Box::merged, types.h:178-184
+                for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], a.lo[k]); hi[k] = fmaxf(hi[k], a.hi[k]); }
+                for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], b.lo[k]); hi[k] = fmaxf(hi[k], b.hi[k]); }
+                pt_tlas_node nd = dest[idx];
+                nd.vmin = pt_float3{lo[0], lo[1], lo[2]}; nd.vmax = pt_float3{hi[0], hi[1], hi[2]}; nd.children = A | (B << 16);
+                dest[idx] = nd;
+                alive[A] = 0; alive[B] = 0; alive[idx] = 1;
+            }
+            __syncthreads();
+            live--;
+            A = idx;
+            B = live > 1 ? tlasBestMatch(dest, alive, nodeCount, total, A, sArea, sIdx) : A;
+        } else { A = B; B = Cc; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {                                                                  // depth in edges (children always sit above their parent)
+        uint deepest = 0;
+        depthScratch[0] = 0;
+        for (uint i = 0; i < total; i++) {
+            const uint c = dest[i].children;
+            if (c == 0) { deepest = max(deepest, depthScratch[i]); continue; }
+            depthScratch[c & 0xffffu] = depthScratch[i] + 1; depthScratch[(c >> 16) & 0xffffu] = depthScratch[i] + 1;
+        }
+        *maxDepthOut = deepest;
+    }
+}
+
 __global__ void k_rc_init(float4* rc, float* add, uint T) {                          // kernels.h:848-861
     const uint i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= T) return;

@@ -186,6 +186,10 @@ PT_API const char* pt_last_error(const pt_ctx* ctx);                /* ctx may b
 
 PT_API int  pt_upload_scene(pt_ctx*, const pt_scene_desc*);         /* ~ upload half of Init() (pathtracer.h:129-190,216-220) */
 PT_API int  pt_update_instances(pt_ctx*, const pt_instance*, uint32_t n, const pt_tlas_node*, uint32_t n_nodes); /* pathtracer.h:245-246 */
+/* Same re-sync with the top-level BVH rebuilt ON THE DEVICE from the instance matrices (BuildTopLevelBVH / FindBestMatch /
+ * transformBox, scene.h:27-118: same nodes as the host code); stream-ordered, no host-side tree. */
+PT_API int  pt_update_instances_device_tlas(pt_ctx*, const pt_instance*, uint32_t n);
+PT_API int  pt_debug_read_tlas(pt_ctx*, pt_tlas_node* out, uint32_t n_nodes);   /* test hook: the top-level BVH as it sits on the device */
 PT_API int  pt_set_toggles(pt_ctx*, int nee, int guiding);          /* HNEE / HCACHE (globals.h:19-20); takes effect on the next should_clear render (pathtracer.h:242-243) */
 PT_API int  pt_set_guiding_frames(pt_ctx*, uint32_t frames);           /* run-time value of the training window (pathtracer.h:292: sampleIdx < 100) */
 PT_API int  pt_set_skydome(pt_ctx*, const float* rgba, uint32_t w, uint32_t h);   /* ~ loadTextureHDR (use_cuda.h:202-263): rows already flipped */

@@ -145,3 +145,54 @@ def test_device_wide_bvh_equals_host_converter(name):
     assert len(bad) == 0, "wide node %d of %d differs: host %s device %s" % (bad[0], len(hn), hn[bad[0]], dn[bad[0]])
     bad = np.nonzero((ht != dt).any(axis=1))[0]
     assert len(bad) == 0, "triangle record %d of %d differs" % (bad[0], len(ht))
+
+
+def _instanced_scene(n, seed):
+    rng = np.random.default_rng(seed)
+    s = Scene()
+    s.addMaterial(material())
+    s.addModelSoup(scenes.cube_soup())
+    s.addModelSoup(scenes.statue_soup()[:2000])
+    for i in range(n):
+        s.addObject(int(i % 2), position=rng.uniform(-20, 20, 3), rotation=rng.uniform(-3, 3, 3), scale=rng.uniform(0.3, 2.5, 3))
+    s.finalize()
+    return s, rng
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 10, 33, 200])
+def test_device_top_level_bvh_equals_host_build(n):
+    """k_build_tlas against the host BuildTopLevelBVH (pinned to the reference in tests/test_cpu_host_scene.py): the same
+    nodes bit for bit, also after the objects moved (Scene::update, scene.h:367-401)."""
+    s, rng = _instanced_scene(n, 100 + n)
+    a = s.arrays()
+    pt = api.Pathtracer(a, abi.default_config(64, 64, max_ray_depth=2, interactive_depth=1)).Init()
+    for step in range(3):
+        pt.update_instances_device_tlas(a["instances"])
+        got, want = pt.debug_read_tlas(), a["topBvh"]
+        assert len(got) == 2 * n - 1
+        for f in ("vmin", "vmax", "children"):
+            bad = np.nonzero((got[f] != want[f]).reshape(len(got), -1).any(axis=1))[0]
+            assert len(bad) == 0, "step %d: %s differs at node %d: device %s host %s" % (step, f, bad[0], got[bad[0]], want[bad[0]])
+        leaves = want["children"] == 0
+        assert np.array_equal(got["leaf"][leaves], want["leaf"][leaves])
+        for i in range(n):                                   # move everything, rebuild on the host, compare again
+            s.setObject(i, rng.uniform(-20, 20, 3), rng.uniform(-3, 3, 3), rng.uniform(0.3, 2.5, 3))
+        s.update()
+        a = s.arrays()
+    pt.close()
+
+
+def test_render_with_device_top_level_bvh_is_bit_identical():
+    imgs = []
+    for device_tlas in (False, True):
+        sc = scenes.outside_scene()
+        pt = api.Pathtracer(sc.arrays(), abi.default_config(160, 120, max_ray_depth=6, interactive_depth=1)).Init()
+        pt.DEVICE_TLAS = device_tlas
+        cam = scenes.camera_sweep("outside", 160, 120, 4)[1]
+        pt.Render(cam, shouldClear=True)
+        for _ in range(4):
+            pt.Render(cam)
+        pt.Finish()
+        imgs.append(pt.read_image())
+        pt.close()
+    assert imgs[0].tobytes() == imgs[1].tobytes() and float(imgs[0][..., :3].sum()) > 0
