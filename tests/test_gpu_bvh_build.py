@@ -196,3 +196,19 @@ def test_render_with_device_top_level_bvh_is_bit_identical():
         imgs.append(pt.read_image())
         pt.close()
     assert imgs[0].tobytes() == imgs[1].tobytes() and float(imgs[0][..., :3].sum()) > 0
+
+
+def test_scene_script_renders_headless(tmp_path):
+    """examples/render_script.py: scene script + camera state file -> PFM (the reference's `pathtracer scene.chai` flow)."""
+    import subprocess, sys, os
+    from util import read_pfm, write_obj
+    write_obj(str(tmp_path / "box.obj"), scenes.cube_soup())
+    (tmp_path / "scene.chai").write_text('var m = DiffuseMaterial(make_float3(0.8, 0.7, 0.6))\nvar id = scene_add_material(m)\n'
+                                         'var box = scene_add_model("box.obj", 2, make_float3(0,0,0), make_float3(0,0,0), id, false)\n'
+                                         'var o = GameObject(box)\no.position = make_float3(0, 2, 4)\no.rotation.y = 0.5\nscene_add_object(o);\n')
+    root = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "render_script.py"), str(tmp_path / "scene.chai"), str(tmp_path / "o.pfm"),
+                        "--state", str(tmp_path / "none.txt"), "--spp", "8", "--size", "160x120", "--depth", "4"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-1500:]
+    img = read_pfm(str(tmp_path / "o.pfm"))
+    assert img.shape[:2] == (120, 160) and np.isfinite(img).all() and img.std() > 0.01          # the box is in view against the white sky
