@@ -46,6 +46,9 @@ def load_library():
     L.pt_upload_scene.argtypes = [C.c_void_p, C.POINTER(abi.SceneDesc)]
     L.pt_build_bvh.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
     L.pt_build_bvh_last_error.restype = C.c_char_p
+    L.pt_read_image_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+    L.pt_read_tiles_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+    L.pt_wait_read.argtypes = [C.c_void_p, C.c_uint64]
     L.pt_debug_read_wide_bvh.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint32)]
     L.pt_update_instances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
     L.pt_update_instances_device_tlas.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
@@ -222,6 +225,18 @@ class Pathtracer:
         out = np.zeros(len(self._arrays()["topBvh"]), abi.TLAS_NODE)
         self._ck(self.L.pt_debug_read_tlas(self.h, abi.ptr(out), len(out)), "pt_debug_read_tlas")
         return out
+
+    def read_image_async(self, out, which=0, tiles=False):
+        """Streaming read-back into `out` (pinned host memory: (H, W, 4) float32, or (num_slots, 4) with tiles=True): the
+        image as it is after every Render call made so far, copied while later samples render.  Returns a ticket for
+        wait_read(); Finish() / join() cover all outstanding copies."""
+        t = C.c_uint64()
+        fn = self.L.pt_read_tiles_async if tiles else self.L.pt_read_image_async
+        self._ck(fn(self.h, abi.ptr(out), int(which), C.byref(t)), "pt_read_image_async")
+        return t.value
+
+    def wait_read(self, ticket):
+        self._ck(self.L.pt_wait_read(self.h, C.c_uint64(ticket)), "pt_wait_read")
 
     def debug_read_wide_bvh(self):
         """(nodes [n, 20] uint32, triangle records [m, 12] uint32) of the 8-wide BVH as it sits on the device."""

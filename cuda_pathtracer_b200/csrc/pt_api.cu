@@ -38,6 +38,13 @@ struct pt_ctx {
     int nSets = 4, cur = 0;
     bool forked = false, prevTraining = false;
     cudaEvent_t forkEv = nullptr;
+    // Asynchronous read-back (pt_read_image_async): copies run on their own stream after the sample they follow; the
+    // next accumulate waits for the copy, so the snapshot is exactly "after that sample".  Tickets index a ring of events.
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t copyReady = nullptr, copyEv[8] = {};
+    uint64_t copyTickets = 0;
+    bool copyPending = false;
+    int lastSet = -1;
     float4 *image = nullptr, *albedo = nullptr, *postBuf = nullptr, *packBuf = nullptr;
     unsigned long long* stats = nullptr;
     // scene
@@ -121,6 +128,7 @@ static int devUpload(pt_ctx* ctx, T** p, const T* host, size_t n, bool sceneOwne
 // Work enqueued by pt_render lives on the private streams of the sample sets.  joinStreams() orders everything
 // enqueued so far before whatever comes next on the context's public stream (pt_cuda_stream()).
 static int joinStreams(pt_ctx* ctx) {
+    if (ctx->copyPending) { CK(cudaStreamWaitEvent(ctx->stream, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0)); ctx->copyPending = false; }
     if (!ctx->forked) return PT_OK;
     for (auto& S : ctx->set) {
         if (S.doneValid) { CK(cudaStreamWaitEvent(ctx->stream, S.done, 0)); S.doneValid = false; }
@@ -166,6 +174,9 @@ PT_API void pt_destroy(pt_ctx* ctx) {
         if (S.stream) cudaStreamDestroy(S.stream);
     }
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
+    if (ctx->copyReady) cudaEventDestroy(ctx->copyReady);
+    for (auto e : ctx->copyEv) if (e) cudaEventDestroy(e);
+    if (ctx->copyStream) cudaStreamDestroy(ctx->copyStream);
     void* bufs[] = {ctx->image, ctx->albedo, ctx->postBuf, ctx->packBuf, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
     for (void* p : bufs) if (p) cudaFree(p);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -591,6 +602,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         pt_ctx::SampleSet& S = ctx->set[pipelined ? ctx->cur : 0];
         pt_ctx::SampleSet& other = ctx->set[pipelined ? (ctx->cur + ctx->nSets - 1) % ctx->nSets : 0];     // the previous sample's set
         cudaStream_t s = pipelined ? S.stream : ctx->stream;
+        ctx->lastSet = pipelined ? ctx->cur : -1;
         if (pipelined) ctx->cur = (ctx->cur + 1) % ctx->nSets;
         const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots;   // :292
         // Short queues: a sample that runs alone (clearing / profiled / cache-training frames) spreads its rays over all
@@ -667,6 +679,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             }
             ctx->launches++, k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
         }
+        if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0));    // a read-back in flight still reads the image
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
                           ctx->launches++, k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
         if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
@@ -705,6 +718,47 @@ PT_API int pt_read_image(pt_ctx* ctx, float* host_rgbw, int which) {
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaMemcpyAsync(host_rgbw, which == 0 ? ctx->image : ctx->albedo, (size_t)ctx->map.W * ctx->map.H * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+// Asynchronous read-back: the image as it is after everything enqueued so far, copied on a private stream while later
+// samples render (only their accumulate waits for the copy).  host should be pinned memory.  *ticket (optional) can be
+// handed to pt_wait_read; pt_finish / pt_join also cover it.  tiles != 0: this rank's tiles only, slot order (pt_read_tiles).
+static int readAsync(pt_ctx* ctx, float* host, int which, bool tiles, uint64_t* ticket) {
+    if (!ctx || !host) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (!ctx->copyStream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->copyReady, cudaEventDisableTiming));
+        for (auto& e : ctx->copyEv) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    if (ctx->forked && ctx->lastSet >= 0 && ctx->set[ctx->lastSet].doneValid) CK(cudaStreamWaitEvent(ctx->copyStream, ctx->set[ctx->lastSet].done, 0));
+    else { CK(cudaEventRecord(ctx->copyReady, ctx->stream)); CK(cudaStreamWaitEvent(ctx->copyStream, ctx->copyReady, 0)); }
+    const float4* src = which == 0 ? ctx->image : ctx->albedo;
+    if (tiles) {
+        const uint32_t n = ctx->map.nSlots;
+        if (n) {
+            if (!ctx->packBuf) CK(cudaMalloc((void**)&ctx->packBuf, (size_t)n * sizeof(float4)));
+            k_pack_tiles<<<n / 256, 256, 0, ctx->copyStream>>>(ctx->map, src, ctx->packBuf);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(host, ctx->packBuf, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->copyStream));
+        }
+    } else {
+        CK(cudaMemcpyAsync(host, src, (size_t)ctx->map.W * ctx->map.H * sizeof(float4), cudaMemcpyDeviceToHost, ctx->copyStream));
+    }
+    CK(cudaEventRecord(ctx->copyEv[ctx->copyTickets & 7], ctx->copyStream));
+    if (ticket) *ticket = ctx->copyTickets;
+    ctx->copyTickets++;
+    ctx->copyPending = true;
+    return PT_OK;
+}
+PT_API int pt_read_image_async(pt_ctx* ctx, float* host_rgbw, int which, uint64_t* ticket) { return readAsync(ctx, host_rgbw, which, false, ticket); }
+PT_API int pt_read_tiles_async(pt_ctx* ctx, float* host_rgbw_slots, int which, uint64_t* ticket) { return readAsync(ctx, host_rgbw_slots, which, true, ticket); }
+// Blocks the host until the read-back with this ticket has landed (valid for the 8 most recent tickets; older ones have landed).
+PT_API int pt_wait_read(pt_ctx* ctx, uint64_t ticket) {
+    if (!ctx || ticket >= ctx->copyTickets) return PT_ERR_INVALID;
+    if (ctx->copyTickets - ticket > 8) return PT_OK;
+    CK(cudaEventSynchronize(ctx->copyEv[ticket & 7]));
     return PT_OK;
 }
 

@@ -203,6 +203,12 @@ PT_API int  pt_join(pt_ctx*);                                         /* asynchr
 PT_API int  pt_finish(pt_ctx*);                                       /* == Pathtracer::Finish (pathtracer.h:305-310); synchronises */
 PT_API int  pt_read_image(pt_ctx*, float* host_rgbw, int which);      /* headless stand-in for the GL textures: which = 0 luminance (rgb sum, w = samples), 1 albedo */
 PT_API int  pt_read_tiles(pt_ctx*, float* host_rgbw_slots, int which);  /* this rank's pixels only: pt_tile_num_slots() float4 in slot order (multi-GPU: 1/N of the image per rank) */
+/* Streaming read-back: the image as it is after everything enqueued so far, copied to (pinned) host memory on a private
+ * stream while later samples render (only their accumulate step waits for the copy, so the snapshot is exact).
+ * pt_wait_read(ticket) blocks until that copy has landed; pt_finish / pt_join cover all of them. */
+PT_API int  pt_read_image_async(pt_ctx*, float* host_rgbw, int which, uint64_t* ticket);
+PT_API int  pt_read_tiles_async(pt_ctx*, float* host_rgbw_slots, int which, uint64_t* ticket);
+PT_API int  pt_wait_read(pt_ctx*, uint64_t ticket);
 PT_API int  pt_write_pfm(pt_ctx*, const char* path, int which);        /* headless render-to-PFM (display value rgb / w, main.cpp:58-62) in place of the GLFW window */
 /* Display post-process (main.cpp:46-171,316-376: demodulated separable Gaussian, remodulate, gamma 2, vignette) as CUDA
  * kernels; host float4 in (or NULL, NULL = the context's accumulators), host float4 RGBA out. */

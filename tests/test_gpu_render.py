@@ -311,3 +311,37 @@ def test_display_postprocess_matches_shader_restatement(sibenik_small, blur):
     np.testing.assert_allclose(got[ok], want[ok], rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(pt.postprocess(blur=blur, lum=lum, albedo=alb, nr_samples=8.0)[ok], got[ok], rtol=0, atol=0)   # host-image path
     pt.close(); ora.close()
+
+
+def test_async_read_back_snapshots_are_exact():
+    """pt_read_image_async while later samples render: snapshot k == the blocking read after k samples, bit for bit
+    (full image and this rank's tiles)."""
+    import torch
+    arrays = scenes.teapot_like_scene().arrays()
+    cfg = abi.default_config(160, 120, max_ray_depth=6, interactive_depth=1)
+    cam = scenes.camera_sweep("outside", 160, 120, 4)[0]
+    n = 12
+
+    def run(async_mode):
+        pt = api.Pathtracer(arrays, cfg).Init()
+        pt.Render(cam, shouldClear=True)
+        out, tickets = [], []
+        for k in range(n):
+            pt.Render(cam)
+            if async_mode:
+                buf = torch.empty((120, 160, 4) if k % 2 == 0 else (pt.num_slots(), 4), dtype=torch.float32, pin_memory=True).numpy()
+                tickets.append(pt.read_image_async(buf, tiles=(k % 2 == 1)))
+                out.append(buf)
+                if k >= 3:
+                    pt.wait_read(tickets[k - 3])
+            else:
+                pt.Finish()
+                out.append(pt.read_image() if k % 2 == 0 else pt.read_tiles())
+        pt.Finish()
+        pt.close()
+        return out
+
+    a, b = run(True), run(False)
+    for k in range(n):
+        assert a[k].tobytes() == b[k].tobytes(), "snapshot %d differs" % k
+    assert a[1].tobytes() != a[3].tobytes()
