@@ -68,6 +68,7 @@ struct pt_ctx {
     int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0, gridTail = 0;
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
+    uint32_t knobMinWidth = 0; bool knobNoTailWait = false;   // developer knobs (environment, read in pt_create)
     // per-stage timing (pt_set_profiling): CUDA event pairs around every stage launch, resolved in pt_finish
     bool prof = false;
     std::vector<cudaEvent_t> evPool;
@@ -288,6 +289,8 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if (cfg->flags & PT_FLAG_WAVEFRONT_ONLY) ctx->tailBounce = PT_MAX_BOUNCES;
         else if ((cfg->flags >> 8) & 0xffu) { ctx->tailBounce = std::max(1u, ((cfg->flags >> 8) & 0xffu) - 1u); ctx->tailForced = true; }
         if (const char* e = getenv("PTB200_TAIL_BOUNCE")) { ctx->tailBounce = std::max(1, atoi(e)); ctx->tailForced = true; }      // developer knob (tools/tune.sh)
+        if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->knobMinWidth = (uint32_t)std::max(1, std::min(32, atoi(e)));          // developer knobs, read once
+        ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
         CK(cudaStreamSynchronize(ctx->stream));
         return PT_OK;
     };
@@ -609,11 +612,11 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // warps (latency); samples that overlap others keep their warps full (throughput: 0.41 -> 0.32 ms/sample on a
         // 1/8-image shard), the other samples in flight fill the machine.
         ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
-        if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->sc.minWidth = (uint)std::max(1, std::min(32, atoi(e)));   // developer knob
+        if (ctx->knobMinWidth) ctx->sc.minWidth = ctx->knobMinWidth;
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
-        if (pipelined && (training || ctx->prevTraining) && other.tailValid && !getenv("PTB200_NO_TAIL_WAIT")) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
+        if (pipelined && (training || ctx->prevTraining) && other.tailValid && !ctx->knobNoTailWait) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
         CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                      // :265 (+ cursors)
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); ctx->launches++, k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
