@@ -87,8 +87,7 @@ __global__ void __launch_bounds__(256) k_primary(DCamera cam, TileMap map, uint 
     const bool valid = slotToPixel(map, slot, x, y);
     float3 o = f3(0), d = f3(0);
     if (valid) {
-        accucolors[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                    // kernels.h:489
-        masks[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(1u));           // kernels.h:490
+        // (the per-sample state reset of kernels.h:485-491 happens in the first shade: every valid slot gets a primary ray)
         uint seed = getSeed(x, y, randIdx, map.W);
         camGetRay(cam, x, y, seed, map.W, map.H, o, d);
     }

@@ -142,7 +142,12 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
     out.pushExt = out.pushShadow = false;
     uint x, y; slotToPixel(P.map, slot, x, y);
     TraceState state;
-    {
+    if (P.bounce == 0) {
+        // kernel_clear_state (kernels.h:485-491) folded in: the first shade of a sample starts from the cleared state instead of
+        // reading it back (mask 1, fromSpecular, nothing accumulated; `light` is only ever read after the shade that sets it)
+        state.mask = f3(1.0f); state.accucolor = f3(0.0f); state.light = f3(0.0f);
+        state.fromSpecular = true; state.albedoSet = false;
+    } else {
         const float4 m = P.masks[slot], a = P.accucolors[slot], l = P.lights[slot];
         state.mask = f3(m); state.accucolor = f3(a); state.light = f3(l);
         state.fromSpecular = (__float_as_uint(m.w) & 0xffu) != 0; state.albedoSet = (__float_as_uint(a.w) & 0xffu) != 0;
