@@ -24,6 +24,10 @@ private:
     static void die(pt_ctx* c, const char* what) { fprintf(stderr, "%s: %s\n", what, pt_last_error(c)); exit(1); }
 
 public:
+    /* true: the top-level BVH is rebuilt on the device from scene.instances on every clearing frame
+     * (pt_update_instances_device_tlas), so the host loop may drop its BuildTopLevelBVH call (scene.h:396-400) */
+    bool deviceTopLevelBVH = false;
+
     Pathtracer(Scene& scene, GLuint luminanceTexture, GLuint albedoTexture) : Application(scene, luminanceTexture, albedoTexture) {}
     ~Pathtracer() { pt_destroy(ctx); }
 
@@ -55,8 +59,9 @@ public:
         (void)currentTime; (void)frameTime;
         if (shouldClear) {
             pt_set_toggles(ctx, HNEE, HCACHE);                                                    // pathtracer.h:242-243
-            if (pt_update_instances(ctx, (const pt_instance*)scene.instances, (uint32_t)scene.objects.size(),
-                                    (const pt_tlas_node*)scene.topLevelBVH.data(), (uint32_t)scene.topLevelBVH.size()))   // :245-246
+            if (deviceTopLevelBVH ? pt_update_instances_device_tlas(ctx, (const pt_instance*)scene.instances, (uint32_t)scene.objects.size())
+                                  : pt_update_instances(ctx, (const pt_instance*)scene.instances, (uint32_t)scene.objects.size(),
+                                                        (const pt_tlas_node*)scene.topLevelBVH.data(), (uint32_t)scene.topLevelBVH.size()))   // :245-246
                 die(ctx, "pt_update_instances");
         }
         if (pt_render(ctx, (const pt_camera*)&camera, shouldClear)) die(ctx, "pt_render");
@@ -68,6 +73,9 @@ public:
     void SetSkyConstant(float r, float g, float b) { pt_set_sky_constant(ctx, r, g, b); }
     void ReadLuminance(float* rgbw) { if (pt_read_image(ctx, rgbw, 0)) die(ctx, "pt_read_image"); }
     void ReadAlbedo(float* rgbw) { if (pt_read_image(ctx, rgbw, 1)) die(ctx, "pt_read_image"); }
+    /* streaming read-back into pinned host memory while the next samples render; WaitRead(ticket) or Finish() before use */
+    uint64_t ReadLuminanceAsync(float* rgbw) { uint64_t t = 0; if (pt_read_image_async(ctx, rgbw, 0, &t)) die(ctx, "pt_read_image_async"); return t; }
+    void WaitRead(uint64_t ticket) { if (pt_wait_read(ctx, ticket)) die(ctx, "pt_wait_read"); }
     void WritePFM(const char* path) { if (pt_write_pfm(ctx, path, 0)) die(ctx, "pt_write_pfm"); }
     pt_ctx* Context() { return ctx; }
 };

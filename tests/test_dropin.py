@@ -74,6 +74,21 @@ def test_reference_host_code_renders_through_the_adapter(tmp_path):
 EXAMPLE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "examples", "render_pfm")
 
 
+@needs_dropin
+@pytest.mark.gpu
+def test_adapter_with_device_top_level_bvh_gives_the_same_picture(tmp_path):
+    """Pathtracer::deviceTopLevelBVH: the clearing frame rebuilds the top-level BVH on the device from scene.instances (the
+    host tree is scrambled after Init, so a render that still read it would differ)."""
+    obj = _mesh(tmp_path)
+    outs = []
+    for dev in ("0", "1"):
+        out = str(tmp_path / ("tlas%s.pfm" % dev))
+        r = subprocess.run([DROPIN, obj, out, "4", str(EYE[0]), str(EYE[1]), str(EYE[2]), "1", dev], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(open(out, "rb").read())
+    assert outs[0] == outs[1]
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(not os.path.exists(EXAMPLE), reason="examples/render_pfm not built")
 def test_cpp_only_headless_render_to_pfm(tmp_path):
