@@ -170,9 +170,16 @@ def gpu_arm(args):
     cfg = abi.default_config(W, H, max_ray_depth=DEPTH, interactive_depth=1, device=local, rank=rank, world_size=world)
     pt = api.Pathtracer(arrays, cfg).Init()
     stream = torch.cuda.ExternalStream(pt.stream(), device=torch.device("cuda", local))
+    exchange = "none"
     if world > 1:
-        from cuda_pathtracer_b200.distributed import make_allreduce_hook
-        pt.set_allreduce_hook(make_allreduce_hook(torch.device("cuda", local)))   # NCCL sum over NVLink on the stream the sample runs on
+        # radiance-cache exchange of the training frames: the library's fused reduce + propagate + broadcast kernel over NVLink
+        # peer memory; --exchange nccl (or a failed peer mapping) selects the all-reduce hook + local propagate instead
+        from cuda_pathtracer_b200.distributed import make_allreduce_hook, connect_peers
+        exchange = "nccl all-reduce + propagate"
+        if args.exchange == "peer" and connect_peers(pt, torch.device("cuda", local)):
+            exchange = "fused reduce+propagate over NVLink peer memory"
+        else:
+            pt.set_allreduce_hook(make_allreduce_hook(torch.device("cuda", local)))   # NCCL sum over NVLink on the stream the sample runs on
     cams = [camera_for(i, W, H) for i in range(16)]
 
     def barrier():
@@ -301,7 +308,7 @@ def gpu_arm(args):
         tot_prof_ms = sum(v[0] for v in prof.values())
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "samples_in_flight": 4 if pt.num_slots() > 1200000 else 8, "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
+                "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "exchange": exchange, "samples_in_flight": 4 if pt.num_slots() > 1200000 else 8, "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
                            "cameras": "16-camera sweep inside the nave, one camera per step", "global_pixels": W * H},
                 "spp_per_s": args.steps / (ms * 1e-3), "rays_per_step": total_rays / args.steps,
                 "phases": {"note": "timed steps follow the reference frame loop from sample %d: the radiance cache trains (update + all-reduce + propagate) while sampleIdx < 100, then stays frozen" % (1 + max(args.warmup, 3)),
@@ -324,6 +331,9 @@ def gpu_arm(args):
                 "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": "oracle/pt_oracle.cpp: %d converge samples of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_SAMPLES, CPU_W, CPU_H, cpu_rays, cpu_s)}}
         print(json.dumps(line), flush=True)
+    if world > 1 and exchange.startswith("fused"):
+        from cuda_pathtracer_b200.distributed import disconnect_peers
+        disconnect_peers(pt)
     pt.close()
     if world > 1:
         dist.destroy_process_group()
@@ -335,6 +345,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--exchange", default=os.environ.get("PTB200_EXCHANGE", "peer"), choices=["peer", "nccl"],
+                    help="N>1: radiance-cache exchange of the training frames (peer = fused kernel over NVLink peer memory)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

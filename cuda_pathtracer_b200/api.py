@@ -59,6 +59,9 @@ def load_library():
     L.pt_set_blue_noise.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
     L.pt_texture_create.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
     L.pt_set_allreduce_hook.argtypes = [C.c_void_p, abi.ALLREDUCE_HOOK, C.c_void_p]
+    L.pt_peer_export.argtypes = [C.c_void_p, C.c_void_p]
+    L.pt_peer_connect.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    L.pt_peer_disconnect.argtypes = [C.c_void_p]
     L.pt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.pt_finish.argtypes = [C.c_void_p]
     L.pt_join.argtypes = [C.c_void_p]
@@ -266,6 +269,21 @@ class Pathtracer:
         else:
             self._hook = abi.ALLREDUCE_HOOK(lambda user, p, n, s: int(fn(p or 0, n, s or 0)))
         self._ck(self.L.pt_set_allreduce_hook(self.h, self._hook, None), "pt_set_allreduce_hook")
+
+    def peer_export(self):
+        """cudaIpc handle (64 bytes) of this rank's radiance-cache block; gather them over all ranks for peer_connect."""
+        buf = C.create_string_buffer(64)
+        self._ck(self.L.pt_peer_export(self.h, buf), "pt_peer_export")
+        return buf.raw
+
+    def peer_connect(self, handles):
+        """handles: the 64-byte handles of all ranks in rank order.  Training frames then exchange the radiance-cache
+        additions with the fused reduce + propagate kernel over NVLink peer memory instead of hook + propagate."""
+        blob = b"".join(handles)
+        self._ck(self.L.pt_peer_connect(self.h, blob, len(blob) // 64), "pt_peer_connect")
+
+    def peer_disconnect(self):
+        self._ck(self.L.pt_peer_disconnect(self.h), "pt_peer_disconnect")
 
     # -- statistics / stage hooks --
     def stats(self):

@@ -65,6 +65,11 @@ struct pt_ctx {
     unsigned long long launches = 0;      // kernels launched by pt_render since the last pt_reset_stats
     pt_allreduce_hook hook = nullptr;
     void* hookUser = nullptr;
+    // radiance-cache block: [flags 4 KB][rcAdditions][rcRadiance] in ONE allocation, so that a single cudaIpc handle
+    // gives the peers everything the fused reduce+propagate needs (pt_peer_export / pt_peer_connect)
+    unsigned char* rcBlock = nullptr;
+    size_t rcAddOffset = 0, rcRcOffset = 0;
+    struct Peers { bool on = false; PeerSet ps; void* opened[PT_PEER_MAX] = {}; uint32_t epoch = 0; unsigned long long timeoutNs = 10000000000ull; } peer;
     int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0, gridTail = 0;
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
@@ -155,6 +160,11 @@ PT_API void pt_default_config(pt_config* c) {
 
 PT_API const char* pt_last_error(const pt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
 
+static void peerClose(pt_ctx* ctx) {
+    for (auto& p : ctx->peer.opened) if (p) { cudaIpcCloseMemHandle(p); p = nullptr; }
+    ctx->peer.on = false;
+}
+
 PT_API void pt_destroy(pt_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
@@ -164,6 +174,7 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     for (auto e : ctx->evPool) cudaEventDestroy(e);
     for (auto t : ctx->textures) cudaDestroyTextureObject(t);
     for (auto a : ctx->arrays) cudaFreeArray(a);
+    peerClose(ctx);
     for (void* p : ctx->sceneAllocs) cudaFree(p);
     for (auto& S : ctx->set) {
         if (S.stream) cudaStreamSynchronize(S.stream);
@@ -403,8 +414,10 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaStreamSynchronize(ctx->stream));
+    peerClose(ctx);                                // the peers' mappings of the old block die with it
     for (void* p : ctx->sceneAllocs) cudaFree(p);
     ctx->sceneAllocs.clear();
+    ctx->rcBlock = nullptr;
     ctx->haveScene = false;
     DScene& sc = ctx->sc;
     memset(&sc, 0, sizeof(sc));
@@ -506,8 +519,15 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     if ((r = devUpload(ctx, &dp, d->planes, d->num_planes, true))) return r;
     if ((r = devUpload(ctx, &dli, lights.data(), lights.size(), true))) return r;
     if ((r = devAlloc(ctx, &sc.lightTab, lights.size() * PT_LIGHT_STRIDE, true))) return r;
-    if ((r = devAlloc(ctx, &sc.rcRadiance, (size_t)d->num_triangles * 3, true))) return r;
-    if ((r = devAlloc(ctx, &sc.rcAdditions, (size_t)d->num_triangles * 16, true))) return r;
+    {
+        const size_t addBytes = ((size_t)d->num_triangles * 16 * sizeof(float) + 255) & ~(size_t)255;
+        ctx->rcAddOffset = 4096; ctx->rcRcOffset = 4096 + addBytes;
+        const size_t total = std::max<size_t>(ctx->rcRcOffset + (size_t)d->num_triangles * 3 * sizeof(float4), (size_t)4 << 20);   // >= 4 MB: never sub-allocated, the IPC handle maps exactly this range
+        if ((r = devAlloc(ctx, &ctx->rcBlock, total, true))) return r;
+        CK(cudaMemsetAsync(ctx->rcBlock, 0, 4096, ctx->stream));
+        sc.rcAdditions = reinterpret_cast<float*>(ctx->rcBlock + ctx->rcAddOffset);
+        sc.rcRadiance = reinterpret_cast<float4*>(ctx->rcBlock + ctx->rcRcOffset);
+    }
     phase("other H2D + allocations");
     sc.nodes = dn; sc.wtris = dt; sc.vertices = dv; sc.vertexData = dd; sc.materials = dm; sc.instances = di; sc.tlas = dl;
     sc.models = dmo; sc.spheres = ds; sc.planes = dp; sc.lights = dli;
@@ -676,11 +696,22 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         if (training) {                                                                    // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING, s);
             ctx->launches++, k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
-            if (ctx->hook) {
-                int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
-                if (hr) return fail(ctx, PT_ERR_INVALID, "pt_render: all-reduce hook failed");
+            if (ctx->peer.on) {
+                // reduce + propagate + broadcast over peer memory (pt_kernels.cuh): the owner of a triangle range sums every
+                // rank's additions out of their HBM, propagates once and stores the result into every rank's cache
+                const PeerSet& ps = ctx->peer.ps;
+                const uint32_t T = ctx->sc.num_triangles, epoch = ++ctx->peer.epoch;
+                const uint32_t lo = (uint32_t)((uint64_t)T * ps.rank / ps.world), hi = (uint32_t)((uint64_t)T * (ps.rank + 1) / ps.world);
+                ctx->launches++, k_peer_arrive<<<1, 32, 0, s>>>(ps, epoch);
+                ctx->launches++, k_peer_reduce_propagate<<<std::max(1u, (hi - lo + 255u) / 256u), 256, 0, s>>>(ps, epoch, T, lo, hi, ctx->peer.timeoutNs);
+                ctx->launches++, k_peer_finish<<<(unsigned)std::min<size_t>(296, ((size_t)16 * T + 255) / 256), 256, 0, s>>>(ps, epoch, T, ctx->peer.timeoutNs);
+            } else {
+                if (ctx->hook) {
+                    int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
+                    if (hr) return fail(ctx, PT_ERR_INVALID, "pt_render: all-reduce hook failed");
+                }
+                ctx->launches++, k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             }
-            ctx->launches++, k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
         }
         if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0));    // a read-back in flight still reads the image
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
@@ -699,6 +730,66 @@ PT_API int pt_finish(pt_ctx* ctx) {                                             
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaStreamSynchronize(ctx->stream));
     resolveProfile(ctx);
+    if (ctx->peer.on) {
+        uint32_t e = 0;
+        CK(cudaMemcpy(&e, ctx->rcBlock + PT_PEER_ERROR * sizeof(uint32_t), sizeof(e), cudaMemcpyDeviceToHost));
+        if (e) return fail(ctx, PT_ERR_CUDA, "pt_finish: a peer did not reach the radiance-cache exchange in time (ranks must render the same frames)");
+    }
+    return PT_OK;
+}
+
+// ---- multi-GPU exchange over NVLink peer memory --------------------------------------------------------------------------
+// pt_peer_export: the cudaIpc handle of this rank's radiance-cache block (flags | additions | cache).  The caller gathers the
+// handles of all ranks (any transport: torch.distributed, MPI, a file) and passes them, in rank order, to pt_peer_connect,
+// which maps every peer's block and switches the training frames from "hook + propagate" to the fused peer kernels.
+PT_API int pt_peer_export(pt_ctx* ctx, void* handle_out) {
+    if (!ctx || !handle_out) return PT_ERR_INVALID;
+    if (!ctx->haveScene || !ctx->rcBlock) return fail(ctx, PT_ERR_INVALID, "pt_peer_export: no scene uploaded");
+    static_assert(sizeof(cudaIpcMemHandle_t) == PT_PEER_HANDLE_BYTES, "handle size");
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    CK(cudaStreamSynchronize(ctx->stream));
+    peerClose(ctx);
+    uint32_t flags[1024] = {};
+    flags[PT_PEER_MAGIC] = 0x50544230u + ctx->cfg.rank;
+    CK(cudaMemcpy(ctx->rcBlock, flags, sizeof(flags), cudaMemcpyHostToDevice));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, ctx->rcBlock));
+    memcpy(handle_out, &h, sizeof(h));
+    return PT_OK;
+}
+PT_API int pt_peer_connect(pt_ctx* ctx, const void* handles, uint32_t world) {
+    if (!ctx || !handles) return PT_ERR_INVALID;
+    if (!ctx->haveScene || !ctx->rcBlock) return fail(ctx, PT_ERR_INVALID, "pt_peer_connect: no scene uploaded");
+    if (world != ctx->cfg.world_size || world > PT_PEER_MAX) return fail(ctx, PT_ERR_INVALID, "pt_peer_connect: world size differs from pt_config.world_size (or exceeds 16)");
+    CK(cudaSetDevice(ctx->cfg.device));
+    peerClose(ctx);
+    PeerSet ps; memset(&ps, 0, sizeof(ps));
+    ps.rank = ctx->cfg.rank; ps.world = world; ps.addOffset = ctx->rcAddOffset; ps.rcOffset = ctx->rcRcOffset;
+    for (uint32_t r = 0; r < world; r++) {
+        if (r == ctx->cfg.rank) { ps.block[r] = ctx->rcBlock; continue; }
+        cudaIpcMemHandle_t h; memcpy(&h, (const unsigned char*)handles + (size_t)r * sizeof(h), sizeof(h));
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        uint32_t magic = 0;
+        if (e == cudaSuccess) { ctx->peer.opened[r] = p; e = cudaMemcpy(&magic, (unsigned char*)p + PT_PEER_MAGIC * sizeof(uint32_t), sizeof(magic), cudaMemcpyDeviceToHost); }
+        if (e != cudaSuccess || magic != 0x50544230u + r) {
+            cudaGetLastError(); peerClose(ctx);
+            char buf[256]; snprintf(buf, sizeof(buf), "pt_peer_connect: cannot map the block of rank %u (%s)", r, e != cudaSuccess ? cudaGetErrorString(e) : "wrong contents");
+            return fail(ctx, PT_ERR_CUDA, buf);
+        }
+        ps.block[r] = (unsigned char*)p;
+    }
+    if (const char* t = getenv("PTB200_PEER_TIMEOUT_MS")) ctx->peer.timeoutNs = (unsigned long long)atof(t) * 1000000ull;
+    ctx->peer.ps = ps; ctx->peer.epoch = 0; ctx->peer.on = true;
+    return PT_OK;
+}
+PT_API int pt_peer_disconnect(pt_ctx* ctx) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    CK(cudaStreamSynchronize(ctx->stream));
+    peerClose(ctx);
     return PT_OK;
 }
 

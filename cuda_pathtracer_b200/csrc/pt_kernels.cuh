@@ -479,4 +479,121 @@ __global__ void __launch_bounds__(256) k_rc_propagate(float4* rc, float* add, ui
     }
 }
 
+// ---- multi-GPU: reduce + propagate + broadcast over NVLink peer memory in place of all-reduce + propagate -----------------
+// Every rank maps every peer's radiance-cache block (cudaIpc, pt_peer_connect).  Triangles are split into `world`
+// contiguous ranges; the OWNER of a range reads all ranks' additions for it straight out of their HBM (fixed rank order:
+// deterministic sums), runs the reference's propagate step once (kernels.h:884-905) and stores the new radianceCache[8] /
+// radianceTotal into every rank's copy.  Per rank and frame that moves 64 B/triangle in and <= 48 B/triangle out over
+// NVLink instead of the ~2 x 64 B of a ring all-reduce, needs no intermediate buffer, and the cross-GPU ordering is three
+// flag words per peer:  arrive[r] = "rank r's additions of this epoch are complete",  done[r] = "owner r has read every
+// rank's additions and written every rank's cache".  Flags live at the head of each rank's block and are written by the
+// peers with release stores at system scope; waiting is a bounded spin (a missing peer sets an error word, never hangs).
+#define PT_PEER_MAX 16
+#define PT_PEER_ARRIVE 0        /* uint[16] at the head of the block */
+#define PT_PEER_DONE 64         /* uint[16] */
+#define PT_PEER_COUNTER 128     /* blocks of k_peer_reduce_propagate that finished */
+#define PT_PEER_ERROR 129       /* set when a wait timed out */
+#define PT_PEER_MAGIC 130       /* 0x50544230 + rank, checked by pt_peer_connect through the mapped pointer */
+struct PeerSet {
+    unsigned char* block[PT_PEER_MAX];      // base of every rank's block (own rank: the local pointer)
+    uint rank, world;
+    size_t addOffset, rcOffset;             // byte offsets of rcAdditions / rcRadiance inside a block (same on every rank)
+};
+__device__ __forceinline__ uint* peerFlags(const PeerSet& ps, uint r) { return reinterpret_cast<uint*>(ps.block[r]); }
+__device__ __forceinline__ void stReleaseSys(uint* p, uint v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint ldAcquireSys(const uint* p) { uint v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ float ldPeer(const float* p) { float v; asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ void stPeer4(float4* p, float4 v) { asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory"); }
+__device__ __forceinline__ unsigned long long globalTimerNs() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+// threads 0..world-1 of the block wait until flag word [base + t] of the LOCAL block has reached `epoch`
+__device__ __forceinline__ void peerWait(const PeerSet& ps, uint base, uint epoch, unsigned long long timeoutNs) {
+    if (threadIdx.x < ps.world) {
+        uint* f = peerFlags(ps, ps.rank);
+        const unsigned long long t0 = globalTimerNs();
+        while ((int)(ldAcquireSys(f + base + threadIdx.x) - epoch) < 0) {
+            if (globalTimerNs() - t0 > timeoutNs) { atomicExch(f + PT_PEER_ERROR, 1u + base + threadIdx.x); break; }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+}
+__global__ void k_peer_arrive(PeerSet ps, uint epoch) {
+    __threadfence_system();                                  // this rank's k_rc_update (previous kernel on the stream) before the flag
+    if (threadIdx.x < ps.world) stReleaseSys(peerFlags(ps, threadIdx.x) + PT_PEER_ARRIVE + ps.rank, epoch);
+}
+__global__ void __launch_bounds__(256) k_peer_reduce_propagate(PeerSet ps, uint epoch, uint T, uint lo, uint hi, unsigned long long timeoutNs) {
+    peerWait(ps, PT_PEER_ARRIVE, epoch, timeoutNs);
+    const uint i = lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < hi) {
+        float cnt[8], en[8];
+#pragma unroll
+        for (uint t = 0; t < 8; t++) { cnt[t] = 0.0f; en[t] = 0.0f; }
+        // Fixed rank order: the sums do not depend on arrival order.  NVLink round trips are the cost here, so the loads
+        // are issued in batches that do not wait for each other: the 8 counts of rank r+1 go out before the energies of
+        // rank r are requested (only where the count is non-zero: a zero count means a zero energy sum).
+        float cNext[8];
+        {
+            const float* add0 = reinterpret_cast<const float*>(ps.block[0] + ps.addOffset);
+#pragma unroll
+            for (uint t = 0; t < 8; t++) cNext[t] = ldPeer(add0 + (size_t)(8 + t) * T + i);
+        }
+        for (uint r = 0; r < ps.world; r++) {
+            const float* add = reinterpret_cast<const float*>(ps.block[r] + ps.addOffset);
+            float c[8], e[8];
+#pragma unroll
+            for (uint t = 0; t < 8; t++) c[t] = cNext[t];
+            if (r + 1 < ps.world) {
+                const float* addN = reinterpret_cast<const float*>(ps.block[r + 1] + ps.addOffset);
+#pragma unroll
+                for (uint t = 0; t < 8; t++) cNext[t] = ldPeer(addN + (size_t)(8 + t) * T + i);
+            }
+#pragma unroll
+            for (uint t = 0; t < 8; t++) { e[t] = 0.0f; if (c[t] != 0.0f) e[t] = ldPeer(add + (size_t)t * T + i); }
+#pragma unroll
+            for (uint t = 0; t < 8; t++) { cnt[t] += c[t]; en[t] += e[t]; }
+        }
+        float4* rc = reinterpret_cast<float4*>(ps.block[ps.rank] + ps.rcOffset);
+        const float4 r0 = rc[(size_t)i * 3], r1 = rc[(size_t)i * 3 + 1], r2 = rc[(size_t)i * 3 + 2];
+        float v[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+        float total = r2.x;
+        const float alpha = 0.95f;
+        bool dirty = false;
+#pragma unroll
+        for (uint t = 0; t < 8; t++) {                       // kernels.h:890-903, as k_rc_propagate
+            if (cnt[t] < PT_EPS) continue;
+            const float oldValue = v[t];
+            const float incomingEnergy = en[t] / cnt[t];
+            const float newValue = clampf(alpha * oldValue + (1 - alpha) * incomingEnergy, 0.1f, 2.0f);
+            total += newValue - oldValue;
+            v[t] = newValue;
+            dirty = true;
+        }
+        if (dirty)
+            for (uint r = 0; r < ps.world; r++) {
+                float4* dst = reinterpret_cast<float4*>(ps.block[r] + ps.rcOffset) + (size_t)i * 3;
+                stPeer4(dst, make_float4(v[0], v[1], v[2], v[3]));
+                stPeer4(dst + 1, make_float4(v[4], v[5], v[6], v[7]));
+                stPeer4(dst + 2, make_float4(total, 0.0f, 0.0f, 0.0f));
+            }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint* f = peerFlags(ps, ps.rank);
+        if (atomicAdd(f + PT_PEER_COUNTER, 1u) == gridDim.x - 1u) {             // last block of this owner: tell every rank
+            f[PT_PEER_COUNTER] = 0u;
+            __threadfence_system();
+            for (uint r = 0; r < ps.world; r++) stReleaseSys(peerFlags(ps, r) + PT_PEER_DONE + ps.rank, epoch);
+        }
+    }
+}
+// Once every owner is done nobody reads this rank's additions any more: clear them for the next frame (k_rc_propagate
+// clears the entries it consumed; untouched ones are zero already, so the state is the same).
+__global__ void __launch_bounds__(256) k_peer_finish(PeerSet ps, uint epoch, uint T, unsigned long long timeoutNs) {
+    peerWait(ps, PT_PEER_DONE, epoch, timeoutNs);
+    float* add = reinterpret_cast<float*>(ps.block[ps.rank] + ps.addOffset);
+    const size_t n = (size_t)16 * T;
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) add[k] = 0.0f;
+}
+
 }  // namespace ptb

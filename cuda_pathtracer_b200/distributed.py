@@ -1,8 +1,10 @@
 """Multi-GPU plumbing: one process per GPU, image tiles dealt round-robin to ranks (pt_config.rank /
-world_size), scene replicated, and ONE collective per guiding-training frame: an in-place SUM all-reduce of
-the radiance-cache additions (additionCache || additionCacheCount, 16 floats per triangle) between the
-local update and the propagate step (reference kernels: src/kernels.h:863-905).
-torch.distributed is the transport (NCCL over NVLink on GPUs, gloo in the CPU tests)."""
+world_size), scene replicated, and ONE exchange per guiding-training frame: the radiance-cache additions
+(additionCache || additionCacheCount, 16 floats per triangle) are summed over the ranks between the local
+update and the propagate step (reference kernels: src/kernels.h:863-905).  Two transports:
+connect_peers() -- the library's own fused reduce + propagate + broadcast kernel over NVLink peer memory (default on
+one box); make_allreduce_hook() -- an in-place SUM all-reduce through torch.distributed (NCCL on GPUs, gloo in the
+CPU tests) followed by the local propagate kernel."""
 import ctypes as C
 
 import numpy as np
@@ -47,6 +49,36 @@ def make_allreduce_hook(device, stream=None, group=None):
             dist.all_reduce(t, group=group)
         return 0
     return hook
+
+
+def connect_peers(pt, device=None, group=None):
+    """Switches the radiance-cache exchange of `pt` to the fused reduce + propagate kernel over NVLink peer memory
+    (pt_peer_export / pt_peer_connect): the cudaIpc handles travel through one all_gather, after that the data path
+    never touches NCCL.  Every rank of the group must call it after Init().  Returns True when every rank mapped every
+    peer; otherwise every rank stays on (or falls back to) the all-reduce hook and False is returned."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    handles = [None] * world
+    dist.all_gather_object(handles, pt.peer_export(), group=group)
+    ok = True
+    try:
+        pt.peer_connect(handles)
+    except Exception:                                    # noqa: BLE001 -- reported through the return value on every rank
+        ok = False
+    oks = [None] * world
+    dist.all_gather_object(oks, ok, group=group)
+    if not all(oks):
+        pt.peer_disconnect()
+        return False
+    return True
+
+
+def disconnect_peers(pt, group=None):
+    """Unmaps the peers' blocks; collective (a barrier on both sides keeps a rank from freeing a block in use)."""
+    import torch.distributed as dist
+    dist.barrier(group=group)
+    pt.peer_disconnect()
+    dist.barrier(group=group)
 
 
 def gather_image(local_image, group=None):

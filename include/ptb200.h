@@ -197,6 +197,15 @@ PT_API int  pt_set_sky_constant(pt_ctx*, float r, float g, float b);            
 PT_API int  pt_set_blue_noise(pt_ctx*, const float* lum, uint32_t w, uint32_t h); /* ~ loadTextureL (use_cuda.h:166-200) */
 PT_API int  pt_texture_create(pt_ctx*, const float* rgba, uint32_t w, uint32_t h, uint64_t* out_handle); /* ~ loadTexture (use_cuda.h:108-164) */
 PT_API int  pt_set_allreduce_hook(pt_ctx*, pt_allreduce_hook hook, void* user);
+/* Multi-GPU exchange over NVLink peer memory, the default transport of the radiance-cache step on one box (replaces the
+ * hook + propagate pair == what kernel_update_buckets -> [all-reduce] -> kernel_propagate_buckets needs, kernels.h:863-905):
+ * every rank exports the cudaIpc handle of its radiance-cache block, the caller gathers the handles of all ranks in rank
+ * order (any transport) and hands them to pt_peer_connect; training frames then run ONE fused reduce + propagate +
+ * broadcast kernel per rank over the peers' HBM.  All ranks must render the same sequence of frames. */
+#define PT_PEER_HANDLE_BYTES 64
+PT_API int  pt_peer_export(pt_ctx*, void* handle_out /* PT_PEER_HANDLE_BYTES */);
+PT_API int  pt_peer_connect(pt_ctx*, const void* handles /* world_size x PT_PEER_HANDLE_BYTES, rank order */, uint32_t world_size);
+PT_API int  pt_peer_disconnect(pt_ctx*);
 
 PT_API int  pt_render(pt_ctx*, const pt_camera*, int should_clear);   /* == Pathtracer::Render (pathtracer.h:224-302); asynchronous */
 PT_API int  pt_join(pt_ctx*);                                         /* asynchronous: orders every render enqueued so far before later work on pt_cuda_stream() (e.g. a timing event) */

@@ -1,0 +1,84 @@
+"""-m gpu: the radiance-cache exchange over peer memory (pt_peer_export / pt_peer_connect, k_peer_arrive /
+k_peer_reduce_propagate / k_peer_finish) against the plain propagate step (reference src/kernels.h:884-905).
+world 1: the fused kernel must give the SAME bits as k_rc_propagate.  world 2: two processes on the one GPU of the test
+box map each other's block through cudaIpc and run the real protocol (flags, owner ranges, broadcast); checked against
+the all-reduce hook and against one rank (tools/multi_gpu_check.py --same-gpu)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from cuda_pathtracer_b200 import abi, api, scenes
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def run(arrays, cam, cfg, frames, peer):
+    pt = api.Pathtracer(arrays, cfg).Init()
+    if peer:
+        pt.peer_connect([pt.peer_export()])
+    pt.HNEE, pt.HCACHE = True, True
+    pt.Render(cam, shouldClear=True)
+    for _ in range(frames):
+        pt.Render(cam)
+    pt.Finish()
+    img = pt.read_image().copy()
+    rc = pt.read_radiance_cache().copy()
+    pt.close()
+    return img, rc
+
+
+def rel_rmse(a, b):
+    return float(np.sqrt(np.mean((a.astype(np.float64) - b) ** 2)) / max(1e-12, np.sqrt(np.mean(b.astype(np.float64) ** 2))))
+
+
+def test_world1_fused_exchange_matches_propagate():
+    """The float atomics of the update step are unordered, so two runs of the SAME configuration already differ in the
+    last bits (and then in the paths the cache steers): the fused kernel has to agree with the plain propagate step as
+    well as the plain step agrees with itself (bounds as tests/test_gpu_render.py uses for guiding)."""
+    W, H = 256, 144
+    arrays = scenes.sibenik_scene().arrays()
+    cam = scenes.camera_sweep("sibenik", W, H, 16)[5]
+    cfg = abi.default_config(W, H, max_ray_depth=8, interactive_depth=1)
+    a_img, a_rc = run(arrays, cam, cfg, 24, False)
+    a2_img, a2_rc = run(arrays, cam, cfg, 24, False)
+    b_img, b_rc = run(arrays, cam, cfg, 24, True)
+    assert np.any(a_rc["radianceCache"] != np.float32(0.1)), "the cache did not train"
+    self_img, self_rc = rel_rmse(a2_img[..., :3], a_img[..., :3]), rel_rmse(a2_rc["radianceCache"], a_rc["radianceCache"])
+    peer_img, peer_rc = rel_rmse(b_img[..., :3], a_img[..., :3]), rel_rmse(b_rc["radianceCache"], a_rc["radianceCache"])
+    print("run-to-run: image %.3g cache %.3g; fused vs plain: image %.3g cache %.3g" % (self_img, self_rc, peer_img, peer_rc))
+    assert np.array_equal(a_img[..., 3], b_img[..., 3])
+    assert peer_img <= max(2e-2, 3 * self_img) and peer_rc <= max(2e-2, 3 * self_rc)
+    assert np.all(b_rc["additionCache"] == 0) and np.all(b_rc["additionCacheCount"] == 0)      # cleared for the next frame
+    assert np.allclose(b_rc["radianceCache"].sum(axis=1), b_rc["radianceTotal"], rtol=1e-3)
+
+
+def test_peer_connect_rejects_wrong_world_and_missing_scene():
+    cfg = abi.default_config(64, 64, max_ray_depth=4, interactive_depth=1)
+    arrays = scenes.teapot_like_scene(8).arrays()
+    pt = api.Pathtracer(arrays, cfg).Init()
+    h = pt.peer_export()
+    assert len(h) == 64
+    with pytest.raises(api.PtError):
+        pt.peer_connect([h, h])                     # world_size is 1 in the config
+    pt.peer_connect([h]); pt.peer_disconnect()
+    pt.close()
+
+
+def test_two_processes_one_gpu_peer_protocol():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ, PTB200_PEER_TIMEOUT_MS="20000")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tools", "multi_gpu_check.py"), "--same-gpu", "--frames", "20", "--size", "256x144"]
+    p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=420)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
+    line = [l for l in p.stdout.splitlines() if l.startswith("{")][-1]
+    r = json.loads(line)
+    assert r["ok"], r
+    assert r["guiding_off"]["bit_identical"]
+    assert r["guiding_on_peer"]["caches_replicated_bitwise"] and r["guiding_on_peer"]["rel_rmse"] < 2e-2
