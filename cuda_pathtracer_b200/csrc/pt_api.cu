@@ -693,6 +693,13 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         }
         // image / albedo / statistics / radiance-cache updates happen in sample order
         if (pipelined && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
+        auto accumulate = [&]() -> int {
+            if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0));    // a read-back in flight still reads the image
+            if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
+                              ctx->launches++, k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
+            return PT_OK;
+        };
+        bool accumulated = false;
         if (training) {                                                                    // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING, s);
             ctx->launches++, k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
@@ -703,6 +710,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
                 const uint32_t T = ctx->sc.num_triangles, epoch = ++ctx->peer.epoch;
                 const uint32_t lo = (uint32_t)((uint64_t)T * ps.rank / ps.world), hi = (uint32_t)((uint64_t)T * (ps.rank + 1) / ps.world);
                 ctx->launches++, k_peer_arrive<<<1, 32, 0, s>>>(ps, epoch);
+                if (!ctx->prof) { int ar = accumulate(); if (ar) return ar; accumulated = true; }   // the image update fills the wait for the slowest rank
                 ctx->launches++, k_peer_reduce_propagate<<<std::max(1u, (hi - lo + 255u) / 256u), 256, 0, s>>>(ps, epoch, T, lo, hi, ctx->peer.timeoutNs);
                 ctx->launches++, k_peer_finish<<<(unsigned)std::min<size_t>(296, ((size_t)16 * T + 255) / 256), 256, 0, s>>>(ps, epoch, T, ctx->peer.timeoutNs);
             } else {
@@ -713,9 +721,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
                 ctx->launches++, k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             }
         }
-        if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0));    // a read-back in flight still reads the image
-        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
-                          ctx->launches++, k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
+        if (!accumulated) { int ar = accumulate(); if (ar) return ar; }
         if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
         ctx->prevTraining = training;
         ctx->sampleIdx++;                                                                  // :300
