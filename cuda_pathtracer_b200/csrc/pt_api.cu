@@ -73,7 +73,7 @@ struct pt_ctx {
     int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0, gridTail = 0;
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
-    uint32_t knobMinWidth = 0; bool knobNoTailWait = false;   // developer knobs (environment, read in pt_create)
+    uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     // per-stage timing (pt_set_profiling): CUDA event pairs around every stage launch, resolved in pt_finish
     bool prof = false;
     std::vector<cudaEvent_t> evPool;
@@ -302,6 +302,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if (const char* e = getenv("PTB200_TAIL_BOUNCE")) { ctx->tailBounce = std::max(1, atoi(e)); ctx->tailForced = true; }      // developer knob (tools/tune.sh)
         if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->knobMinWidth = (uint32_t)std::max(1, std::min(32, atoi(e)));          // developer knobs, read once
         ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
+        ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
         CK(cudaStreamSynchronize(ctx->stream));
         return PT_OK;
     };
@@ -633,6 +634,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // 1/8-image shard), the other samples in flight fill the machine.
         ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
         if (ctx->knobMinWidth) ctx->sc.minWidth = ctx->knobMinWidth;
+        ctx->sc.tailPair = (ctx->sc.minWidth < 32u && !ctx->knobNoTailPair) ? 1u : 0u;     // latency mode only: a sample that runs alone
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.

@@ -102,6 +102,7 @@ struct DScene {
     float* rcAdditions;         // SoA [16][num_triangles]: additionCache[8] then additionCacheCount[8]
     uint num_triangles, num_instances, num_spheres, num_planes, num_lights;
     uint minWidth;              // scheduling: least number of rays a warp claims from a short queue (1..32)
+    uint tailPair;              // scheduling: k_tail may give a path two lanes (extension + shadow ray in parallel) when the queue is short
 };
 
 struct DCamera { float3 eye, viewDir, lt, u, v; float d, focalLength, aperture; };

@@ -197,12 +197,25 @@ __global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P
 #ifndef PT_TAIL_MINBLOCKS
 #define PT_TAIL_MINBLOCKS 3
 #endif
+__device__ __forceinline__ float4 shfl4(const float4 v, const uint src) {
+    return make_float4(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src), __shfl_sync(0xffffffffu, v.w, src));
+}
+// Pair mode (sc.tailPair, chosen per launch when the paths fit the machine 16 to a warp): a path owns TWO lanes.  The even
+// lane carries the extension rays and shades; the shadow ray of bounce b is handed (shuffles) to the odd lane, which traces
+// it WHILE the even lane traces the extension ray of bounce b+1 -- the two are independent once shade(b) has run, exactly
+// the pairing k_trace_pair gives the wavefront.  The even lane shades bounce b+1 only after its helper has finished
+// connect(b), so the float additions into accucolor keep the wavefront's (the reference's) order: identical bits.  A lone
+// sample on a small shard is latency bound and has the lanes to spare: the per-bounce latency becomes
+// max(extend, connect) + shade instead of their sum.
 __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, Queues q, int inBuf, int b0, int maxBounces, uint* cursor) {
     const DScene& sc = P.sc;
     const uint n = q.cnt[CNT_EXT(b0)];
     const uint lane = laneId();
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
-    const uint width = min(32u, max(max(1u, sc.minWidth), (n + totalWarps - 1u) / totalWarps));
+    const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * 16u;
+    const bool isHelper = pair && (lane & 1u) != 0u;
+    const uint ownerMask = pair ? 0x55555555u : 0xffffffffu;
+    const uint width = min(pair ? 16u : 32u, max(max(1u, pair ? 1u : sc.minWidth), (n + totalWarps - 1u) / totalWarps));
     uint2 stack[PT_STACK];
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
@@ -213,9 +226,17 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
     auto loadCur = [&](float4& o4, float4& d4) {
         if (any) { o4 = q.shO[L.ray]; d4 = q.shD[L.ray]; } else { o4 = q.rayO[buf][L.ray]; d4 = q.rayD[buf][L.ray]; }
     };
+    auto addLight = [&]() {                                                     // unoccluded: kernels.h:806-809
+        const uint slot = __float_as_uint(q.shD[L.ray].w);
+        const float4 l = P.lights[slot];
+        float4 a = P.accucolors[slot];
+        a.x += l.x; a.y += l.y; a.z += l.z;
+        P.accucolors[slot] = a;
+    };
     while (true) {
-        // ---- F: idle lanes claim new paths ----
-        const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
+        // ---- F: idle lanes (pair mode: idle even lanes) claim new paths ----
+        const uint activeAll = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
+        const uint activeMask = activeAll & ownerMask;
         const uint nActive = __popc(activeMask);
         if (!exhausted && nActive < width) {
             const uint want = width - nActive;
@@ -223,25 +244,31 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
             if (lane == 0) base = atomicAdd(cursor, want);
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base + want >= n) exhausted = true;
-            const uint r = __popc(~activeMask & ((1u << lane) - 1u));
-            if (L.ray == PT_NONE && r < want && base + r < n) {
+            const uint r = __popc(~activeAll & ownerMask & ((1u << lane) - 1u));
+            if (!isHelper && L.ray == PT_NONE && r < want && base + r < n) {
                 L.ray = base + r; bounce = b0; buf = inBuf; any = false; extPending = false;
                 float4 o4, d4; loadCur(o4, d4);
                 rayDone = !beginRay(sc, L, o4, d4, false);
             }
-        } else if (nActive == 0) break;
+        } else if (activeAll == 0u) break;
         // ---- C: a finished ray continues its path: shade, then the shadow ray, then the next extension ray ----
-        while (L.ray != PT_NONE && rayDone) {
+        bool helperBusy = false;
+        if (pair) {
+            if (isHelper && L.ray != PT_NONE && rayDone) {                      // the helper's shadow ray is done
+                if (L.hitId == PT_NONE) addLight();
+                L.ray = PT_NONE; rayDone = false;
+            }
+            __syncwarp();                                                       // its accucolor update before the owner's next shade
+            helperBusy = __shfl_xor_sync(0xffffffffu, (int)(L.ray != PT_NONE), 1) != 0;
+        }
+        bool handoff = false;
+        uint hpath = PT_NONE;
+        float4 hso = make_float4(0.f, 0.f, 0.f, 0.f), hsd = hso;
+        while (!isHelper && L.ray != PT_NONE && rayDone && !helperBusy && !handoff) {
             rayDone = false;
             bool startExt = false;
             if (any) {
-                if (L.hitId == PT_NONE) {                                       // unoccluded: kernels.h:806-809
-                    const uint slot = __float_as_uint(q.shD[L.ray].w);
-                    const float4 l = P.lights[slot];
-                    float4 a = P.accucolors[slot];
-                    a.x += l.x; a.y += l.y; a.z += l.z;
-                    P.accucolors[slot] = a;
-                }
+                if (L.hitId == PT_NONE) addLight();
                 any = false;
                 startExt = extPending;
             } else {
@@ -262,8 +289,8 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
                     const float4 so4 = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
                     const float4 sd4 = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
                     q.shO[L.ray] = so4; q.shD[L.ray] = sd4;
-                    any = true;
-                    rayDone = !beginRay(sc, L, so4, sd4, true);
+                    if (pair) { handoff = true; hpath = L.ray; hso = so4; hsd = sd4; startExt = extPending; }
+                    else { any = true; rayDone = !beginRay(sc, L, so4, sd4, true); }
                 } else startExt = extPending;
             }
             if (startExt) {
@@ -272,8 +299,16 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
                 rayDone = !beginRay(sc, L, o4, d4, false);
             } else if (!any) L.ray = PT_NONE;                                    // path ended
         }
+        if (pair) {                                                             // hand the new shadow rays to the helpers
+            const uint src = lane & ~1u;
+            const bool take = __shfl_sync(0xffffffffu, (int)handoff, src) != 0;
+            const uint path = __shfl_sync(0xffffffffu, hpath, src);
+            const float4 o4 = shfl4(hso, src), d4 = shfl4(hsd, src);
+            __syncwarp();                                                       // q.shO/shD[path] (re-read when an instance is left) written by the owner
+            if (isHelper && take) { L.ray = path; any = true; rayDone = !beginRay(sc, L, o4, d4, true); }
+        }
         // ---- T: top level ----
-        if (L.ray != PT_NONE && !hasBlasWork(L)) rayDone = tlasTrip(sc, L, stack, loadCur);
+        if (L.ray != PT_NONE && !rayDone && !hasBlasWork(L)) rayDone = tlasTrip(sc, L, stack, loadCur);
         // ---- B: bottom level ----
         const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
         const uint minKeep = max(1u, (nB * PT_KEEP_NUM + PT_KEEP_DEN - 1u) / PT_KEEP_DEN);

@@ -290,6 +290,31 @@ def test_write_pfm_and_sample_pipelining_are_invisible(sibenik_small, tmp_path):
         assert imgs[0][2] == other[2] and imgs[0][3] == other[3]
 
 
+@pytest.mark.parametrize("size,depth", [((192, 108), 8), ((640, 360), 12)])
+def test_tail_kernel_with_paired_shadow_lanes_is_invisible(sibenik_small, size, depth):
+    """k_tail in pair mode (a sample that runs alone, NEE on, short queue: the shadow ray of bounce b is traced by the
+    neighbour lane while the path's own lane traces the extension ray of bounce b+1) against the wavefront-only
+    schedule: same bits, same ray counts -- the helper's accucolor update is ordered before the next shade."""
+    w, h = size
+    cam = scenes.camera_sweep("sibenik", w, h, 16)[3]
+    res = []
+    for flags in (2, 1 | 2, 2 | ((1 + 1) << 8)):      # NO_PIPELINE (k_tail from bounce 3, paired); + WAVEFRONT_ONLY; k_tail from bounce 1
+        cfg = abi.default_config(w, h, max_ray_depth=depth, interactive_depth=1, flags=flags)
+        pt = api.Pathtracer(sibenik_small, cfg).Init()
+        pt.HNEE, pt.HCACHE = True, False
+        pt.Render(cam, shouldClear=True)
+        for _ in range(5):
+            pt.Render(cam)
+        pt.Finish()
+        st = pt.stats()
+        res.append((pt.read_image().copy(), pt.read_image(1).copy(), st.extend_rays, st.shadow_rays))
+        pt.close()
+    assert res[0][3] > 0
+    for other in res[1:]:
+        assert np.array_equal(res[0][0], other[0]) and np.array_equal(res[0][1], other[1])
+        assert res[0][2] == other[2] and res[0][3] == other[3]
+
+
 @pytest.mark.parametrize("blur", [True, False])
 def test_display_postprocess_matches_shader_restatement(sibenik_small, blur):
     """gauss_horz / gauss_vert / quad_fs(_blurred) (main.cpp:46-171) as CUDA kernels vs the CPU
