@@ -628,7 +628,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         cudaStream_t s = pipelined ? S.stream : ctx->stream;
         ctx->lastSet = pipelined ? ctx->cur : -1;
         if (pipelined) ctx->cur = (ctx->cur + 1) % ctx->nSets;
-        const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles && map.nSlots;   // :292
+        const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles;   // :292 (a rank without pixels still takes part in the exchange)
         // Short queues: a sample that runs alone (clearing / profiled / cache-training frames) spreads its rays over all
         // warps (latency); samples that overlap others keep their warps full (throughput: 0.41 -> 0.32 ms/sample on a
         // 1/8-image shard), the other samples in flight fill the machine.
@@ -704,7 +704,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         bool accumulated = false;
         if (training) {                                                                    // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING, s);
-            ctx->launches++, k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            if (map.nSlots) ctx->launches++, k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             if (ctx->peer.on) {
                 // reduce + propagate + broadcast over peer memory (pt_kernels.cuh): the owner of a triangle range sums every
                 // rank's additions out of their HBM, propagates once and stores the result into every rank's cache

@@ -70,11 +70,12 @@ def test_peer_connect_rejects_wrong_world_and_missing_scene():
     pt.close()
 
 
-def test_two_processes_one_gpu_peer_protocol():
+@pytest.mark.parametrize("size", ["256x144", "32x32"])          # 32x32: one tile, rank 1 has no pixels but still takes part in the exchange
+def test_two_processes_one_gpu_peer_protocol(size):
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     env = dict(os.environ, PTB200_PEER_TIMEOUT_MS="20000")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", str(port), os.path.join(ROOT, "tools", "multi_gpu_check.py"), "--same-gpu", "--frames", "20", "--size", "256x144"]
+           "--master-port", str(port), os.path.join(ROOT, "tools", "multi_gpu_check.py"), "--same-gpu", "--frames", "20", "--size", size]
     p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=420)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
     line = [l for l in p.stdout.splitlines() if l.startswith("{")][-1]
