@@ -69,7 +69,7 @@ struct pt_ctx {
     // gives the peers everything the fused reduce+propagate needs (pt_peer_export / pt_peer_connect)
     unsigned char* rcBlock = nullptr;
     size_t rcAddOffset = 0, rcRcOffset = 0;
-    struct Peers { bool on = false; PeerSet ps; void* opened[PT_PEER_MAX] = {}; uint32_t epoch = 0; unsigned long long timeoutNs = 10000000000ull; } peer;
+    struct Peers { bool on = false; PeerSet ps; void* opened[PT_PEER_MAX] = {}; uint32_t epoch = 0; unsigned long long timeoutNs = 30000000000ull; } peer;
     int gridTraceExt = 0, gridTraceAny = 0, gridShade = 0, gridTail = 0;
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too

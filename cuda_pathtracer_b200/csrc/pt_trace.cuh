@@ -4,6 +4,9 @@
 // bit-identical for every triangle that is tested.
 #pragma once
 #include "pt_device.cuh"
+#if defined(PT_BYTE_HALF)
+#include <cuda_fp16.h>
+#endif
 
 namespace ptb {
 
@@ -19,6 +22,14 @@ __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 // one more instruction per value; measured slower on B200 (tune run r1e), kept as a build knob.
 #if defined(PT_BYTE_PRMT)
 __device__ __forceinline__ float byteToFloat(uint x, uint j) { return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7540u + j)) - 8388608.0f; }
+#elif defined(PT_BYTE_HALF)
+// Tuning variant: bytes j, j+1 of x become the half2 {1024 + b_j, 1024 + b_j+1} with one PRMT (0x64 in the exponent byte), each
+// half widens to float on the FMA pipe (HADD2.F32); the caller folds the 1024 into the FMA's addend.
+__device__ __forceinline__ float byteToFloat(uint x, uint j) {
+    const uint h2 = __byte_perm(x, 0x64646464u, j < 2 ? 0x4140u : 0x4342u);
+    const __half2 h = *reinterpret_cast<const __half2*>(&h2);
+    return (j & 1u) ? __high2float(h) : __low2float(h);
+}
 #else
 __device__ __forceinline__ float byteToFloat(uint x, uint j) { return (float)((x >> (j * 8u)) & 0xffu); }
 #endif
@@ -216,7 +227,11 @@ __device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, uin
     const uint ew = __float_as_uint(n0.w);
     const float sx = __uint_as_float((ew & 0xffu) << 23), sy = __uint_as_float(((ew >> 8) & 0xffu) << 23), sz = __uint_as_float(((ew >> 16) & 0xffu) << 23);
     const float aix = sx * L.idir.x, aiy = sy * L.idir.y, aiz = sz * L.idir.z;
+#if defined(PT_BYTE_HALF)
+    const float aox = __fmaf_rn(-1024.0f, aix, (n0.x - L.o.x) * L.idir.x), aoy = __fmaf_rn(-1024.0f, aiy, (n0.y - L.o.y) * L.idir.y), aoz = __fmaf_rn(-1024.0f, aiz, (n0.z - L.o.z) * L.idir.z);
+#else
     const float aox = (n0.x - L.o.x) * L.idir.x, aoy = (n0.y - L.o.y) * L.idir.y, aoz = (n0.z - L.o.z) * L.idir.z;
+#endif
     const uint octinv4 = L.octinv * 0x01010101u;
     const bool negx = L.d.x < 0.0f, negy = L.d.y < 0.0f, negz = L.d.z < 0.0f;
     uint hitmask = 0;

@@ -5,5 +5,5 @@ mkdir -p gpurun_out
 for e in "$@"; do
   echo "== world $WORLD env $e" | tee -a gpurun_out/${TAG}_shard.log
   [ "$e" = "-" ] && e=""
-  env $e python tools/shard_probe.py $WORLD 100 2>&1 | tail -4 | tee -a gpurun_out/${TAG}_shard.log
+  env $e python tools/shard_probe.py $WORLD 100 2>&1 | tail -5 | tee -a gpurun_out/${TAG}_shard.log
 done
