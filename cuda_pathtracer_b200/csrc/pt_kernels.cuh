@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
     const bool isHelper = pair && (lane & 1u) != 0u;
     const uint ownerMask = pair ? 0x55555555u : 0xffffffffu;
     const uint width = min(pair ? 16u : 32u, max(max(1u, pair ? 1u : sc.minWidth), (n + totalWarps - 1u) / totalWarps));
-    uint2 stack[PT_STACK];
+    TravStack stack; stack.init();
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     int bounce = b0, buf = inBuf;

@@ -90,6 +90,9 @@ __device__ __forceinline__ bool triIntersect(float3 o, float3 d, float3 v0, floa
 
 
 #define PT_STACK 40            /* unified stack: TLAS entries below the node groups of the instance being traversed */
+#ifndef PT_SMEM_STACK
+#define PT_SMEM_STACK 0        /* tuning variant: the first PT_SMEM_STACK entries of every lane's stack live in shared memory */
+#endif
 #define PT_NONE 0xffffffffu
 #ifndef PT_TRIS_PER_ITER
 #define PT_TRIS_PER_ITER 2     /* triangle tests a lane performs per loop trip before node work resumes */
@@ -101,6 +104,27 @@ __device__ __forceinline__ bool triIntersect(float3 o, float3 d, float3 v0, floa
 #define PT_KEEP_NUM 1          /* the bottom-level loop runs while >= PT_KEEP_NUM/PT_KEEP_DEN of the lanes that */
 #define PT_KEEP_DEN 32         /* entered it still have bottom-level work; the others wait for the next top-level phase */
 #endif
+
+// The traversal stack of one lane.  Default: a local-memory array (L1-resident).  With PT_SMEM_STACK = n the n entries
+// nearest the bottom sit in shared memory, one column per thread (entry i of thread t at [i][t]: conflict-free 8-byte
+// accesses), deeper entries in local memory.  All trace kernels run 128-thread blocks.
+struct TravStack {
+#if PT_SMEM_STACK > 0
+    uint2* sh;
+    uint2 loc[PT_STACK - PT_SMEM_STACK];
+    __device__ __forceinline__ void init() {
+        __shared__ uint2 shStack[PT_SMEM_STACK * 128];
+        sh = shStack + threadIdx.x;
+    }
+    __device__ __forceinline__ void push(int& sp, const uint2 v) { if (sp < PT_SMEM_STACK) sh[sp * 128] = v; else loc[sp - PT_SMEM_STACK] = v; sp++; }
+    __device__ __forceinline__ uint2 pop(int& sp) { --sp; return sp < PT_SMEM_STACK ? sh[sp * 128] : loc[sp - PT_SMEM_STACK]; }
+#else
+    uint2 loc[PT_STACK];
+    __device__ __forceinline__ void init() {}
+    __device__ __forceinline__ void push(int& sp, const uint2 v) { loc[sp++] = v; }
+    __device__ __forceinline__ uint2 pop(int& sp) { return loc[--sp]; }
+#endif
+};
 
 // Per-lane traversal state.  A lane is idle (ray == PT_NONE), in the top level (curT / TLAS entries
 // on the stack), or inside an instance (ngroup / tgroup / node groups above spBase on the stack).
@@ -185,7 +209,7 @@ __device__ __forceinline__ bool beginRay(const DScene& sc, LaneState& L, const f
 
 // One top-level step for the TLAS node L.curT (kernels.h:320-386): a leaf enters its instance
 // (transformRay, kernels.h:81-86), an inner node tests both children in the reference's order.
-__device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, uint2* stack) {
+__device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, TravStack& stack) {
     const pt_tlas_node cur = sc.tlas[L.curT];
     L.curT = PT_NONE;
     if (cur.children == 0) {
@@ -206,7 +230,7 @@ __device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, uint2* 
         const bool bfar = slabTestRef(L.o, L.idir, &ff.vmin.x, &ff.vmax.x, tfar) && tfar < L.tbest;
         if (bnear && bfar) {
             const bool rev = tnear > tfar;
-            stack[L.sp++] = make_uint2(rev ? near_id : far_id, 0u);
+            stack.push(L.sp, make_uint2(rev ? near_id : far_id, 0u));
             L.curT = rev ? far_id : near_id;
         } else if (bnear) L.curT = near_id;
         else if (bfar) L.curT = far_id;
@@ -215,11 +239,11 @@ __device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, uint2* 
 
 // One bottom-level step: take the nearest pending child of the node group, intersect its 8 quantised
 // child boxes (Ylitie et al. 2017), producing a new node group and a triangle group.
-__device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, uint2* stack) {
+__device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, TravStack& stack) {
     uint2 ngroup = L.ngroup;
     const uint bit = 31u - __clz(ngroup.y);
     ngroup.y &= ~(1u << bit);
-    if (ngroup.y > 0x00FFFFFFu) { stack[L.sp++] = ngroup; }
+    if (ngroup.y > 0x00FFFFFFu) { stack.push(L.sp, ngroup); }
     const uint slot = (bit - 24u) ^ L.octinv;
     const uint rel = __popc(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
     const float4* np = sc.nodes + (size_t)(ngroup.x + rel) * 5;
@@ -283,16 +307,16 @@ __device__ __forceinline__ bool triStep(const DScene& sc, LaneState& L, const bo
 }
 // Bottom-level work of one lane for one loop trip: a node step or triangle tests, then a pop if both ran dry.
 // Returns true when an any-hit ray is finished (occluded).
-__device__ __forceinline__ bool blasTrip(const DScene& sc, LaneState& L, uint2* stack, const bool ANY) {
+__device__ __forceinline__ bool blasTrip(const DScene& sc, LaneState& L, TravStack& stack, const bool ANY) {
     if (L.tgroup.y == 0u) blasNodeStep(sc, L, stack);
     if (triStep(sc, L, ANY)) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
-    if (L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack[--L.sp];
+    if (L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack.pop(L.sp);
     return false;
 }
 // Top-level work of a lane that is not inside an instance: TLAS steps until it enters one (returns false) or
 // the ray is finished (returns true).  reload() re-reads the world-space ray after an instance was left.
 template <class Reload>
-__device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, uint2* stack, const Reload& reload) {
+__device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, TravStack& stack, const Reload& reload) {
     if (L.inBLAS && L.sp > 0) {
         float4 o4, d4; reload(o4, d4);
         L.o = f3(o4); L.d = f3(d4); L.idir = rcp3(L.d);
@@ -301,7 +325,7 @@ __device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, uint2* 
     while (true) {
         if (L.curT == PT_NONE) {
             if (L.sp == 0) return true;
-            L.curT = stack[--L.sp].x;
+            L.curT = stack.pop(L.sp).x;
         }
         tlasStep(sc, L, stack);
         if (L.inBLAS) return false;
@@ -326,7 +350,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
     const uint width = min(32u, max(max(1u, sc.minWidth), (n + totalWarps - 1u) / totalWarps));
     const uint refillAt = max(1u, width / PT_REFILL_DIV);
-    uint2 stack[PT_STACK];
+    TravStack stack; stack.init();
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     bool exhausted = n == 0;
