@@ -5,6 +5,7 @@ import ctypes as C
 import os
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -69,3 +70,81 @@ def test_two_rank_partition_and_allreduce(built):
         assert np.array_equal(r[3], total), "all-reduce hook did not leave the global sum on rank %d" % r[0]
     rc = np.full((T, 8), 0.1, np.float32)
     assert np.array_equal(_propagate(rc, res[0][3]), _propagate(rc, res[1][3]))      # replicas stay identical
+
+
+# ---- radiance-cache exchange over peer memory: host protocol (distributed.connect_peers) and the owner-range algorithm ----
+class _FakePt:
+    """Stands in for api.Pathtracer on a machine without a GPU: records what connect_peers does with the handles."""
+
+    def __init__(self, rank, fail):
+        self.rank, self.fail, self.connected, self.disconnected = rank, fail, None, False
+
+    def peer_export(self):
+        return bytes([self.rank]) * 64
+
+    def peer_connect(self, handles):
+        if self.fail:
+            raise RuntimeError("cannot map the block of rank 0")
+        self.connected = list(handles)
+
+    def peer_disconnect(self):
+        self.disconnected = True
+
+
+def _owner_range_exchange(rc, adds, world):
+    """What k_peer_reduce_propagate does (pt_kernels.cuh), in numpy: the owner of a contiguous triangle range sums every
+    rank's additions for it in rank order, propagates once (kernels.h:884-905) and hands the rows to every rank."""
+    n = rc.shape[0]
+    out = rc.copy()
+    for owner in range(world):
+        lo, hi = n * owner // world, n * (owner + 1) // world          # pt_api.cu: T * rank / world
+        total = np.zeros((16, hi - lo), np.float32)
+        for r in range(world):
+            total += adds[r][:, lo:hi]
+        out[lo:hi] = _propagate(rc[lo:hi], total)
+    return out
+
+
+def _peer_worker(rank, world, port, q):
+    from cuda_pathtracer_b200.distributed import connect_peers
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    good = _FakePt(rank, False)
+    ok1 = connect_peers(good)
+    bad = _FakePt(rank, rank == 1)                   # one rank cannot map its peers: every rank must fall back
+    ok2 = connect_peers(bad)
+    q.put((rank, ok1, good.connected, good.disconnected, ok2, bad.disconnected))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_peer_handle_exchange_and_fallback(built):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_peer_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=180) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    for rank, ok1, handles, disc1, ok2, disc2 in res:
+        assert ok1 is True and handles == [bytes([0]) * 64, bytes([1]) * 64] and not disc1      # every rank got all handles, rank order
+        assert ok2 is False and disc2                                                           # one failure => all ranks disconnect
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_owner_range_exchange_equals_allreduce_then_propagate(world):
+    rng = np.random.default_rng(world)
+    rc = (0.1 + 1.9 * rng.random((T, 8))).astype(np.float32)
+    adds = []
+    for r in range(world):
+        a = (rng.random((16, T)) * (rng.random((16, T)) < 0.3)).astype(np.float32)
+        a[8:] = np.round(a[8:] * 4)
+        a[:8] *= a[8:] > 0                           # energy only where something was counted
+        adds.append(a)
+    total = np.zeros((16, T), np.float32)
+    for a in adds:                                   # the same rank order as the owner kernels use
+        total += a
+    assert np.array_equal(_owner_range_exchange(rc, adds, world), _propagate(rc, total))
