@@ -128,6 +128,67 @@ def reference_gpu_leg(rays_per_sample, frames=40):
         return {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:300])}
 
 
+class _QuietStdout:
+    """The reference's host code prints from inside (bvhBuilder.h:266 ...): keep the bench's stdout one JSON line."""
+
+    def __enter__(self):
+        import ctypes
+        sys.stdout.flush()
+        self.libc = ctypes.CDLL(None)
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *exc):
+        self.libc.fflush(None)
+        os.dup2(self.saved, 1)
+        os.close(self.saved); os.close(self.null)
+
+
+def reference_cpu_traversal_leg(threads, repeats=3):
+    """The reference's OWN CPU traversal (traverseTopLevel<false>, src/kernels.h:277-387, compiled where it lies into
+    oracle/_ref/libptref_1920x1080.so) over the primary rays of camera 0 of the bench workload, parallelised as the reference's
+    CPU renderer does (src/raytracer.h:66, `omp parallel for schedule(dynamic)`), on the scene built by the reference's own
+    createBVHBinned / BuildTopLevelBVH.  kind "reference" for the traversal stage; the whole-path CPU number stays the port."""
+    try:
+        from cuda_pathtracer_b200 import scenes
+        from oracle import oracle_py
+        if not oracle_py.ref_available(W, H):
+            return {"unavailable": "oracle/_ref/libptref_%dx%d.so not built (needs /root/reference at build time)" % (W, H)}
+        with _QuietStdout():
+            return _reference_cpu_traversal(threads, repeats)
+    except Exception as e:                       # a baseline leg must never take the bench line down
+        return {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:300])}
+
+
+def _reference_cpu_traversal(threads, repeats):
+    if True:
+        from cuda_pathtracer_b200 import scenes
+        from oracle import oracle_py
+        ref = oracle_py.RefLib(W, H)
+        rs = oracle_py.RefScene(ref)
+        t0 = time.time()
+        m = rs.add_material(diffuse=(0.2, 0.2, 0.2))
+        rs.add_object(rs.add_model_soup(scenes.cathedral_soup(1), material=m), pos=(0, 12, 0))      # scenes.sibenik_scene(), same soups
+        rs.add_object(rs.add_model_soup(scenes.statue_soup(4), material=m))
+        rs.add_object(rs.add_model_soup(scenes.cube_soup(), material=m), material=m, pos=(0, 3, 0))
+        rs.add_sphere((-2, -1, -3), 2, m); rs.add_sphere((-2, -1, 3), 2, m)
+        rs.finalize()
+        build_s = time.time() - t0
+        cam = camera_for(0, W, H)
+        f = lambda k: [float(x) for x in np.ravel(cam[k])]
+        rays = ref.primary_rays(f("eye")[:3], f("viewDir")[:3], f("d")[0], f("focalLength")[0], f("aperture")[0], 0)
+        best = None
+        for _ in range(repeats):
+            t0 = time.time()
+            hits = rs.trace(rays, False, threads)
+            dt = time.time() - t0
+            best = dt if best is None else min(best, dt)
+        return {"mrays_s": len(rays) / best / 1e6, "rays": int(len(rays)), "seconds": best, "threads": threads, "kind": "reference",
+                "hit_fraction": float(np.mean(hits["primitive_id"] != 0xFFFFFFFF)), "scene_build_s": build_s,
+                "what": "reference traverseTopLevel<false> (closest hit) on the %dx%d primary rays of camera 0, best of %d" % (W, H, repeats)}
+
+
 def reference_arm(args):
     """--impl reference: the CPU implementation of the path (the oracle port of the reference's kernels,
     kind "port": the reference has no CPU build of kernel_shade/connect) on all host cores."""
@@ -150,7 +211,8 @@ def reference_arm(args):
             "data": "synthetic", "config": {"workload": WORKLOAD, "sample": "%dx%d pixels of the same scene/camera/depth per step" % (CPU_W, CPU_H)},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
                              "sample": "oracle/pt_oracle.cpp, 1 converge sample at %dx%d per step, OpenMP %d threads" % (CPU_W, CPU_H, threads)},
-            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "wall_s": time.time() - t0}
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "reference_traversal": reference_cpu_traversal_leg(threads), "wall_s": time.time() - t0}
     print(json.dumps(line), flush=True)
 
 
@@ -328,6 +390,7 @@ def gpu_arm(args):
                              "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray on the reference BVH2); HBM copy peak is the stated denominator, the L2 gather rate the second ceiling; ncu (profiles/) shows the kernel instruction-issue bound (issue active ~67%, 13-26 of 32 lanes per instruction), not bandwidth bound"},
                 "stage_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
                 "reference_on_this_gpu": ref_gpu,
+                "reference_cpu_traversal": reference_cpu_traversal_leg(os.cpu_count() or 1),
                 "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": "oracle/pt_oracle.cpp: %d converge samples of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_SAMPLES, CPU_W, CPU_H, cpu_rays, cpu_s)}}
         print(json.dumps(line), flush=True)

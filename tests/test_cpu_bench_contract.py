@@ -21,6 +21,10 @@ def test_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["unit"] == "Mrays/s" and d["value"] > 0 and d["vs_baseline"] is None
     assert d["cpu_baseline"]["cores"] >= 1 and d["e2e"]["h2d_bytes_per_step"] == 0
     assert "workload" in d["config"] and "model" not in d["config"]
+    assert len(r.stdout.strip().splitlines()) == 1            # the reference's own printf output stays off the bench's stdout
+    rt = d["reference_traversal"]                             # the reference's traverseTopLevel, compiled where it lies (build container)
+    if "unavailable" not in rt:
+        assert rt["kind"] == "reference" and rt["rays"] == 1920 * 1080 and rt["mrays_s"] > 0 and 0.5 < rt["hit_fraction"] <= 1.0
 
 
 def test_product_arm_fails_loudly_without_a_gpu():
