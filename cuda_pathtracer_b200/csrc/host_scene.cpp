@@ -508,6 +508,13 @@ int loadObjModel(SceneImpl& s, const char* path, float scale, const float* rot, 
         if (!strncmp(p, "mtllib", 6) && (p[6] == ' ' || p[6] == '\t')) { loadMtl(dirOf(path) + restOfLine(p + 7), mtls, mtlByName); continue; }
     }
     fclose(f);
+    {   // every index must name an element the file defines (positive indices may point forward; relative ones may not
+        // reach before the first element): pos / tex / nrm are indexed directly below
+        const int nv = (int)pos.size() / 3, nvt = (int)tex.size() / 2, nvn = (int)nrm.size() / 3;
+        for (const Face& fc : faces)
+            for (const ObjIndex& oi : fc.idx)
+                if (oi.v < 0 || oi.v >= nv || oi.vt < -1 || oi.vt >= nvt || oi.vn < -1 || oi.vn >= nvn) { s.err = std::string("face index out of range in OBJ file ") + path; return PT_ERR_IO; }
+    }
 
     std::vector<uint> matIds(mtls.size(), 0);
     if (useMtl) {                                              // scene.h:180-248
@@ -553,6 +560,7 @@ int loadObjModel(SceneImpl& s, const char* path, float scale, const float* rot, 
             if (it[0].vn < 0 || it[1].vn < 0 || it[2].vn < 0) { float c[3]; cross3(e1, e2, c); norm3(c); td.normal = pt_float3{c[0], c[1], c[2]}; }
             else td.normal = pt_float3{nrm[it[0].vn * 3], nrm[it[0].vn * 3 + 1], nrm[it[0].vn * 3 + 2]};   // scene.h:302 (v0's normal, untransformed)
             const uint mat = useMtl ? (fc.mtl >= 0 ? matIds[fc.mtl] : 0u) : material;
+            if (useMtl && mat >= s.materials.size()) { s.err = std::string("OBJ face without a material and no material defined: ") + path; return PT_ERR_IO; }
             if (useMtl && s.materials[mat].hasNormalMap) {          // scene.h:308-328
                 const float d1x = uv[1].x - uv[0].x, d1y = uv[1].y - uv[0].y, d2x = uv[2].x - uv[0].x, d2y = uv[2].y - uv[0].y;
                 const float fi = 1.0f / (d1x * d2y - d2x * d1y);

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <utility>
 #include <chrono>
 #include "pt_kernels.cuh"
 #include "pt_post.cuh"
@@ -372,11 +373,19 @@ PT_API int pt_set_allreduce_hook(pt_ctx* ctx, pt_allreduce_hook hook, void* user
 }
 PT_API int pt_set_guiding_frames(pt_ctx* ctx, uint32_t frames) {
     if (!ctx) return PT_ERR_INVALID;
+    // samples still in flight were enqueued under the old `training` predicate (pt_render): order them before anything
+    // enqueued under the new one, so a training frame never reads sample-cache entries of an overlapped sample
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     ctx->cfg.guiding_frames = frames;
     return PT_OK;
 }
 PT_API int pt_set_toggles(pt_ctx* ctx, int nee, int guiding) {
     if (!ctx) return PT_ERR_INVALID;
+    if ((nee != 0) != ctx->HNEE || (guiding != 0) != ctx->HCACHE) {        // HCACHE feeds the `training` predicate: see pt_set_guiding_frames
+        CK(cudaSetDevice(ctx->cfg.device));
+        int jr = joinStreams(ctx); if (jr) return jr;
+    }
     ctx->HNEE = nee != 0; ctx->HCACHE = guiding != 0;
     return PT_OK;
 }
@@ -387,10 +396,26 @@ PT_API int pt_join(pt_ctx* ctx) {
     return joinStreams(ctx);
 }
 
-static uint32_t tlasDepth(const pt_tlas_node* n, uint32_t count, uint32_t idx, uint32_t depth) {
-    if (idx >= count || depth > 70) return depth;
-    if (n[idx].children == 0) return depth;
-    return std::max(tlasDepth(n, count, n[idx].children & 0xffffu, depth + 1), tlasDepth(n, count, (n[idx].children >> 16) & 0xffffu, depth + 1));
+// Host-side validation of what the traversal will index with: instance model ids, top-level leaf ids and child indices
+// (one bad record would be an out-of-bounds device read in tlasStep, i.e. a sticky CUDA fault).  Walks the tree from the
+// root; returns its depth in edges, or -1 with *why set.
+static int checkTopLevel(const pt_instance* inst, uint32_t n, const pt_tlas_node* tl, uint32_t n_nodes, uint32_t numModels, const char** why) {
+    for (uint32_t i = 0; i < n; i++) if (inst[i].model_id >= numModels) { *why = "instance model_id out of range"; return -1; }
+    if (n == 0 || n_nodes == 0) return 0;
+    if (n_nodes > 65536u) { *why = "top-level BVH has more than 65536 nodes (children are 16-bit)"; return -1; }
+    std::vector<std::pair<uint32_t, uint32_t>> stack{{0u, 0u}};
+    uint32_t visited = 0, deepest = 0;
+    while (!stack.empty()) {
+        const uint32_t idx = stack.back().first, depth = stack.back().second; stack.pop_back();
+        if (++visited > n_nodes) { *why = "top-level BVH is not a tree (a node is reachable twice)"; return -1; }
+        deepest = std::max(deepest, depth);
+        const pt_tlas_node& nd = tl[idx];
+        if (nd.children == 0) { if (nd.leaf >= n) { *why = "top-level BVH leaf names an instance out of range"; return -1; } continue; }
+        const uint32_t a = nd.children & 0xffffu, b = (nd.children >> 16) & 0xffffu;
+        if (a >= n_nodes || b >= n_nodes) { *why = "top-level BVH child index out of range"; return -1; }
+        stack.push_back({a, depth + 1}); stack.push_back({b, depth + 1});
+    }
+    return (int)deepest;
 }
 
 // Test hook: the wide BVH as it sits on the device (80-byte nodes, 48-byte triangle records).  NULL pointers: sizes only.
@@ -415,7 +440,9 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaStreamSynchronize(ctx->stream));
-    peerClose(ctx);                                // the peers' mappings of the old block die with it
+    // the peers map this rank's radiance-cache block (cudaIpc): freeing it under them would turn their next training frame
+    // into stores to freed memory.  Replacing the scene of a connected context needs the collective disconnect first.
+    if (ctx->peer.on) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: peers are connected -- call pt_peer_disconnect on every rank first");
     for (void* p : ctx->sceneAllocs) cudaFree(p);
     ctx->sceneAllocs.clear();
     ctx->rcBlock = nullptr;
@@ -478,12 +505,17 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
         ctx->numWideNodes = nodeCursor; ctx->numWideTris = triCursor;
     }
     phase(hostWide ? "wide BVH (host) + H2D" : "wide BVH (device)");
-    for (uint32_t i = 0; i < d->num_instances; i++)
-        if (d->instances[i].model_id >= d->num_models) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: instance model_id out of range");
+    for (uint32_t m = 0; m < d->num_models; m++)
+        if ((uint64_t)d->models[m].triangleStart + d->models[m].nrTriangles > d->num_triangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: model triangle range exceeds num_triangles");
     // unified traversal stack: TLAS entries below the node groups of the instance being traversed
     ctx->maxWideDepth = maxWide;
-    if (d->num_instances && d->num_tlas_nodes && tlasDepth(d->topBvh, d->num_tlas_nodes, 0, 0) + maxWide + 2 > PT_STACK)
-        return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: top-level + bottom-level BVH deeper than the traversal stack");
+    {
+        const char* why = "";
+        const int depth = checkTopLevel(d->instances, d->num_instances, d->topBvh, d->num_tlas_nodes, d->num_models, &why);
+        if (depth < 0) { ctx->err = std::string("pt_upload_scene: ") + why; return PT_ERR_INVALID; }
+        if (d->num_instances && d->num_tlas_nodes && (uint32_t)depth + maxWide + 2 > PT_STACK)
+            return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: top-level + bottom-level BVH deeper than the traversal stack");
+    }
     // emissive triangles (pathtracer.h:155-167)
     std::vector<pt_triangle_light> lights;
     for (uint32_t i = 0; i < d->num_instances; i++) {
@@ -551,7 +583,13 @@ PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n,
     if (n != ctx->numInstancesCap || n_nodes != ctx->numTlasCap) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: counts differ from the uploaded scene");
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
-    if (tlasDepth(tlas, n_nodes, 0, 0) + ctx->maxWideDepth + 2 > PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: top-level BVH too deep");
+    if (!inst || !tlas) return PT_ERR_INVALID;
+    {
+        const char* why = "";
+        const int depth = checkTopLevel(inst, n, tlas, n_nodes, ctx->numModels, &why);
+        if (depth < 0) { ctx->err = std::string("pt_update_instances: ") + why; return PT_ERR_INVALID; }
+        if ((uint32_t)depth + ctx->maxWideDepth + 2 > PT_STACK) return fail(ctx, PT_ERR_INVALID, "pt_update_instances: top-level BVH too deep");
+    }
     // pathtracer.h:245-246; pageable sources are staged before the call returns
     CK(cudaMemcpyAsync((void*)ctx->sc.instances, inst, n * sizeof(pt_instance), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync((void*)ctx->sc.tlas, tlas, n_nodes * sizeof(pt_tlas_node), cudaMemcpyHostToDevice, ctx->stream));
@@ -565,6 +603,7 @@ PT_API int pt_update_instances(pt_ctx* ctx, const pt_instance* inst, uint32_t n,
 PT_API int pt_update_instances_device_tlas(pt_ctx* ctx, const pt_instance* inst, uint32_t n) {
     if (!ctx || !ctx->haveScene || !inst) return PT_ERR_INVALID;
     if (n == 0 || n != ctx->numInstancesCap || 2 * n - 1 != ctx->numTlasCap) return fail(ctx, PT_ERR_INVALID, "pt_update_instances_device_tlas: counts differ from the uploaded scene");
+    if (n > 32768u) return fail(ctx, PT_ERR_INVALID, "pt_update_instances_device_tlas: more than 32768 instances (top-level children are 16-bit node indices)");
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     for (uint32_t i = 0; i < n; i++) if (inst[i].model_id * 2 + 1 >= ctx->numModels * 2) return fail(ctx, PT_ERR_INVALID, "pt_update_instances_device_tlas: instance model_id out of range");
@@ -741,7 +780,10 @@ PT_API int pt_finish(pt_ctx* ctx) {                                             
     if (ctx->peer.on) {
         uint32_t e = 0;
         CK(cudaMemcpy(&e, ctx->rcBlock + PT_PEER_ERROR * sizeof(uint32_t), sizeof(e), cudaMemcpyDeviceToHost));
-        if (e) return fail(ctx, PT_ERR_CUDA, "pt_finish: a peer did not reach the radiance-cache exchange in time (ranks must render the same frames)");
+        if (e) {                                                                           // reported once: the word is cleared so that a later exchange starts clean
+            CK(cudaMemset(ctx->rcBlock + PT_PEER_ERROR * sizeof(uint32_t), 0, sizeof(uint32_t)));
+            return fail(ctx, PT_ERR_CUDA, "pt_finish: a peer did not reach the radiance-cache exchange in time (ranks must render the same frames); that exchange was skipped on this rank");
+        }
     }
     return PT_OK;
 }
@@ -788,7 +830,7 @@ PT_API int pt_peer_connect(pt_ctx* ctx, const void* handles, uint32_t world) {
         }
         ps.block[r] = (unsigned char*)p;
     }
-    if (const char* t = getenv("PTB200_PEER_TIMEOUT_MS")) ctx->peer.timeoutNs = (unsigned long long)atof(t) * 1000000ull;
+    if (const char* t = getenv("PTB200_PEER_TIMEOUT_MS")) ctx->peer.timeoutNs = (unsigned long long)(atof(t) * 1e6);
     ctx->peer.ps = ps; ctx->peer.epoch = 0; ctx->peer.on = true;
     return PT_OK;
 }

@@ -19,6 +19,13 @@ typedef unsigned int uint;
 
 __device__ __forceinline__ uint laneId() { uint l; asm("mov.u32 %0, %%laneid;" : "=r"(l)); return l; }
 
+// Programmatic dependent launch (sm_90+): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may be
+// scheduled while its predecessor on the stream still drains; pdlWait() blocks until the predecessor has completed and its
+// writes are visible (a no-op for a normal launch), pdlLaunch() lets the successor's blocks take freed SM slots early.
+// Every stage kernel calls pdlWait() before it touches anything an earlier kernel wrote.
+__device__ __forceinline__ void pdlWait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdlLaunch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- float3 helpers with the reference's operator semantics (src/cutil_math.h) -------------------
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 __device__ __forceinline__ float3 f3(float s) { return make_float3(s, s, s); }
@@ -103,6 +110,8 @@ struct DScene {
     uint num_triangles, num_instances, num_spheres, num_planes, num_lights;
     uint minWidth;              // scheduling: least number of rays a warp claims from a short queue (1..32)
     uint tailPair;              // scheduling: k_tail may give a path two lanes (extension + shadow ray in parallel) when the queue is short
+    float3 sortLo, sortScale;   // ray sorting (pt_kernels.cuh sortBin): cell = (origin - sortLo) * sortScale, clamped
+    uint sortBits;              // cells per axis = 1 << sortBits
 };
 
 struct DCamera { float3 eye, viewDir, lt, u, v; float d, focalLength, aperture; };

@@ -540,26 +540,41 @@ __device__ __forceinline__ uint ldAcquireSys(const uint* p) { uint v; asm volati
 __device__ __forceinline__ float ldPeer(const float* p) { float v; asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory"); return v; }
 __device__ __forceinline__ void stPeer4(float4* p, float4 v) { asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory"); }
 __device__ __forceinline__ unsigned long long globalTimerNs() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-// threads 0..world-1 of the block wait until flag word [base + t] of the LOCAL block has reached `epoch`
-__device__ __forceinline__ void peerWait(const PeerSet& ps, uint base, uint epoch, unsigned long long timeoutNs) {
+// threads 0..world-1 of the block wait until flag word [base + t] of the LOCAL block has reached `epoch`.  Returns false
+// (block-uniform) when a wait timed out or an error was already raised for this exchange: the caller then skips its
+// part of the epoch.  The error word is raised on EVERY rank (system-scope exchange over NVLink), so no rank goes on to
+// consume a half-finished exchange silently; pt_finish reports and clears it.
+__device__ __forceinline__ bool peerWait(const PeerSet& ps, uint base, uint epoch, unsigned long long timeoutNs) {
+    __shared__ int peerWaitFailed;
+    if (threadIdx.x == 0) peerWaitFailed = 0;
+    __syncthreads();
     if (threadIdx.x < ps.world) {
         uint* f = peerFlags(ps, ps.rank);
         const unsigned long long t0 = globalTimerNs();
         while ((int)(ldAcquireSys(f + base + threadIdx.x) - epoch) < 0) {
-            if (globalTimerNs() - t0 > timeoutNs) { atomicExch(f + PT_PEER_ERROR, 1u + base + threadIdx.x); break; }
+            if (ldAcquireSys(f + PT_PEER_ERROR) != 0u) { peerWaitFailed = 1; break; }
+            if (globalTimerNs() - t0 > timeoutNs) {
+                for (uint r = 0; r < ps.world; r++) atomicExch_system(peerFlags(ps, r) + PT_PEER_ERROR, 1u + base + threadIdx.x);
+                peerWaitFailed = 1;
+                break;
+            }
             __nanosleep(64);
         }
+        if (threadIdx.x == 0 && ldAcquireSys(f + PT_PEER_ERROR) != 0u) peerWaitFailed = 1;      // raised by another rank meanwhile
     }
     __syncthreads();
+    return peerWaitFailed == 0;
 }
 __global__ void k_peer_arrive(PeerSet ps, uint epoch) {
+    pdlWait(); pdlLaunch();
     __threadfence_system();                                  // this rank's k_rc_update (previous kernel on the stream) before the flag
     if (threadIdx.x < ps.world) stReleaseSys(peerFlags(ps, threadIdx.x) + PT_PEER_ARRIVE + ps.rank, epoch);
 }
 __global__ void __launch_bounds__(256) k_peer_reduce_propagate(PeerSet ps, uint epoch, uint T, uint lo, uint hi, unsigned long long timeoutNs) {
-    peerWait(ps, PT_PEER_ARRIVE, epoch, timeoutNs);
+    pdlWait(); pdlLaunch();
+    const bool ok = peerWait(ps, PT_PEER_ARRIVE, epoch, timeoutNs);     // false: a rank is missing -- nothing is summed, stored or cleared this epoch
     const uint i = lo + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < hi) {
+    if (ok && i < hi) {
         float cnt[8], en[8];
 #pragma unroll
         for (uint t = 0; t < 8; t++) { cnt[t] = 0.0f; en[t] = 0.0f; }
@@ -625,7 +640,8 @@ __global__ void __launch_bounds__(256) k_peer_reduce_propagate(PeerSet ps, uint 
 // Once every owner is done nobody reads this rank's additions any more: clear them for the next frame (k_rc_propagate
 // clears the entries it consumed; untouched ones are zero already, so the state is the same).
 __global__ void __launch_bounds__(256) k_peer_finish(PeerSet ps, uint epoch, uint T, unsigned long long timeoutNs) {
-    peerWait(ps, PT_PEER_DONE, epoch, timeoutNs);
+    pdlWait(); pdlLaunch();
+    if (!peerWait(ps, PT_PEER_DONE, epoch, timeoutNs)) return;          // failed exchange: keep the additions, pt_finish reports the error
     float* add = reinterpret_cast<float*>(ps.block[ps.rank] + ps.addOffset);
     const size_t n = (size_t)16 * T;
     for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) add[k] = 0.0f;

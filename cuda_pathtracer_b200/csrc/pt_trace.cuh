@@ -147,6 +147,8 @@ struct LaneState {
 // Ray sources/sinks.  load() must be repeatable (the world-space ray is re-read when an instance is left).
 struct QueueIO {                // the wavefront queues: SoA float4 streams
     const float4* rayO; const float4* rayD; float4* hits; const float4* lights; float4* accucolors;
+    const uint* perm;           // ray sorting (k_sort_*): fetch position -> queue index, nullptr = queue order
+    __device__ __forceinline__ uint index(uint i) const { return perm ? perm[i] : i; }
     __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const { o4 = rayO[i]; d4 = rayD[i]; }
     template <bool ANY> __device__ __forceinline__ void store(uint i, const LaneState& L) const {
         if (ANY) {
@@ -162,6 +164,7 @@ struct QueueIO {                // the wavefront queues: SoA float4 streams
 };
 struct DebugIO {                // reference-format rays in, reference-format hits out (pt_debug_trace)
     const pt_ray* rays; pt_hit* out;
+    __device__ __forceinline__ uint index(uint i) const { return i; }
     __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const {
         o4 = *reinterpret_cast<const float4*>(&rays[i].origin); d4 = *reinterpret_cast<const float4*>(&rays[i].direction);
     }
@@ -206,6 +209,24 @@ __device__ __forceinline__ bool beginRay(const DScene& sc, LaneState& L, const f
     L.curT = 0;
     return true;
 }
+
+// Work counters of the counting kernels (k_trace_count): node steps, triangle tests, top-level steps per lane, summed per
+// warp and flushed with one atomic per counter.  NoTally compiles to nothing.
+struct NoTally {
+    __device__ __forceinline__ void node() {}
+    __device__ __forceinline__ void tri() {}
+    __device__ __forceinline__ void top() {}
+};
+struct Tally {
+    uint nNode = 0, nTri = 0, nTop = 0;
+    __device__ __forceinline__ void node() { nNode++; }
+    __device__ __forceinline__ void tri() { nTri++; }
+    __device__ __forceinline__ void top() { nTop++; }
+    __device__ __forceinline__ void flush(unsigned long long* out) {
+        const uint a = __reduce_add_sync(0xffffffffu, nNode), b = __reduce_add_sync(0xffffffffu, nTri), c = __reduce_add_sync(0xffffffffu, nTop);
+        if (laneId() == 0) { atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c); }
+    }
+};
 
 // One top-level step for the TLAS node L.curT (kernels.h:320-386): a leaf enters its instance
 // (transformRay, kernels.h:81-86), an inner node tests both children in the reference's order.
@@ -286,9 +307,11 @@ __device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, Tra
 
 // Up to PT_TRIS_PER_ITER Moeller-Trumbore tests from the lane's pending triangle group.  Returns true when an
 // any-hit ray found its occluder.
-__device__ __forceinline__ bool triStep(const DScene& sc, LaneState& L, const bool ANY) {
+template <class TALLY>
+__device__ __forceinline__ bool triStep(const DScene& sc, LaneState& L, const bool ANY, TALLY& tally) {
 #pragma unroll 1
     for (int k = 0; k < PT_TRIS_PER_ITER && L.tgroup.y != 0u; k++) {
+        tally.tri();
         const uint ti = 31u - __clz(L.tgroup.y);
         L.tgroup.y &= ~(1u << ti);
         const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
@@ -307,16 +330,17 @@ __device__ __forceinline__ bool triStep(const DScene& sc, LaneState& L, const bo
 }
 // Bottom-level work of one lane for one loop trip: a node step or triangle tests, then a pop if both ran dry.
 // Returns true when an any-hit ray is finished (occluded).
-__device__ __forceinline__ bool blasTrip(const DScene& sc, LaneState& L, TravStack& stack, const bool ANY) {
-    if (L.tgroup.y == 0u) blasNodeStep(sc, L, stack);
-    if (triStep(sc, L, ANY)) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
+template <class TALLY>
+__device__ __forceinline__ bool blasTrip(const DScene& sc, LaneState& L, TravStack& stack, const bool ANY, TALLY& tally) {
+    if (L.tgroup.y == 0u) { blasNodeStep(sc, L, stack); tally.node(); }
+    if (triStep(sc, L, ANY, tally)) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
     if (L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack.pop(L.sp);
     return false;
 }
 // Top-level work of a lane that is not inside an instance: TLAS steps until it enters one (returns false) or
 // the ray is finished (returns true).  reload() re-reads the world-space ray after an instance was left.
-template <class Reload>
-__device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, TravStack& stack, const Reload& reload) {
+template <class Reload, class TALLY>
+__device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, TravStack& stack, const Reload& reload, TALLY& tally) {
     if (L.inBLAS && L.sp > 0) {
         float4 o4, d4; reload(o4, d4);
         L.o = f3(o4); L.d = f3(d4); L.idir = rcp3(L.d);
@@ -327,7 +351,7 @@ __device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, TravSta
             if (L.sp == 0) return true;
             L.curT = stack.pop(L.sp).x;
         }
-        tlasStep(sc, L, stack);
+        tlasStep(sc, L, stack); tally.top();
         if (L.inBLAS) return false;
     }
 }
@@ -344,8 +368,8 @@ __device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, TravSta
 // instance the lowest reference triangle id wins, which makes the result independent of visit order.
 __device__ __forceinline__ bool hasBlasWork(const LaneState& L) { return L.ray != PT_NONE && (L.tgroup.y | (L.ngroup.y & 0xFF000000u)) != 0u; }
 
-template <bool ANY, class IO>
-__device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* cursor, const IO io) {
+template <bool ANY, class IO, class TALLY>
+__device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* cursor, const IO io, TALLY& tally) {
     const uint lane = laneId();
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
     const uint width = min(32u, max(max(1u, sc.minWidth), (n + totalWarps - 1u) / totalWarps));
@@ -366,7 +390,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
             if (base + want >= n) exhausted = true;
             const uint r = __popc(~activeMask & ((1u << lane) - 1u));          // rank among the idle lanes
             if (L.ray == PT_NONE && r < want && base + r < n) {
-                L.ray = base + r;
+                L.ray = io.index(base + r);
                 float4 o4, d4; io.load(L.ray, o4, d4);
                 if (!beginRay(sc, L, o4, d4, ANY)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
             }
@@ -374,7 +398,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
         // ---- T: top level ----
         if (L.ray != PT_NONE && !hasBlasWork(L)) {
             const uint ray = L.ray;
-            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); })) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); }, tally)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
         // ---- B: bottom level ----
         const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
@@ -382,7 +406,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
         while (true) {
             const bool work = hasBlasWork(L);
             if (__popc(__ballot_sync(0xffffffffu, work)) < minKeep) break;
-            if (work && blasTrip(sc, L, stack, ANY)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+            if (work && blasTrip(sc, L, stack, ANY, tally)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
     }
 }
