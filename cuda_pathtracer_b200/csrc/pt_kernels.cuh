@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(256) k_primary(DCamera cam, TileMap map, uint 
     uint x, y;
     const bool valid = slotToPixel(map, slot, x, y);
     float3 o = f3(0), d = f3(0);
+    pdlWait(); pdlLaunch();
     if (valid) {
         // (the per-sample state reset of kernels.h:485-491 happens in the first shade: every valid slot gets a primary ray)
         uint seed = getSeed(x, y, randIdx, map.W);
@@ -120,9 +121,23 @@ __global__ void k_primary_debug(DCamera cam, uint W, uint H, uint randIdx, pt_ra
 template <bool ANY>
 __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
-                                               const float4* __restrict__ lights, float4* accucolors) {
-    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors;
-    traceLoop<ANY>(sc, *count, cursor, io);
+                                               const float4* __restrict__ lights, float4* accucolors, const uint* __restrict__ perm) {
+    pdlWait(); pdlLaunch();
+    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = perm;
+    NoTally tally;
+    traceLoop<ANY>(sc, *count, cursor, io, tally);
+}
+// counting variant (pt_set_counting): the same traversal, plus the node steps / triangle tests / top-level steps it
+// performs, summed into tallyOut[0..2] -- the bytes the wide layout actually requests (80 B per node step, 48 B per
+// triangle test, 32 B per top-level node) for the roofline line of bench.py
+template <bool ANY>
+__global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_count(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+                                               const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
+                                               const float4* __restrict__ lights, float4* accucolors, unsigned long long* tallyOut) {
+    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = nullptr;
+    Tally tally;
+    traceLoop<ANY>(sc, *count, cursor, io, tally);
+    tally.flush(tallyOut);
 }
 
 // extend(b+1) and connect(b) in ONE launch: both queues exist once shade(b) has run and neither kernel touches what the
@@ -133,18 +148,22 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair(DScene s
                                                     const uint* __restrict__ extCount, uint* extCursor, float4* __restrict__ hits,
                                                     const float4* __restrict__ shO, const float4* __restrict__ shD,
                                                     const uint* __restrict__ shCount, uint* shCursor,
-                                                    const float4* __restrict__ lights, float4* accucolors) {
-    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr;
-    traceLoop<false>(sc, *extCount, extCursor, e);
-    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors;
-    traceLoop<true>(sc, *shCount, shCursor, c);
+                                                    const float4* __restrict__ lights, float4* accucolors,
+                                                    const uint* __restrict__ extPerm, const uint* __restrict__ shPerm) {
+    pdlWait(); pdlLaunch();
+    NoTally tally;
+    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm;
+    traceLoop<false>(sc, *extCount, extCursor, e, tally);
+    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
+    traceLoop<true>(sc, *shCount, shCursor, c, tally);
 }
 
 // stage-parity hook: reference-format rays in, reference-format hits out (pt_debug_trace)
 template <bool ANY>
 __global__ void __launch_bounds__(128) k_trace_debug(DScene sc, const pt_ray* __restrict__ rays, uint n, uint* cursor, pt_hit* __restrict__ out) {
     DebugIO io; io.rays = rays; io.out = out;
-    traceLoop<ANY>(sc, n, cursor, io);
+    NoTally tally;
+    traceLoop<ANY>(sc, n, cursor, io, tally);
 }
 
 __global__ void k_prepare_lights(DScene sc) {
@@ -156,7 +175,51 @@ __global__ void k_prepare_lights(DScene sc) {
 #ifndef PT_SHADE_MINBLOCKS
 #define PT_SHADE_MINBLOCKS 8
 #endif
+// Ray sorting (the reference's experiment sorts by pixel with a CUB radix sort and permutes the rays,
+// src/raySorting.h:1-68).  Here: a counting sort on (Morton cell of the origin, direction octant) whose histogram is
+// built by the shade kernel while it appends the rays; k_sort_scan turns it into bin offsets, k_sort_scatter into a
+// permutation, and the traversal kernels fetch rays through that permutation (hits land at the ray's own queue index, so
+// shading order -- and every result -- is untouched).  Queue sizes stay on the device.
+__device__ __forceinline__ uint sortBin(const DScene& sc, float3 o, float3 d) {
+    const float top = (float)((1u << sc.sortBits) - 1u);
+    const uint cx = (uint)fminf(fmaxf((o.x - sc.sortLo.x) * sc.sortScale.x, 0.0f), top);
+    const uint cy = (uint)fminf(fmaxf((o.y - sc.sortLo.y) * sc.sortScale.y, 0.0f), top);
+    const uint cz = (uint)fminf(fmaxf((o.z - sc.sortLo.z) * sc.sortScale.z, 0.0f), top);
+    uint m = 0;
+    for (uint b = 0; b < sc.sortBits; b++) m |= (((cx >> b) & 1u) << (3u * b)) | (((cy >> b) & 1u) << (3u * b + 1u)) | (((cz >> b) & 1u) << (3u * b + 2u));
+    return (m << 3) | (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+}
+__global__ void __launch_bounds__(1024) k_sort_scan(uint* histExt, uint* histSh, uint nbins) {      // block 0: extension queue, block 1: shadow queue
+    pdlWait(); pdlLaunch();
+    uint* h = blockIdx.x ? histSh : histExt;
+    if (!h) return;
+    __shared__ uint warpSums[32];
+    const uint per = (nbins + 1023u) / 1024u, b0 = threadIdx.x * per, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint sum = 0;
+    for (uint k = 0; k < per && b0 + k < nbins; k++) sum += h[b0 + k];
+    uint incl = sum;
+    for (uint off = 1; off < 32; off <<= 1) { const uint v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+    if (lane == 31) warpSums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const uint w = warpSums[lane]; uint wi = w;
+        for (uint off = 1; off < 32; off <<= 1) { const uint v = __shfl_up_sync(0xffffffffu, wi, off); if (lane >= off) wi += v; }
+        warpSums[lane] = wi - w;
+    }
+    __syncthreads();
+    uint run = warpSums[warp] + incl - sum;
+    for (uint k = 0; k < per && b0 + k < nbins; k++) { const uint c = h[b0 + k]; h[b0 + k] = run; run += c; }
+}
+__global__ void __launch_bounds__(256) k_sort_scatter(const uint* __restrict__ keysExt, uint* histExt, uint* permExt, const uint* __restrict__ nExt,
+                                                      const uint* __restrict__ keysSh, uint* histSh, uint* permSh, const uint* __restrict__ nSh) {
+    pdlWait(); pdlLaunch();
+    const uint stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (keysExt) { const uint n = *nExt; for (uint i = t0; i < n; i += stride) permExt[atomicAdd(histExt + keysExt[i], 1u)] = i; }
+    if (keysSh) { const uint n = *nSh; for (uint i = t0; i < n; i += stride) permSh[atomicAdd(histSh + keysSh[i], 1u)] = i; }
+}
+
 __global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P, Queues q, int inBuf) {
+    pdlWait(); pdlLaunch();
     const uint n = q.cnt[CNT_EXT(P.bounce)];
     const float4* rayO = q.rayO[inBuf]; const float4* rayD = q.rayD[inBuf];
     float4* outO = q.rayO[inBuf ^ 1]; float4* outD = q.rayD[inBuf ^ 1];
@@ -176,11 +239,13 @@ __global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P
         if (so.pushShadow) {
             q.shO[si] = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
             q.shD[si] = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
+            if (P.sortKeys[1]) { const uint bin = sortBin(P.sc, so.shadow.o, so.shadow.d); P.sortKeys[1][si] = bin; atomicAdd(P.sortHist[1] + bin, 1u); }
         }
         const uint ei = blockAppend(so.pushExt, q.cnt + CNT_EXT(P.bounce + 1), sm);
         if (so.pushExt) {
             outO[ei] = make_float4(so.ext.o.x, so.ext.o.y, so.ext.o.z, so.ext.len);
             outD[ei] = make_float4(so.ext.d.x, so.ext.d.y, so.ext.d.z, __uint_as_float(slot));
+            if (P.sortKeys[0]) { const uint bin = sortBin(P.sc, so.ext.o, so.ext.d); P.sortKeys[0][ei] = bin; atomicAdd(P.sortHist[0] + bin, 1u); }
         }
     }
 }
@@ -208,6 +273,7 @@ __device__ __forceinline__ float4 shfl4(const float4 v, const uint src) {
 // sample on a small shard is latency bound and has the lanes to spare: the per-bounce latency becomes
 // max(extend, connect) + shade instead of their sum.
 __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, Queues q, int inBuf, int b0, int maxBounces, uint* cursor) {
+    pdlWait(); pdlLaunch();
     const DScene& sc = P.sc;
     const uint n = q.cnt[CNT_EXT(b0)];
     const uint lane = laneId();
@@ -217,6 +283,7 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
     const uint ownerMask = pair ? 0x55555555u : 0xffffffffu;
     const uint width = min(pair ? 16u : 32u, max(max(1u, pair ? 1u : sc.minWidth), (n + totalWarps - 1u) / totalWarps));
     TravStack stack; stack.init();
+    NoTally tally;
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     int bounce = b0, buf = inBuf;
@@ -308,14 +375,14 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
             if (isHelper && take) { L.ray = path; any = true; rayDone = !beginRay(sc, L, o4, d4, true); }
         }
         // ---- T: top level ----
-        if (L.ray != PT_NONE && !rayDone && !hasBlasWork(L)) rayDone = tlasTrip(sc, L, stack, loadCur);
+        if (L.ray != PT_NONE && !rayDone && !hasBlasWork(L)) rayDone = tlasTrip(sc, L, stack, loadCur, tally);
         // ---- B: bottom level ----
         const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
         const uint minKeep = max(1u, (nB * PT_KEEP_NUM + PT_KEEP_DEN - 1u) / PT_KEEP_DEN);
         while (true) {
             const bool work = hasBlasWork(L);
             if (__popc(__ballot_sync(0xffffffffu, work)) < minKeep) break;
-            if (work && blasTrip(sc, L, stack, any)) rayDone = true;
+            if (work && blasTrip(sc, L, stack, any, tally)) rayDone = true;
         }
     }
 }
@@ -325,6 +392,7 @@ __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* _
                                                     float4* image, float4* albedo, const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces, uint waveBounces) {
     const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint x, y;
+    pdlWait(); pdlLaunch();
     if (slotToPixel(map, slot, x, y)) {
         const float4 c = accucolors[slot];
         const uint pix = x + y * map.W;
@@ -475,6 +543,7 @@ __global__ void __launch_bounds__(256) k_rc_update(TileMap map, const float4* __
                                                    const pt_sample_cache* __restrict__ sampleCache, float* add, uint T) {   // kernels.h:863-882
     const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint x, y;
+    pdlWait(); pdlLaunch();
     if (!slotToPixel(map, slot, x, y)) return;
     const float3 totalEnergy = f3(accucolors[slot]);
     for (uint bounce = 0; bounce < PT_MAX_CACHE_DEPTH; bounce++) {
@@ -488,6 +557,7 @@ __global__ void __launch_bounds__(256) k_rc_update(TileMap map, const float4* __
 }
 __global__ void __launch_bounds__(256) k_rc_propagate(float4* rc, float* add, uint T) {                                   // kernels.h:884-905
     const uint i = blockIdx.x * blockDim.x + threadIdx.x;
+    pdlWait(); pdlLaunch();
     if (i >= T) return;
     float4 r0 = rc[(size_t)i * 3], r1 = rc[(size_t)i * 3 + 1], r2 = rc[(size_t)i * 3 + 2];
     float v[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};

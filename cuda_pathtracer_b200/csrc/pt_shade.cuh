@@ -12,6 +12,10 @@ struct FrameTex {
     cudaTextureObject_t blue;       // float, point, wrap, normalised (use_cuda.h:166-200); 0 => 0.0
     float3 skyConst;
     float2 invBlueSize;
+    // skydome importance sampling (opt-in, pt_set_sky_sampling): the CDF Pathtracer::Init builds (pathtracer.h:85-122)
+    const float* skyPdf;            // values[]: max(r,g,b) of texel i / total
+    const float* skyCdf;            // cumValues[]: running sum / total
+    uint skyW, skyH, skySample;
 };
 
 struct TraceState { float3 mask, accucolor, light; bool fromSpecular, albedoSet; };   // types.h:461-468
@@ -91,6 +95,26 @@ __device__ __forceinline__ float3 sampleHemisphereCached(float3 normal, RandStat
     return sampleHemisphereCosine(normal, r0, r1);
 }
 
+// kernels.h:65-79 (binarySearch over CDF::cumValues).  The reference returns its last probe, which is the texel just
+// BELOW the one containing `target` whenever the search ends by raising L (no kernel ever called it, so it went unnoticed);
+// here the search is completed: the result is the first texel whose cumulative value reaches target.
+__device__ __forceinline__ uint binarySearchCdf(const float* values, uint nrValues, float target) {
+    uint L = 0, R = nrValues - 1;
+    while (L + 1 < R) {
+        const uint m = (L + R) / 2;
+        if (values[m] >= target) R = m; else L = m;
+    }
+    return values[L] >= target ? L : R;
+}
+// inverse of normalToUv (kernels.h:31-36) under the wrap addressing of the skydome texture: u = atan2(n.x, n.z) / 2pi,
+// v = -acos(n.y) / pi (mod 1).  (The reference's uvToNormal, kernels.h:39-49, mirrors n.y and is not that inverse.)
+__device__ __forceinline__ float3 skyUvToDir(float u, float v, float& sinPolar) {
+    const float theta = u * 2.0f * PT_PI;
+    const float a = PT_PI * (1.0f - v);
+    sinPolar = sinf(a);
+    return f3(sinf(theta) * sinPolar, cosf(a), cosf(theta) * sinPolar);
+}
+
 struct ShadeRay { float3 o, d; float len; };
 
 // kernels.h:452-456
@@ -133,6 +157,9 @@ struct ShadeParams {
     uint sampleIdx, randIdx, blueFrames;
     int bounce;
     bool nee, cache;                        // device _NEE (globals.h:23) and DCACHE
+    bool cacheWrite;                        // false: this sample's SampleCache entries are never read (overlapped non-training sample)
+    uint* sortKeys[2];                      // ray sorting: bin per pushed extension [0] / shadow [1] ray, nullptr = off
+    uint* sortHist[2];
 };
 
 struct ShadeOut { bool pushExt, pushShadow; ShadeRay ext, shadow; };
@@ -159,7 +186,8 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
         float3 sk = P.tex.skyConst;
         if (P.tex.sky) { float2 uv = normalToUv(rd); sk = f3(tex2D<float4>(P.tex.sky, uv.x, uv.y)); }
         if (!state.albedoSet) { updateAlbedo(P.albedoSample, slot, state.mask * sk); state.albedoSet = true; }
-        state.accucolor += state.mask * sk;
+        // with skydome sampling on, a diffuse vertex has already collected the sky through its shadow ray (like emitters under NEE, kernels.h:567)
+        if (!(P.tex.skySample && P.tex.sky) || state.fromSpecular) state.accucolor += state.mask * sk;
     } else {
         RandState rs; rs.sampleIdx = P.sampleIdx; rs.randIdx = P.randIdx; rs.blueFrames = P.blueFrames;
         rs.seed = getSeed(x, y, rs.randIdx, P.map.W);
@@ -248,7 +276,32 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
             } else {                                                          // kernels.h:662-782
                 if (!state.albedoSet) { updateAlbedo(P.albedoSample, slot, state.mask * diffuse); state.albedoSet = true; }
                 state.fromSpecular = false;
-                if (P.nee) {                                                  // kernels.h:672-753
+                // Skydome importance sampling (opt-in; the reference builds the CDF but no kernel samples it): a pixel owns one
+                // shadow ray per bounce, so a vertex estimates EITHER the emissive triangles (below) OR the sky, chosen with
+                // probability 1/2 when both exist, the estimate divided by that probability.
+                bool lightNee = P.nee, skyNee = P.tex.skySample != 0u && P.tex.sky != 0;
+                float pickScale = 1.0f;
+                if (lightNee && skyNee) { pickScale = 2.0f; if (rnd(rs) < 0.5f) lightNee = false; else skyNee = false; }
+                if (skyNee) {
+                    const uint m = binarySearchCdf(P.tex.skyCdf, P.tex.skyW * P.tex.skyH, rnd(rs));
+                    const uint tx = m % P.tex.skyW, ty = m / P.tex.skyW;
+                    const float su = ((float)tx + rnd(rs)) / (float)P.tex.skyW, sv = ((float)ty + rnd(rs)) / (float)P.tex.skyH;
+                    float sinPolar;
+                    const float3 sdir = skyUvToDir(su, sv, sinPolar);
+                    const float pdf = P.tex.skyPdf[m] * (float)(P.tex.skyW * P.tex.skyH) / (2.0f * PT_PI * PT_PI * fmaxf(sinPolar, 0.0001f));
+                    const float NL = dot(colliderNormal, sdir);
+                    if (NL > 0 && dot(sdir, surfaceNormal) > 0 && pdf > 0) {
+                        const float2 uv = normalToUv(sdir);
+                        const float3 sk = f3(tex2D<float4>(P.tex.sky, uv.x, uv.y));
+                        state.light = state.mask * (BRDF * sk * (NL * pickScale / pdf));
+                        const float f = NL * NL * NL;
+                        out.pushShadow = true;
+                        out.shadow.o = intersectionPos + PT_EPS * f * sdir + PT_EPS * (1 - f) * colliderNormal;
+                        out.shadow.d = sdir;
+                        out.shadow.len = 9999999;
+                    }
+                }
+                if (lightNee) {                                               // kernels.h:672-753
                     uint successIdx = 0; float valid = 0.0f;
                     for (uint k = 0; k < 4; k++) {                            // kernels.h:676-690; per-light terms come from k_prepare_lights
                         const uint lightSource = uint(rnd(rs) * sc.num_lights) % sc.num_lights;
@@ -277,6 +330,7 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
                             const float A = 0.5f * crLength;
                             const float SA = LNL * A * invShadowLength * invShadowLength;
                             state.light = state.mask * (NL * SA * sc.num_lights * BRDF * f3(em.x, em.y, em.z) * (valid / 4.0f));
+                            if (pickScale != 1.0f) state.light *= pickScale;
                             const float f = LNL * LNL * LNL;
                             out.pushShadow = true;
                             out.shadow.o = samplePoint + f * PT_EPS * shadowDir + (1 - f) * PT_EPS * lightNormal;
@@ -318,7 +372,7 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
         P.accucolors[slot] = make_float4(state.accucolor.x, state.accucolor.y, state.accucolor.z, __uint_as_float(state.albedoSet ? 1u : 0u));
         P.lights[slot] = make_float4(state.light.x, state.light.y, state.light.z, 0.0f);
     }
-    if (writeCache && P.bounce < PT_MAX_CACHE_DEPTH) P.sampleCache[(size_t)P.bounce * P.map.nSlots + slot] = cache;
+    if (writeCache && P.cacheWrite && P.bounce < PT_MAX_CACHE_DEPTH) P.sampleCache[(size_t)P.bounce * P.map.nSlots + slot] = cache;
 }
 
 }  // namespace ptb
