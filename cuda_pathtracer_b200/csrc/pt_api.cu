@@ -18,6 +18,12 @@ using namespace ptb;
 static thread_local std::string g_createError;
 
 #define PT_MAX_SETS 8
+#define PT_SORT_MAX_BITS 5          /* ray sorting: up to 32 cells per axis x 8 octants = 262144 bins */
+#define PT_SORT_MAX_BOUNCES 2       /* queues produced by the first PT_SORT_MAX_BOUNCES shade launches of a sample can be sorted */
+#define PT_GATHER_RING 4            /* image slots of the N-rank framebuffer gather on rank 0 */
+#define PT_GATHER_ARRIVE 256        /* flag words (uint[16]) in the radiance-cache block header: rank r pushed its tiles of this epoch */
+#define PT_GATHER_CONSUMED 320      /* rank 0 has shipped epoch e to the host: the slot of e may be overwritten by e + PT_GATHER_RING */
+#define PT_GATHER_COUNTER 321
 struct pt_ctx {
     pt_config cfg;
     std::string err;
@@ -31,6 +37,7 @@ struct pt_ctx {
         Queues q;
         float4 *masks = nullptr, *accucolors = nullptr, *lights = nullptr, *albedoSample = nullptr;
         pt_sample_cache* sampleCache = nullptr;
+        uint *sortKeys[2] = {nullptr, nullptr}, *sortPerm[2] = {nullptr, nullptr}, *sortHist = nullptr;   // ray sorting: [0] extension, [1] shadow queue; hist = [bounce][queue][bins] behind the counters
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;       // recorded after the sample's accumulate
         cudaEvent_t tailStart = nullptr;  // recorded right before the sample's k_tail launch
@@ -42,7 +49,7 @@ struct pt_ctx {
     // Asynchronous read-back (pt_read_image_async): copies run on their own stream after the sample they follow; the
     // next accumulate waits for the copy, so the snapshot is exactly "after that sample".  Tickets index a ring of events.
     cudaStream_t copyStream = nullptr;
-    cudaEvent_t copyReady = nullptr, copyEv[8] = {};
+    cudaEvent_t copyReady = nullptr, copyEv[8] = {}, imgFree = nullptr;   // imgFree: the pending read-back no longer reads the image
     uint64_t copyTickets = 0;
     bool copyPending = false;
     int lastSet = -1;
@@ -75,6 +82,12 @@ struct pt_ctx {
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
+    bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
+    bool sortOn = false; uint32_t sortBits = 4, sortBounces = PT_SORT_MAX_BOUNCES;          // pt_set_ray_sorting
+    bool counting = false; unsigned long long* tally = nullptr;                            // pt_set_counting: [0..2] extend, [3..5] connect
+    float *skyPdf = nullptr, *skyCdf = nullptr;                                           // pt_set_skydome builds them (pathtracer.h:85-122)
+    // N-rank framebuffer gather (pt_gather_image_async): image ring on rank 0, flags in the radiance-cache block header
+    unsigned char* gatherBlock = nullptr; size_t gatherBytes = 0; void* gatherOpened = nullptr; float4* gatherRoot = nullptr; uint32_t gatherEpoch = 0;
     // per-stage timing (pt_set_profiling): CUDA event pairs around every stage launch, resolved in pt_finish
     bool prof = false;
     std::vector<cudaEvent_t> evPool;
@@ -116,6 +129,21 @@ static void resolveProfile(pt_ctx* ctx) {   // call after the stream has been sy
 }
 
 static int fail(pt_ctx* ctx, int code, const char* msg) { ctx->err = msg; return code; }
+
+// Every stage launch of pt_render goes through here: counted (pt_stats.kernel_launches) and, unless switched off, launched
+// with programmatic stream serialization, so the next kernel's blocks are scheduled while this one drains (each kernel
+// starts with pdlWait(), pt_device.cuh).  Errors surface through the cudaGetLastError at the end of pt_render.
+template <typename... KA, typename... A>
+static inline void launchK(pt_ctx* ctx, void (*kernel)(KA...), dim3 grid, dim3 block, cudaStream_t s, A&&... args) {
+    ctx->launches++;
+    cudaLaunchConfig_t c; memset(&c, 0, sizeof(c));
+    c.gridDim = grid; c.blockDim = block; c.dynamicSmemBytes = 0; c.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    c.attrs = at; c.numAttrs = ctx->pdl ? 1u : 0u;
+    cudaLaunchKernelEx(&c, kernel, std::forward<A>(args)...);
+}
 
 template <typename T>
 static int devAlloc(pt_ctx* ctx, T** p, size_t n, bool sceneOwned) {
@@ -163,6 +191,8 @@ PT_API const char* pt_last_error(const pt_ctx* ctx) { return ctx ? ctx->err.c_st
 
 static void peerClose(pt_ctx* ctx) {
     for (auto& p : ctx->peer.opened) if (p) { cudaIpcCloseMemHandle(p); p = nullptr; }
+    if (ctx->gatherOpened) { cudaIpcCloseMemHandle(ctx->gatherOpened); ctx->gatherOpened = nullptr; }
+    ctx->gatherRoot = nullptr;
     ctx->peer.on = false;
 }
 
@@ -180,7 +210,8 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     for (auto& S : ctx->set) {
         if (S.stream) cudaStreamSynchronize(S.stream);
         void* sb[] = {S.q.rayO[0], S.q.rayO[1], S.q.rayD[0], S.q.rayD[1], S.q.shO, S.q.shD, S.q.hits, S.q.cnt,
-                      S.masks, S.accucolors, S.lights, S.albedoSample, &S == &ctx->set[0] ? S.sampleCache : nullptr};
+                      S.masks, S.accucolors, S.lights, S.albedoSample, &S == &ctx->set[0] ? S.sampleCache : nullptr,
+                      S.sortKeys[0], S.sortKeys[1], S.sortPerm[0], S.sortPerm[1]};
         for (void* p : sb) if (p) cudaFree(p);
         if (S.done) cudaEventDestroy(S.done);
         if (S.tailStart) cudaEventDestroy(S.tailStart);
@@ -188,6 +219,11 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     }
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
     if (ctx->copyReady) cudaEventDestroy(ctx->copyReady);
+    if (ctx->imgFree) cudaEventDestroy(ctx->imgFree);
+    if (ctx->gatherBlock) cudaFree(ctx->gatherBlock);
+    if (ctx->skyPdf) cudaFree(ctx->skyPdf);
+    if (ctx->skyCdf) cudaFree(ctx->skyCdf);
+    if (ctx->tally) cudaFree(ctx->tally);
     for (auto e : ctx->copyEv) if (e) cudaEventDestroy(e);
     if (ctx->copyStream) cudaStreamDestroy(ctx->copyStream);
     void* bufs[] = {ctx->image, ctx->albedo, ctx->postBuf, ctx->packBuf, ctx->stats, ctx->dbgRays, ctx->dbgHits, ctx->dbgCursor};
@@ -263,7 +299,10 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
             if ((r = devAlloc(ctx, &S.q.shO, cap, false))) return r;
             if ((r = devAlloc(ctx, &S.q.shD, cap, false))) return r;
             if ((r = devAlloc(ctx, &S.q.hits, cap, false))) return r;
-            if ((r = devAlloc(ctx, &S.q.cnt, (size_t)CNT_TOTAL, false))) return r;
+            // counters, then the ray-sorting histograms [bounce][queue][bins]: one allocation, zeroed by ONE memset per sample
+            if ((r = devAlloc(ctx, &S.q.cnt, (size_t)CNT_TOTAL + (size_t)PT_SORT_MAX_BOUNCES * 2 * (8u << (3 * PT_SORT_MAX_BITS)), false))) return r;
+            S.sortHist = S.q.cnt + CNT_TOTAL;
+            CK(cudaMemsetAsync(S.sortHist, 0, (size_t)PT_SORT_MAX_BOUNCES * 2 * (8u << (3 * PT_SORT_MAX_BITS)) * sizeof(uint), ctx->stream));
             if ((r = devAlloc(ctx, &S.masks, cap, false))) return r;
             if ((r = devAlloc(ctx, &S.accucolors, cap, false))) return r;
             if ((r = devAlloc(ctx, &S.lights, cap, false))) return r;
@@ -282,6 +321,9 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if ((r = devAlloc(ctx, &ctx->image, (size_t)m.W * m.H, false))) return r;
         if ((r = devAlloc(ctx, &ctx->albedo, (size_t)m.W * m.H, false))) return r;
         if ((r = devAlloc(ctx, &ctx->stats, (size_t)8, false))) return r;
+        if ((r = devAlloc(ctx, &ctx->tally, (size_t)8, false))) return r;
+        CK(cudaMemsetAsync(ctx->tally, 0, 8 * sizeof(unsigned long long), ctx->stream));
+        CK(cudaEventCreateWithFlags(&ctx->imgFree, cudaEventDisableTiming));
         if ((r = devAlloc(ctx, &ctx->dbgCursor, (size_t)1, false))) return r;
         CK(cudaMemsetAsync(ctx->image, 0, (size_t)m.W * m.H * sizeof(float4), ctx->stream));
         CK(cudaMemsetAsync(ctx->albedo, 0, (size_t)m.W * m.H * sizeof(float4), ctx->stream));
@@ -304,6 +346,13 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->knobMinWidth = (uint32_t)std::max(1, std::min(32, atoi(e)));          // developer knobs, read once
         ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
         ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
+        ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
+        if (cfg->flags & PT_FLAG_SORT_RAYS) ctx->sortOn = true;
+        if (const char* e = getenv("PTB200_SORT")) {                                       // developer knob: "bits[,bounces]", 0 = off
+            ctx->sortOn = atoi(e) > 0;
+            if (ctx->sortOn) ctx->sortBits = (uint32_t)std::min(PT_SORT_MAX_BITS, std::max(1, atoi(e)));
+            if (const char* c = strchr(e, ',')) ctx->sortBounces = (uint32_t)std::min(PT_SORT_MAX_BOUNCES, std::max(1, atoi(c + 1)));
+        }
         CK(cudaStreamSynchronize(ctx->stream));
         return PT_OK;
     };
@@ -337,10 +386,83 @@ static int makeTexture(pt_ctx* ctx, const float* data, uint32_t w, uint32_t h, i
 PT_API int pt_set_skydome(pt_ctx* ctx, const float* rgba, uint32_t w, uint32_t h) {
     if (!ctx) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
-    if (!rgba) { ctx->tex.sky = 0; return PT_OK; }
+    if (!rgba) { ctx->tex.sky = 0; ctx->tex.skySample = 0; return PT_OK; }
+    { int jr = joinStreams(ctx); if (jr) return jr; }
     cudaTextureObject_t t; int r = makeTexture(ctx, rgba, w, h, 4, true, &t);
     if (r) return r;
     ctx->tex.sky = t;
+    // the CDF over the dome's texels, pathtracer.h:85-122: energy = max(r,g,b), running float sum in texel order, both
+    // arrays divided by the total afterwards (same operation order, so the same floats as the reference's host loop)
+    const size_t n = (size_t)w * h;
+    std::vector<float> values(n), cum(n);
+    float totalEnergy = 0.0f;
+    for (size_t i = 0; i < n; i++) {
+        const float energy = fmaxf(rgba[4 * i], fmaxf(rgba[4 * i + 1], rgba[4 * i + 2]));
+        values[i] = energy; totalEnergy += energy; cum[i] = totalEnergy;
+    }
+    for (size_t i = 0; i < n; i++) { values[i] /= totalEnergy; cum[i] /= totalEnergy; }
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->skyPdf) { cudaFree(ctx->skyPdf); ctx->skyPdf = nullptr; }
+    if (ctx->skyCdf) { cudaFree(ctx->skyCdf); ctx->skyCdf = nullptr; }
+    CK(cudaMalloc((void**)&ctx->skyPdf, n * sizeof(float))); CK(cudaMalloc((void**)&ctx->skyCdf, n * sizeof(float)));
+    CK(cudaMemcpy(ctx->skyPdf, values.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->skyCdf, cum.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    ctx->tex.skyPdf = ctx->skyPdf; ctx->tex.skyCdf = ctx->skyCdf; ctx->tex.skyW = w; ctx->tex.skyH = h;
+    if (!(totalEnergy > 0.0f)) ctx->tex.skySample = 0;
+    return PT_OK;
+}
+// Opt-in: importance-sample the skydome through the CDF above (the reference builds the CDF and ships
+// binarySearch, kernels.h:65-79, but no kernel samples it -- README.md:55).  Off by default, so parity is untouched.
+PT_API int pt_set_sky_sampling(pt_ctx* ctx, int on) {
+    if (!ctx) return PT_ERR_INVALID;
+    if (on && (!ctx->tex.sky || !ctx->skyCdf)) return fail(ctx, PT_ERR_INVALID, "pt_set_sky_sampling: no skydome texture set (pt_set_skydome)");
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    ctx->tex.skySample = on ? 1u : 0u;
+    return PT_OK;
+}
+// Opt-in: sort the extension / shadow queues the first `bounces` shade launches of a sample produce (counting sort on
+// origin cell x direction octant, 2^bits cells per axis) before they are traced.  Results are identical; scheduling only.
+PT_API int pt_set_ray_sorting(pt_ctx* ctx, int on, uint32_t bits, uint32_t bounces) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    ctx->sortOn = on != 0;
+    if (bits) ctx->sortBits = std::min<uint32_t>(PT_SORT_MAX_BITS, bits);
+    if (bounces) ctx->sortBounces = std::min<uint32_t>(PT_SORT_MAX_BOUNCES, bounces);
+    return PT_OK;
+}
+// Measurement mode: every bounce runs as separate wavefront launches of the counting traversal kernels; pt_get_tally returns
+// node steps / triangle tests / top-level steps of the extension rays [0..2] and of the shadow rays [3..5] since it was
+// switched on.  Images are identical to the normal schedule.
+PT_API int pt_set_counting(pt_ctx* ctx, int on) {
+    if (!ctx) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    ctx->counting = on != 0;
+    if (on) CK(cudaMemsetAsync(ctx->tally, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    return PT_OK;
+}
+PT_API int pt_get_tally(pt_ctx* ctx, uint64_t* out6) {
+    if (!ctx || !out6) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    unsigned long long h[8];
+    CK(cudaMemcpyAsync(h, ctx->tally, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 6; i++) out6[i] = h[i];
+    return PT_OK;
+}
+// Test / measurement hook: the per-bounce queue counters of the most recent sample that ran on working set 0 (clearing,
+// profiled and counting frames always do): out[b] = extension rays of bounce b, out[max_bounces_cap + b] = shadow rays.
+PT_API int pt_debug_read_counters(pt_ctx* ctx, uint32_t* ext_out, uint32_t* shadow_out, uint32_t n) {
+    if (!ctx || !ext_out || !shadow_out || n > PT_MAX_BOUNCES + 1) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    uint32_t h[CNT_TOTAL];
+    CK(cudaMemcpyAsync(h, ctx->set[0].q.cnt, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (uint32_t b = 0; b < n; b++) { ext_out[b] = h[CNT_EXT(b)]; shadow_out[b] = h[CNT_SHADOW(b)]; }
     return PT_OK;
 }
 PT_API int pt_set_sky_constant(pt_ctx* ctx, float r, float g, float b) {
@@ -567,6 +689,22 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     sc.num_triangles = d->num_triangles; sc.num_instances = d->num_instances; sc.num_spheres = d->num_spheres;
     sc.num_planes = d->num_planes; sc.num_lights = (uint)lights.size();
     ctx->numInstancesCap = d->num_instances; ctx->numTlasCap = d->num_tlas_nodes; ctx->numModels = d->num_models;
+    {   // ray-sorting cells span the top-level root box and the spheres (planes are unbounded: origins outside are clamped)
+        float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+        if (d->num_instances && d->num_tlas_nodes) {
+            const pt_tlas_node& rt = d->topBvh[0];
+            const float a[3] = {rt.vmin.x, rt.vmin.y, rt.vmin.z}, b[3] = {rt.vmax.x, rt.vmax.y, rt.vmax.z};
+            for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], a[k]); hi[k] = fmaxf(hi[k], b[k]); }
+        }
+        for (uint32_t i = 0; i < d->num_spheres; i++) {
+            const float c[3] = {d->spheres[i].pos.x, d->spheres[i].pos.y, d->spheres[i].pos.z};
+            for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], c[k] - d->spheres[i].radius); hi[k] = fmaxf(hi[k], c[k] + d->spheres[i].radius); }
+        }
+        float sc3[3];
+        for (int k = 0; k < 3; k++) { if (!(hi[k] > lo[k])) { lo[k] = 0.0f; hi[k] = 1.0f; } sc3[k] = 1.0f / (hi[k] - lo[k]); }
+        sc.sortLo = make_float3(lo[0], lo[1], lo[2]);
+        sc.sortScale = make_float3(sc3[0], sc3[1], sc3[2]);
+    }
     if (d->num_triangles) {
         k_rc_init<<<(d->num_triangles + 255) / 256, 256, 0, ctx->stream>>>(sc.rcRadiance, sc.rcAdditions, d->num_triangles);   // pathtracer.h:220
         CK(cudaGetLastError());
@@ -638,6 +776,20 @@ static DCamera toDCamera(const pt_camera* c) {
     return d;
 }
 
+// Ray sorting buffers (bin keys + fetch permutation per queue entry, both queues) are allocated when sorting is first enabled.
+static int ensureSortBuffers(pt_ctx* ctx) {
+    const size_t cap = std::max<uint32_t>(ctx->map.nSlots, 1024u);
+    for (int k = 0; k < ctx->nSets; k++) {
+        pt_ctx::SampleSet& S = ctx->set[k];
+        for (int qd = 0; qd < 2; qd++) {
+            int r;
+            if (!S.sortKeys[qd] && (r = devAlloc(ctx, &S.sortKeys[qd], cap, false))) return r;
+            if (!S.sortPerm[qd] && (r = devAlloc(ctx, &S.sortPerm[qd], cap, false))) return r;
+        }
+    }
+    return PT_OK;
+}
+
 // Pathtracer::Render, pathtracer.h:224-302.  Asynchronous: only enqueues work.
 PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
     if (!ctx || !cam) return PT_ERR_INVALID;
@@ -646,21 +798,25 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
     const TileMap& map = ctx->map;
     const DCamera dcam = toDCamera(cam);
     const uint32_t npix = map.W * map.H;
-    // Clearing frames and profiled frames run alone on the public stream; converge samples are pipelined.
-    const bool pipelined = !should_clear && !ctx->prof && ctx->nSets >= 2;
+    // Clearing frames, profiled frames and counting frames run alone on the public stream; converge samples are pipelined.
+    const bool pipelined = !should_clear && !ctx->prof && !ctx->counting && ctx->nSets >= 2;
     if (!pipelined) { int jr = joinStreams(ctx); if (jr) return jr; }
     else if (!ctx->forked) {
         CK(cudaEventRecord(ctx->forkEv, ctx->stream));
         for (int k = 0; k < ctx->nSets; k++) CK(cudaStreamWaitEvent(ctx->set[k].stream, ctx->forkEv, 0));
         ctx->forked = true;
     }
+    if (ctx->sortOn) { int sr = ensureSortBuffers(ctx); if (sr) return sr; }
     if (should_clear) {
         ctx->DNEE = ctx->HNEE; ctx->DCACHE = ctx->HCACHE;                                  // :242-243
-        ctx->launches++, k_clear_image<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(ctx->image, ctx->albedo, npix);    // :248-249
+        launchK(ctx, k_clear_image, dim3((npix + 255) / 256), dim3(256), ctx->stream, ctx->image, ctx->albedo, npix);    // :248-249
         ctx->sampleIdx = 0; ctx->randIdx = 0;                                              // :250-251
     }
     const uint32_t nsamples = should_clear ? ctx->cfg.interactive_depth : 1;               // :255
     const bool deviceNEE = ctx->DNEE && ctx->sc.num_lights > 0;                            // globals.h:23
+    const bool skyNEE = ctx->tex.skySample && ctx->tex.sky;                                // opt-in skydome sampling: shadow rays towards the sky
+    const uint32_t nbins = 8u << (3 * ctx->sortBits);
+    ctx->sc.sortBits = ctx->sortBits;
     for (uint32_t sample = 0; sample < nsamples; sample++) {
         pt_ctx::SampleSet& S = ctx->set[pipelined ? ctx->cur : 0];
         pt_ctx::SampleSet& other = ctx->set[pipelined ? (ctx->cur + ctx->nSets - 1) % ctx->nSets : 0];     // the previous sample's set
@@ -678,12 +834,25 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
         if (pipelined && (training || ctx->prevTraining) && other.tailValid && !ctx->knobNoTailWait) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
-        CK(cudaMemsetAsync(S.q.cnt, 0, CNT_TOTAL * sizeof(uint), s));                      // :265 (+ cursors)
-        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); ctx->launches++, k_primary<<<map.nSlots / 256, 256, 0, s>>>(dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
+        const bool overlapped = pipelined && !training && !ctx->prevTraining;
+        const bool sorting = ctx->sortOn && !ctx->counting;
+        CK(cudaMemsetAsync(S.q.cnt, 0, (CNT_TOTAL + (sorting ? (size_t)ctx->sortBounces * 2 * nbins : 0)) * sizeof(uint), s));   // :265 (+ cursors, + sort histograms)
+        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); launchK(ctx, k_primary, dim3(map.nSlots / 256), dim3(256), s, dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
         uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
         if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
         else max_bounces = should_clear ? ctx->cfg.interactive_depth + 1 : ctx->cfg.max_ray_depth;
+        // k_tail (one per-path launch for every bounce >= tailBounce) shortens the dependent-launch chain of a sample that
+        // runs alone (clearing / profiled / cache-training frames: 0.95 -> 0.72 ms on a 1/8 shard).  Samples that overlap
+        // others stay wavefront to the last bounce: their short launches are filled in by the neighbours (measured
+        // 1.77 -> 1.58 ms/sample at 1080p).  Either way the per-path operation order is the same: identical images.
+        const uint32_t waveBounces = ctx->counting ? max_bounces : std::min(max_bounces, (overlapped && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : ctx->tailBounce);
+        const bool connects = (ctx->HNEE && deviceNEE) || skyNEE;                          // :286 (no shadow rays exist when the device _NEE is false)
+        const bool fuse = connects && !ctx->prof && !ctx->counting;                        // connect(b) rides in the launch of extend(b+1)
+        // ray sorting: shade(b) bins the rays it pushes, the two small kernels after it turn the bins into fetch permutations
+        auto sortsExt = [&](uint32_t bounce) { return sorting && bounce < ctx->sortBounces && bounce + 1 < waveBounces; };
+        auto sortsSh = [&](uint32_t bounce) { return sorting && bounce < ctx->sortBounces && connects; };
+        auto histOf = [&](uint32_t bounce, int queue) { return S.sortHist + ((size_t)bounce * 2 + queue) * nbins; };
         auto shadeParams = [&](uint32_t bounce) {
             ShadeParams P;
             P.sc = ctx->sc; P.map = map; P.tex = ctx->tex;
@@ -691,36 +860,51 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             P.sampleCache = S.sampleCache; P.albedoSample = S.albedoSample;
             P.sampleIdx = ctx->sampleIdx; P.randIdx = ctx->randIdx; P.blueFrames = ctx->cfg.blue_noise_frames;
             P.bounce = (int)bounce; P.nee = deviceNEE; P.cache = ctx->DCACHE;
+            // Overlapped (non-training) samples do not write the sample cache: nothing reads it until the cache trains again
+            // after a clearing frame, and then the entries a path does not rewrite (emissive hits, kernels.h:563-576) must be
+            // those of ONE earlier frame -- here the last clearing / training frame -- not of whichever of the samples in
+            // flight wrote last.  (The reference, one sample at a time, leaves the last converge sample's entries there.)
+            P.cacheWrite = !overlapped;
+            P.sortKeys[0] = sortsExt(bounce) ? S.sortKeys[0] : nullptr; P.sortHist[0] = sortsExt(bounce) ? histOf(bounce, 0) : nullptr;
+            P.sortKeys[1] = sortsSh(bounce) ? S.sortKeys[1] : nullptr; P.sortHist[1] = sortsSh(bounce) ? histOf(bounce, 1) : nullptr;
             return P;
         };
-        // k_tail (one per-path launch for every bounce >= tailBounce) shortens the dependent-launch chain of a sample that
-        // runs alone (clearing / profiled / cache-training frames: 0.95 -> 0.72 ms on a 1/8 shard).  Samples that overlap
-        // others stay wavefront to the last bounce: their short launches are filled in by the neighbours (measured
-        // 1.77 -> 1.58 ms/sample at 1080p).  Either way the per-path operation order is the same: identical images.
-        const bool overlapped = pipelined && !training && !ctx->prevTraining;
-        const uint32_t waveBounces = std::min(max_bounces, (overlapped && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : ctx->tailBounce);
-        const bool connects = ctx->HNEE && deviceNEE;                                      // :286 (no shadow rays exist when the device _NEE is false)
-        const bool fuse = connects && !ctx->prof;                                          // connect(b) rides in the launch of extend(b+1)
         auto launchConnect = [&](uint32_t bounce) {
             StageTimer tm(ctx, PT_STAGE_CONNECT, s);
-            ctx->launches++, k_trace<true><<<ctx->gridTraceAny, 128, 0, s>>>(ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
-                                                            S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors);
+            if (ctx->counting)
+                launchK(ctx, k_trace_count<true>, dim3(ctx->gridTraceAny), dim3(128), s, ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
+                        S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors, ctx->tally + 3);
+            else
+                launchK(ctx, k_trace<true>, dim3(ctx->gridTraceAny), dim3(128), s, ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
+                        S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors, sortsSh(bounce) ? S.sortPerm[1] : nullptr);
         };
         for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
+            const uint* extPerm = (bounce > 0 && sortsExt(bounce - 1)) ? S.sortPerm[0] : nullptr;
             if (fuse && bounce > 0) {
                 StageTimer tm(ctx, PT_STAGE_EXTEND, s);
-                ctx->launches++, k_trace_pair<<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce), S.q.cnt + CUR_EXT(bounce), S.q.hits,
-                                                               S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce - 1), S.q.cnt + CUR_CONN(bounce - 1), S.lights, S.accucolors);
+                launchK(ctx, k_trace_pair, dim3(ctx->gridTraceExt), dim3(128), s, ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce), S.q.cnt + CUR_EXT(bounce), S.q.hits,
+                        S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce - 1), S.q.cnt + CUR_CONN(bounce - 1), S.lights, S.accucolors,
+                        extPerm, sortsSh(bounce - 1) ? S.sortPerm[1] : nullptr);
+            } else if (ctx->counting) {
+                launchK(ctx, k_trace_count<false>, dim3(ctx->gridTraceExt), dim3(128), s, ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce),
+                        S.q.cnt + CUR_EXT(bounce), S.q.hits, nullptr, nullptr, ctx->tally);
             } else {
                 StageTimer tm(ctx, PT_STAGE_EXTEND, s);
-                ctx->launches++, k_trace<false><<<ctx->gridTraceExt, 128, 0, s>>>(ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce),
-                                                                 S.q.cnt + CUR_EXT(bounce), S.q.hits, nullptr, nullptr);
+                launchK(ctx, k_trace<false>, dim3(ctx->gridTraceExt), dim3(128), s, ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce),
+                        S.q.cnt + CUR_EXT(bounce), S.q.hits, nullptr, nullptr, extPerm);
             }
             // the previous sample's propagate step rewrites the radiance cache (and shares the sample cache) shading uses:
             // while the cache trains, only primary rays + the first extend overlap the previous sample
-            if (bounce == 0 && pipelined && ctx->prevTraining && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
-            { StageTimer tm(ctx, PT_STAGE_SHADE, s); ctx->launches++, k_shade<<<ctx->gridShade, 128, 0, s>>>(shadeParams(bounce), S.q, buf); }
+            if (bounce == 0 && pipelined && (ctx->prevTraining || training) && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
+            { StageTimer tm(ctx, PT_STAGE_SHADE, s); launchK(ctx, k_shade, dim3(ctx->gridShade), dim3(128), s, shadeParams(bounce), S.q, buf); }
+            if (sortsExt(bounce) || sortsSh(bounce)) {
+                StageTimer tm(ctx, PT_STAGE_OTHER, s);
+                const bool e = sortsExt(bounce), c = sortsSh(bounce);
+                launchK(ctx, k_sort_scan, dim3(2), dim3(1024), s, e ? histOf(bounce, 0) : nullptr, c ? histOf(bounce, 1) : nullptr, nbins);
+                launchK(ctx, k_sort_scatter, dim3(ctx->numSMs * 4), dim3(256), s, e ? S.sortKeys[0] : nullptr, e ? histOf(bounce, 0) : nullptr, S.sortPerm[0], S.q.cnt + CNT_EXT(bounce + 1),
+                        c ? S.sortKeys[1] : nullptr, c ? histOf(bounce, 1) : nullptr, S.sortPerm[1], S.q.cnt + CNT_SHADOW(bounce));
+            }
             ctx->randIdx++;                                                                // :283
             if (connects && (!fuse || bounce + 1 == waveBounces)) launchConnect(bounce);
         }
@@ -728,38 +912,38 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         if (max_bounces > waveBounces) {                                                   // the same bounces, one launch (k_tail)
             if (pipelined) { CK(cudaEventRecord(S.tailStart, s)); S.tailValid = true; }
             StageTimer tm(ctx, PT_STAGE_TAIL, s);
-            ctx->launches++, k_tail<<<ctx->gridTail, 128, 0, s>>>(shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
-                                                 S.q.cnt + CUR_EXT(waveBounces));
+            launchK(ctx, k_tail, dim3(ctx->gridTail), dim3(128), s, shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
+                    S.q.cnt + CUR_EXT(waveBounces));
             ctx->randIdx += max_bounces - waveBounces;                                     // :283, once per bounce
         }
         // image / albedo / statistics / radiance-cache updates happen in sample order
         if (pipelined && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
         auto accumulate = [&]() -> int {
-            if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0));    // a read-back in flight still reads the image
+            if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->imgFree, 0));    // a read-back in flight still reads the image
             if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
-                              ctx->launches++, k_accumulate<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
+                              launchK(ctx, k_accumulate, dim3(map.nSlots / 256), dim3(256), s, map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
             return PT_OK;
         };
         bool accumulated = false;
         if (training) {                                                                    // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING, s);
-            if (map.nSlots) ctx->launches++, k_rc_update<<<map.nSlots / 256, 256, 0, s>>>(map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            if (map.nSlots) launchK(ctx, k_rc_update, dim3(map.nSlots / 256), dim3(256), s, map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             if (ctx->peer.on) {
                 // reduce + propagate + broadcast over peer memory (pt_kernels.cuh): the owner of a triangle range sums every
                 // rank's additions out of their HBM, propagates once and stores the result into every rank's cache
                 const PeerSet& ps = ctx->peer.ps;
                 const uint32_t T = ctx->sc.num_triangles, epoch = ++ctx->peer.epoch;
                 const uint32_t lo = (uint32_t)((uint64_t)T * ps.rank / ps.world), hi = (uint32_t)((uint64_t)T * (ps.rank + 1) / ps.world);
-                ctx->launches++, k_peer_arrive<<<1, 32, 0, s>>>(ps, epoch);
+                launchK(ctx, k_peer_arrive, dim3(1), dim3(32), s, ps, epoch);
                 if (!ctx->prof) { int ar = accumulate(); if (ar) return ar; accumulated = true; }   // the image update fills the wait for the slowest rank
-                ctx->launches++, k_peer_reduce_propagate<<<std::max(1u, (hi - lo + 255u) / 256u), 256, 0, s>>>(ps, epoch, T, lo, hi, ctx->peer.timeoutNs);
-                ctx->launches++, k_peer_finish<<<(unsigned)std::min<size_t>(296, ((size_t)16 * T + 255) / 256), 256, 0, s>>>(ps, epoch, T, ctx->peer.timeoutNs);
+                launchK(ctx, k_peer_reduce_propagate, dim3(std::max(1u, (hi - lo + 255u) / 256u)), dim3(256), s, ps, epoch, T, lo, hi, ctx->peer.timeoutNs);
+                launchK(ctx, k_peer_finish, dim3((unsigned)std::min<size_t>(296, ((size_t)16 * T + 255) / 256)), dim3(256), s, ps, epoch, T, ctx->peer.timeoutNs);
             } else {
                 if (ctx->hook) {
                     int hr = ctx->hook(ctx->hookUser, ctx->sc.rcAdditions, (size_t)16 * ctx->sc.num_triangles, (void*)s);
                     if (hr) return fail(ctx, PT_ERR_INVALID, "pt_render: all-reduce hook failed");
                 }
-                ctx->launches++, k_rc_propagate<<<(ctx->sc.num_triangles + 255) / 256, 256, 0, s>>>(ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+                launchK(ctx, k_rc_propagate, dim3((ctx->sc.num_triangles + 255) / 256), dim3(256), s, ctx->sc.rcRadiance, ctx->sc.rcAdditions, ctx->sc.num_triangles);
             }
         }
         if (!accumulated) { int ar = accumulate(); if (ar) return ar; }
@@ -795,7 +979,7 @@ PT_API int pt_finish(pt_ctx* ctx) {                                             
 PT_API int pt_peer_export(pt_ctx* ctx, void* handle_out) {
     if (!ctx || !handle_out) return PT_ERR_INVALID;
     if (!ctx->haveScene || !ctx->rcBlock) return fail(ctx, PT_ERR_INVALID, "pt_peer_export: no scene uploaded");
-    static_assert(sizeof(cudaIpcMemHandle_t) == PT_PEER_HANDLE_BYTES, "handle size");
+    static_assert(2 * sizeof(cudaIpcMemHandle_t) == PT_PEER_HANDLE_BYTES, "handle size");
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     CK(cudaStreamSynchronize(ctx->stream));
@@ -806,6 +990,16 @@ PT_API int pt_peer_export(pt_ctx* ctx, void* handle_out) {
     cudaIpcMemHandle_t h;
     CK(cudaIpcGetMemHandle(&h, ctx->rcBlock));
     memcpy(handle_out, &h, sizeof(h));
+    // second handle: the framebuffer-gather block.  Rank 0 owns the image ring every rank pushes its tiles into
+    // (pt_gather_image_async); the other ranks export a minimal block so that the handle layout is uniform.
+    if (!ctx->gatherBlock) {
+        ctx->gatherBytes = std::max<size_t>(ctx->cfg.rank == 0 ? (size_t)PT_GATHER_RING * ctx->map.W * ctx->map.H * sizeof(float4) : 0, (size_t)4 << 20);
+        CK(cudaMalloc((void**)&ctx->gatherBlock, ctx->gatherBytes));
+        CK(cudaMemset(ctx->gatherBlock, 0, ctx->gatherBytes));
+    }
+    ctx->gatherEpoch = 0;
+    CK(cudaIpcGetMemHandle(&h, ctx->gatherBlock));
+    memcpy((unsigned char*)handle_out + sizeof(h), &h, sizeof(h));
     return PT_OK;
 }
 PT_API int pt_peer_connect(pt_ctx* ctx, const void* handles, uint32_t world) {
@@ -818,7 +1012,7 @@ PT_API int pt_peer_connect(pt_ctx* ctx, const void* handles, uint32_t world) {
     ps.rank = ctx->cfg.rank; ps.world = world; ps.addOffset = ctx->rcAddOffset; ps.rcOffset = ctx->rcRcOffset;
     for (uint32_t r = 0; r < world; r++) {
         if (r == ctx->cfg.rank) { ps.block[r] = ctx->rcBlock; continue; }
-        cudaIpcMemHandle_t h; memcpy(&h, (const unsigned char*)handles + (size_t)r * sizeof(h), sizeof(h));
+        cudaIpcMemHandle_t h; memcpy(&h, (const unsigned char*)handles + (size_t)r * PT_PEER_HANDLE_BYTES, sizeof(h));
         void* p = nullptr;
         cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
         uint32_t magic = 0;
@@ -831,7 +1025,15 @@ PT_API int pt_peer_connect(pt_ctx* ctx, const void* handles, uint32_t world) {
         ps.block[r] = (unsigned char*)p;
     }
     if (const char* t = getenv("PTB200_PEER_TIMEOUT_MS")) ctx->peer.timeoutNs = (unsigned long long)(atof(t) * 1e6);
-    ctx->peer.ps = ps; ctx->peer.epoch = 0; ctx->peer.on = true;
+    if (ctx->cfg.rank == 0) ctx->gatherRoot = reinterpret_cast<float4*>(ctx->gatherBlock);
+    else {                                           // rank 0's image ring
+        cudaIpcMemHandle_t h; memcpy(&h, (const unsigned char*)handles + sizeof(h), sizeof(h));
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { cudaGetLastError(); peerClose(ctx); return fail(ctx, PT_ERR_CUDA, "pt_peer_connect: cannot map the framebuffer ring of rank 0"); }
+        ctx->gatherOpened = p; ctx->gatherRoot = reinterpret_cast<float4*>(p);
+    }
+    ctx->peer.ps = ps; ctx->peer.epoch = 0; ctx->gatherEpoch = 0; ctx->peer.on = true;
     return PT_OK;
 }
 PT_API int pt_peer_disconnect(pt_ctx* ctx) {
@@ -890,6 +1092,44 @@ static int readAsync(pt_ctx* ctx, float* host, int which, bool tiles, uint64_t* 
     } else {
         CK(cudaMemcpyAsync(host, src, (size_t)ctx->map.W * ctx->map.H * sizeof(float4), cudaMemcpyDeviceToHost, ctx->copyStream));
     }
+    CK(cudaEventRecord(ctx->imgFree, ctx->copyStream));
+    CK(cudaEventRecord(ctx->copyEv[ctx->copyTickets & 7], ctx->copyStream));
+    if (ticket) *ticket = ctx->copyTickets;
+    ctx->copyTickets++;
+    ctx->copyPending = true;
+    return PT_OK;
+}
+// N ranks, ONE framebuffer: every rank calls this after the same Render calls.  Each rank's tiles of the accumulated image go
+// over NVLink into rank 0's image ring (k_gather_push), rank 0 ships the assembled image to `host_full` (pinned, W*H float4;
+// ignored on the other ranks) with one copy.  Asynchronous like pt_read_image_async: later samples keep rendering, only their
+// accumulate step waits until this rank's tiles have been read.  Needs pt_peer_connect; with world_size 1 it is
+// pt_read_image_async.
+PT_API int pt_gather_image_async(pt_ctx* ctx, float* host_full, int which, uint64_t* ticket) {
+    if (!ctx) return PT_ERR_INVALID;
+    if (ctx->cfg.world_size == 1) return readAsync(ctx, host_full, which, false, ticket);
+    if (!ctx->peer.on || !ctx->gatherRoot) return fail(ctx, PT_ERR_INVALID, "pt_gather_image_async: peers are not connected (pt_peer_connect)");
+    if (ctx->cfg.rank == 0 && !host_full) return PT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->cfg.device));
+    if (!ctx->copyStream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->copyReady, cudaEventDisableTiming));
+        for (auto& e : ctx->copyEv) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    if (ctx->forked && ctx->lastSet >= 0 && ctx->set[ctx->lastSet].doneValid) CK(cudaStreamWaitEvent(ctx->copyStream, ctx->set[ctx->lastSet].done, 0));
+    else { CK(cudaEventRecord(ctx->copyReady, ctx->stream)); CK(cudaStreamWaitEvent(ctx->copyStream, ctx->copyReady, 0)); }
+    const uint32_t epoch = ++ctx->gatherEpoch;
+    const size_t npix = (size_t)ctx->map.W * ctx->map.H;
+    float4* slot = ctx->gatherRoot + (size_t)(epoch % PT_GATHER_RING) * npix;
+    const PeerSet& ps = ctx->peer.ps;
+    k_gather_push<<<std::max(1u, ctx->map.nSlots / 256), 256, 0, ctx->copyStream>>>(ps, ctx->map, which == 0 ? ctx->image : ctx->albedo, slot, epoch, PT_GATHER_RING,
+                                                                                  PT_GATHER_ARRIVE, PT_GATHER_CONSUMED, PT_GATHER_COUNTER, ctx->peer.timeoutNs);
+    CK(cudaEventRecord(ctx->imgFree, ctx->copyStream));
+    if (ctx->cfg.rank == 0) {
+        k_gather_wait<<<1, 32, 0, ctx->copyStream>>>(ps, epoch, PT_GATHER_ARRIVE, ctx->peer.timeoutNs);
+        CK(cudaMemcpyAsync(host_full, slot, npix * sizeof(float4), cudaMemcpyDeviceToHost, ctx->copyStream));
+        k_gather_release<<<1, 32, 0, ctx->copyStream>>>(ps, epoch, PT_GATHER_CONSUMED);
+    }
+    CK(cudaGetLastError());
     CK(cudaEventRecord(ctx->copyEv[ctx->copyTickets & 7], ctx->copyStream));
     if (ticket) *ticket = ctx->copyTickets;
     ctx->copyTickets++;

@@ -134,6 +134,7 @@ template <bool ANY>
 __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_count(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
                                                const float4* __restrict__ lights, float4* accucolors, unsigned long long* tallyOut) {
+    pdlWait(); pdlLaunch();
     QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = nullptr;
     Tally tally;
     traceLoop<ANY>(sc, *count, cursor, io, tally);
@@ -181,10 +182,10 @@ __global__ void k_prepare_lights(DScene sc) {
 // permutation, and the traversal kernels fetch rays through that permutation (hits land at the ray's own queue index, so
 // shading order -- and every result -- is untouched).  Queue sizes stay on the device.
 __device__ __forceinline__ uint sortBin(const DScene& sc, float3 o, float3 d) {
-    const float top = (float)((1u << sc.sortBits) - 1u);
-    const uint cx = (uint)fminf(fmaxf((o.x - sc.sortLo.x) * sc.sortScale.x, 0.0f), top);
-    const uint cy = (uint)fminf(fmaxf((o.y - sc.sortLo.y) * sc.sortScale.y, 0.0f), top);
-    const uint cz = (uint)fminf(fmaxf((o.z - sc.sortLo.z) * sc.sortScale.z, 0.0f), top);
+    const float cells = (float)(1u << sc.sortBits), top = cells - 1.0f;          // sortScale = 1 / extent of the scene box
+    const uint cx = (uint)fminf(fmaxf((o.x - sc.sortLo.x) * sc.sortScale.x * cells, 0.0f), top);
+    const uint cy = (uint)fminf(fmaxf((o.y - sc.sortLo.y) * sc.sortScale.y * cells, 0.0f), top);
+    const uint cz = (uint)fminf(fmaxf((o.z - sc.sortLo.z) * sc.sortScale.z * cells, 0.0f), top);
     uint m = 0;
     for (uint b = 0; b < sc.sortBits; b++) m |= (((cx >> b) & 1u) << (3u * b)) | (((cy >> b) & 1u) << (3u * b + 1u)) | (((cz >> b) & 1u) << (3u * b + 2u));
     return (m << 3) | (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
@@ -422,6 +423,7 @@ __global__ void __launch_bounds__(256) k_pack_tiles(TileMap map, const float4* _
 }
 __global__ void k_clear_image(float4* a, float4* b, uint n) {
     const uint i = blockIdx.x * blockDim.x + threadIdx.x;
+    pdlWait(); pdlLaunch();
     if (i < n) { a[i] = make_float4(0, 0, 0, 0); b[i] = make_float4(0, 0, 0, 0); }
 }
 
@@ -715,6 +717,52 @@ __global__ void __launch_bounds__(256) k_peer_finish(PeerSet ps, uint epoch, uin
     float* add = reinterpret_cast<float*>(ps.block[ps.rank] + ps.addOffset);
     const size_t n = (size_t)16 * T;
     for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) add[k] = 0.0f;
+}
+
+// ---- multi-GPU: one framebuffer on rank 0 --------------------------------------------------------------------------------
+// pt_gather_image_async: every rank writes its tiles of the accumulated image straight into a slot of the image ring in
+// rank 0's HBM (NVLink stores through the mapped block), then raises its ARRIVE flag; rank 0 waits for all flags, ships the
+// slot to the host with ONE copy and tells the ranks (CONSUMED) that the slot may be reused PT_GATHER_RING epochs later.
+// Flags live in the header of the radiance-cache block every rank already maps (pt_peer_connect).
+__global__ void __launch_bounds__(256) k_gather_push(PeerSet ps, TileMap map, const float4* __restrict__ image, float4* rootSlot, uint epoch, uint ring,
+                                                     uint arriveWord, uint consumedWord, uint counterWord, unsigned long long timeoutNs) {
+    __shared__ int failed;
+    if (threadIdx.x == 0) {                                  // the slot's previous content (epoch - ring) must have left for the host
+        failed = 0;
+        uint* f = peerFlags(ps, ps.rank);
+        const unsigned long long t0 = globalTimerNs();
+        while (epoch > ring && (int)(ldAcquireSys(f + consumedWord) - (epoch - ring)) < 0) {
+            if (globalTimerNs() - t0 > timeoutNs) { atomicExch_system(f + PT_PEER_ERROR, 1000u + consumedWord); failed = 1; break; }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint x, y;
+    if (!failed && slotToPixel(map, slot, x, y)) stPeer4(rootSlot + (size_t)y * map.W + x, image[(size_t)y * map.W + x]);
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint* f = peerFlags(ps, ps.rank);
+        if (atomicAdd(f + counterWord, 1u) == gridDim.x - 1u) {
+            f[counterWord] = 0u;
+            __threadfence_system();
+            stReleaseSys(peerFlags(ps, 0) + arriveWord + ps.rank, epoch);
+        }
+    }
+}
+__global__ void k_gather_wait(PeerSet ps, uint epoch, uint arriveWord, unsigned long long timeoutNs) {      // rank 0, one block
+    if (threadIdx.x < ps.world) {
+        uint* f = peerFlags(ps, ps.rank);
+        const unsigned long long t0 = globalTimerNs();
+        while ((int)(ldAcquireSys(f + arriveWord + threadIdx.x) - epoch) < 0) {
+            if (globalTimerNs() - t0 > timeoutNs) { atomicExch_system(f + PT_PEER_ERROR, 2000u + threadIdx.x); break; }
+            __nanosleep(64);
+        }
+    }
+}
+__global__ void k_gather_release(PeerSet ps, uint epoch, uint consumedWord) {                                 // rank 0, after the copy to the host
+    if (threadIdx.x < ps.world) stReleaseSys(peerFlags(ps, threadIdx.x) + consumedWord, epoch);
 }
 
 }  // namespace ptb

@@ -163,6 +163,11 @@ typedef struct {
 /* pt_upload_scene converts the BVH2 to the 8-wide layout on the device; this flag selects the host converter instead
  * (same bytes; kept as the checker of the device converter). */
 #define PT_FLAG_HOST_WIDE_BVH 4u
+/* Stage kernels are launched with programmatic dependent launch (the next kernel's blocks are scheduled while the previous
+ * one drains; every kernel waits for its predecessor's results itself).  This flag restores plain stream order. */
+#define PT_FLAG_NO_PDL 8u
+/* Ray sorting between shade and trace on from the start (see pt_set_ray_sorting). */
+#define PT_FLAG_SORT_RAYS 16u
 
 typedef struct {                       /* device-side ray counters since the last pt_reset_stats */
     uint64_t primary_rays, extend_rays, shadow_rays, shade_calls, samples;
@@ -196,13 +201,21 @@ PT_API int  pt_set_skydome(pt_ctx*, const float* rgba, uint32_t w, uint32_t h); 
 PT_API int  pt_set_sky_constant(pt_ctx*, float r, float g, float b);            /* constant sky radiance (default 1,1,1) when no HDR dome is available */
 PT_API int  pt_set_blue_noise(pt_ctx*, const float* lum, uint32_t w, uint32_t h); /* ~ loadTextureL (use_cuda.h:166-200) */
 PT_API int  pt_texture_create(pt_ctx*, const float* rgba, uint32_t w, uint32_t h, uint64_t* out_handle); /* ~ loadTexture (use_cuda.h:108-164) */
+/* SURVEY 8(f) row 4, both opt-in (defaults reproduce the reference's shipped behaviour):
+ * skydome importance sampling through the CDF Pathtracer::Init builds (pathtracer.h:85-122, binarySearch kernels.h:65-79;
+ * the reference never samples it): diffuse vertices send their shadow ray to a dome texel drawn from the CDF, sky radiance
+ * is then counted by those rays instead of by diffuse paths that escape;
+ * ray sorting (the reference's disabled experiment, src/raySorting.h:1-68): counting sort of the extension and shadow queues
+ * by (origin cell, direction octant) between shade and trace; results are bit-identical, only the traversal order changes. */
+PT_API int  pt_set_sky_sampling(pt_ctx*, int on);
+PT_API int  pt_set_ray_sorting(pt_ctx*, int on, uint32_t bits_per_axis /* 1..5, 0 = keep */, uint32_t bounces /* 1..2, 0 = keep */);
 PT_API int  pt_set_allreduce_hook(pt_ctx*, pt_allreduce_hook hook, void* user);
 /* Multi-GPU exchange over NVLink peer memory, the default transport of the radiance-cache step on one box (replaces the
  * hook + propagate pair == what kernel_update_buckets -> [all-reduce] -> kernel_propagate_buckets needs, kernels.h:863-905):
  * every rank exports the cudaIpc handle of its radiance-cache block, the caller gathers the handles of all ranks in rank
  * order (any transport) and hands them to pt_peer_connect; training frames then run ONE fused reduce + propagate +
  * broadcast kernel per rank over the peers' HBM.  All ranks must render the same sequence of frames. */
-#define PT_PEER_HANDLE_BYTES 64
+#define PT_PEER_HANDLE_BYTES 128    /* two cudaIpc handles: radiance-cache block, framebuffer-gather block */
 PT_API int  pt_peer_export(pt_ctx*, void* handle_out /* PT_PEER_HANDLE_BYTES */);
 PT_API int  pt_peer_connect(pt_ctx*, const void* handles /* world_size x PT_PEER_HANDLE_BYTES, rank order */, uint32_t world_size);
 PT_API int  pt_peer_disconnect(pt_ctx*);
@@ -218,6 +231,10 @@ PT_API int  pt_read_tiles(pt_ctx*, float* host_rgbw_slots, int which);  /* this 
 PT_API int  pt_read_image_async(pt_ctx*, float* host_rgbw, int which, uint64_t* ticket);
 PT_API int  pt_read_tiles_async(pt_ctx*, float* host_rgbw_slots, int which, uint64_t* ticket);
 PT_API int  pt_wait_read(pt_ctx*, uint64_t ticket);
+/* N ranks, one framebuffer (SURVEY 8(e) "end of run: gather tiles"; main.cpp:308-319 has one consumer per frame): collective
+ * over the connected peers.  Every rank's tiles travel over NVLink into an image ring in rank 0's HBM, rank 0 ships the
+ * assembled W*H float4 image to host_full (pinned; ignored on other ranks) with one copy.  Asynchronous, tickets as above. */
+PT_API int  pt_gather_image_async(pt_ctx*, float* host_full, int which, uint64_t* ticket);
 PT_API int  pt_write_pfm(pt_ctx*, const char* path, int which);        /* headless render-to-PFM (display value rgb / w, main.cpp:58-62) in place of the GLFW window */
 /* Display post-process (main.cpp:46-171,316-376: demodulated separable Gaussian, remodulate, gamma 2, vignette) as CUDA
  * kernels; host float4 in (or NULL, NULL = the context's accumulators), host float4 RGBA out. */
@@ -246,6 +263,11 @@ PT_API int  pt_debug_read_wide_bvh(pt_ctx*, void* nodes, uint32_t* n_nodes, void
 #define PT_NUM_STAGES 6
 PT_API int  pt_set_profiling(pt_ctx*, int on);                         /* also resets the accumulators */
 PT_API int  pt_get_profile(pt_ctx*, double* ms /*[PT_NUM_STAGES]*/, uint64_t* launches /*[PT_NUM_STAGES]*/);
+/* Measurement mode for the roofline line: every bounce as separate wavefront launches of counting traversal kernels;
+ * pt_get_tally: node steps, triangle tests, top-level steps of the extension rays [0..2] and of the shadow rays [3..5]. */
+PT_API int  pt_set_counting(pt_ctx*, int on);
+PT_API int  pt_get_tally(pt_ctx*, uint64_t* out6);
+PT_API int  pt_debug_read_counters(pt_ctx*, uint32_t* ext_out, uint32_t* shadow_out, uint32_t n_bounces);   /* per-bounce queue sizes of the last sample on working set 0 */
 PT_API int  pt_get_stats(pt_ctx*, pt_stats* out);
 PT_API int  pt_reset_stats(pt_ctx*);
 PT_API int  pt_get_rand_state(pt_ctx*, uint32_t* sampleIdx, uint32_t* randIdx);
