@@ -71,7 +71,7 @@ class Stats(C.Structure):              # pt_stats
 ALLREDUCE_HOOK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 
 
-FLAG_WAVEFRONT_ONLY, FLAG_NO_PIPELINE, FLAG_HOST_WIDE_BVH = 1, 2, 4      # PT_FLAG_* (include/ptb200.h)
+FLAG_WAVEFRONT_ONLY, FLAG_NO_PIPELINE, FLAG_HOST_WIDE_BVH, FLAG_NO_PDL, FLAG_SORT_RAYS = 1, 2, 4, 8, 16      # PT_FLAG_* (include/ptb200.h)
 
 
 def default_config(width=640, height=480, max_ray_depth=32, interactive_depth=1, guiding_frames=100,

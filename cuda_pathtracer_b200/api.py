@@ -81,6 +81,12 @@ def load_library():
     L.pt_get_rand_state.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.pt_debug_primary_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
     L.pt_debug_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+    L.pt_set_sky_sampling.argtypes = [C.c_void_p, C.c_int]
+    L.pt_set_ray_sorting.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32]
+    L.pt_set_counting.argtypes = [C.c_void_p, C.c_int]
+    L.pt_get_tally.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    L.pt_debug_read_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+    L.pt_gather_image_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
     L.pt_debug_trace_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.POINTER(C.c_float), C.c_void_p]
     _LIB = L
     return L
@@ -189,6 +195,36 @@ class Pathtracer:
         self._ck(self.L.pt_texture_create(self.h, abi.ptr(rgba), rgba.shape[1], rgba.shape[0], C.byref(out)), "pt_texture_create")
         return out.value
 
+    def set_sky_sampling(self, on):
+        """Opt-in skydome importance sampling through the CDF of pathtracer.h:85-122 (the reference builds it, no kernel samples it)."""
+        self._ck(self.L.pt_set_sky_sampling(self.h, int(bool(on))), "pt_set_sky_sampling")
+
+    def set_ray_sorting(self, on, bits=0, bounces=0):
+        """Opt-in counting sort of the extension / shadow queues by (origin cell, direction octant) between shade and trace
+        (the reference's disabled experiment, src/raySorting.h); images are bit-identical."""
+        self._ck(self.L.pt_set_ray_sorting(self.h, int(bool(on)), int(bits), int(bounces)), "pt_set_ray_sorting")
+
+    def set_counting(self, on):
+        self._ck(self.L.pt_set_counting(self.h, int(bool(on))), "pt_set_counting")
+
+    def tally(self):
+        """{'extend': (node steps, triangle tests, top-level steps), 'connect': (...)} since set_counting(True)."""
+        out = (C.c_uint64 * 6)()
+        self._ck(self.L.pt_get_tally(self.h, out), "pt_get_tally")
+        return {"extend": tuple(int(x) for x in out[0:3]), "connect": tuple(int(x) for x in out[3:6])}
+
+    def debug_read_counters(self, n):
+        e, s = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        self._ck(self.L.pt_debug_read_counters(self.h, abi.ptr(e), abi.ptr(s), n), "pt_debug_read_counters")
+        return e, s
+
+    def gather_image_async(self, out, which=0):
+        """Collective over the connected peers: the N-rank framebuffer assembled over NVLink in rank 0's HBM and shipped to
+        `out` ((H, W, 4) pinned float32 on rank 0, None elsewhere) with one copy.  Returns a ticket for wait_read()."""
+        t = C.c_uint64()
+        self._ck(self.L.pt_gather_image_async(self.h, abi.ptr(out) if out is not None else None, int(which), C.byref(t)), "pt_gather_image_async")
+        return t.value
+
     def set_guiding_frames(self, frames):
         """Frames during which the radiance cache trains (reference pathtracer.h:292 hard-codes 100)."""
         self._ck(self.L.pt_set_guiding_frames(self.h, int(frames)), "pt_set_guiding_frames")
@@ -271,16 +307,17 @@ class Pathtracer:
         self._ck(self.L.pt_set_allreduce_hook(self.h, self._hook, None), "pt_set_allreduce_hook")
 
     def peer_export(self):
-        """cudaIpc handle (64 bytes) of this rank's radiance-cache block; gather them over all ranks for peer_connect."""
-        buf = C.create_string_buffer(64)
+        """cudaIpc handles (2 x 64 bytes: radiance-cache block, framebuffer-gather block) of this rank; gather them over all
+        ranks for peer_connect."""
+        buf = C.create_string_buffer(128)
         self._ck(self.L.pt_peer_export(self.h, buf), "pt_peer_export")
         return buf.raw
 
     def peer_connect(self, handles):
-        """handles: the 64-byte handles of all ranks in rank order.  Training frames then exchange the radiance-cache
+        """handles: the 128-byte handle blobs of all ranks in rank order.  Training frames then exchange the radiance-cache
         additions with the fused reduce + propagate kernel over NVLink peer memory instead of hook + propagate."""
         blob = b"".join(handles)
-        self._ck(self.L.pt_peer_connect(self.h, blob, len(blob) // 64), "pt_peer_connect")
+        self._ck(self.L.pt_peer_connect(self.h, blob, len(blob) // 128), "pt_peer_connect")
 
     def peer_disconnect(self):
         self._ck(self.L.pt_peer_disconnect(self.h), "pt_peer_disconnect")

@@ -48,7 +48,7 @@ class OracleLib:
             L.ora_add_texture.restype = C.c_uint64
             L.ora_rand.restype = C.c_float
             for n in ("ora_destroy", "ora_set_threads", "ora_upload_scene", "ora_update_instances", "ora_set_toggles",
-                      "ora_set_skydome", "ora_set_sky_constant", "ora_set_blue_noise", "ora_add_texture", "ora_render",
+                      "ora_set_skydome", "ora_set_sky_sampling", "ora_set_sky_constant", "ora_set_blue_noise", "ora_add_texture", "ora_render",
                       "ora_read_image", "ora_read_radiance_cache", "ora_get_stats", "ora_reset_stats",
                       "ora_get_rand_state", "ora_primary_rays", "ora_trace"):
                 getattr(L, n).argtypes = None
@@ -87,6 +87,10 @@ class OracleLib:
 
     def set_sky_constant(self, r, g, b):
         self.L.ora_set_sky_constant(self.h, F(r), F(g), F(b))
+
+    def set_sky_sampling(self, on):
+        if self.L.ora_set_sky_sampling(self.h, C.c_int(int(on))) != 0:
+            raise RuntimeError("ora_set_sky_sampling: no skydome set")
 
     def set_blue_noise(self, lum):
         lum = np.ascontiguousarray(lum, np.float32)

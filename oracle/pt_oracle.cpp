@@ -172,6 +172,7 @@ struct Scene {
     std::vector<pt_triangle_light> lights;     // pathtracer.h:155-167
     std::vector<pt_radiance_cache> rc;         // kernels.h:848-861
     Tex sky; f3 skyConst; bool hasSky;
+    std::vector<float> skyPdf, skyCdf; bool skySample = false;   // CDF of pathtracer.h:85-122; sampling is this repo's opt-in (pt_set_sky_sampling)
     Tex blue; bool hasBlue;
     std::vector<Tex> textures;                 // material.texture / normal_texture = index+1 into this table
 };
@@ -472,6 +473,19 @@ static inline f3 skyLookup(const Oracle& o, f3 dir) {           // kernels.h:527
     f2 uv = normalToUv(dir); float c[4]; tex2D4(o.sc.sky, uv.x, uv.y, c); return mk3(c[0], c[1], c[2]);
 }
 
+// kernels.h:65-79 completed (see binarySearchCdf in csrc/pt_shade.cuh): first texel whose cumulative value reaches target
+static inline uint binarySearchCdf(const float* values, uint nrValues, float target) {
+    uint L = 0, R = nrValues - 1;
+    while (L + 1 < R) { const uint m = (L + R) / 2; if (values[m] >= target) R = m; else L = m; }
+    return values[L] >= target ? L : R;
+}
+static inline f3 skyUvToDir(float u, float v, float& sinPolar) {     // inverse of normalToUv under wrap addressing
+    const float theta = u * 2.0f * PI;
+    const float a = PI * (1.0f - v);
+    sinPolar = sinf(a);
+    return mk3(sinf(theta) * sinPolar, cosf(a), cosf(theta) * sinPolar);
+}
+
 struct ShadeOut { bool pushExt, pushShadow; pt_ray ext, shadow; };
 
 // kernel_shade, kernels.h:513-796, for queue entry i.  Queue pushes are returned instead of atomically appended.
@@ -488,7 +502,7 @@ static void shadeOne(Oracle& o, uint i, int bounce, uint randIdx, ShadeOut& out)
     if (!hit.intersected()) {                                // kernels.h:526-538
         f3 sk = skyLookup(o, ray.direction);
         if (!state.albedoSet) { updateAlbedo(o, state.mask * sk, x, y); state.albedoSet = true; }
-        state.accucolor += state.mask * sk;
+        if (!(o.sc.skySample && o.sc.hasSky) || state.fromSpecular) state.accucolor += state.mask * sk;
         setState(o, ray.pixeli, state);
         if (bounce < MAX_CACHE_DEPTH) o.sampleCache[cache_id] = cache;
         return;
@@ -589,7 +603,29 @@ static void shadeOne(Oracle& o, uint i, int bounce, uint randIdx, ShadeOut& out)
     } else {                                                 // kernels.h:662-782
         if (!state.albedoSet) { updateAlbedo(o, state.mask * diffuse, x, y); state.albedoSet = true; }
         state.fromSpecular = false;
-        if (NEE) {                                           // kernels.h:672-753
+        // skydome importance sampling, opt-in: same statements as shadeOne in csrc/pt_shade.cuh
+        bool lightNee = NEE, skyNee = o.sc.skySample && o.sc.hasSky;
+        float pickScale = 1.0f;
+        if (lightNee && skyNee) { pickScale = 2.0f; if (rnd(rs) < 0.5f) lightNee = false; else skyNee = false; }
+        if (skyNee) {
+            const uint SW = o.sc.sky.w, SH = o.sc.sky.h;
+            const uint m = binarySearchCdf(o.sc.skyCdf.data(), SW * SH, rnd(rs));
+            const uint tx = m % SW, ty = m / SW;
+            const float sa = rnd(rs); const float sb = rnd(rs);
+            const float su = ((float)tx + sa) / (float)SW, sv = ((float)ty + sb) / (float)SH;
+            float sinPolar;
+            const f3 sdir = skyUvToDir(su, sv, sinPolar);
+            const float pdf = o.sc.skyPdf[m] * (float)(SW * SH) / (2.0f * PI * PI * fmaxf(sinPolar, 0.0001f));
+            const float NL = dot(colliderNormal, sdir);
+            if (NL > 0 && dot(sdir, surfaceNormal) > 0 && pdf > 0) {
+                const f3 sk = skyLookup(o, sdir);
+                state.light = state.mask * (BRDF * sk * (NL * pickScale / pdf));
+                const float f = NL * NL * NL;
+                Ray shadowRay = mkRay(intersectionPos + EPS * f * sdir + EPS * (1 - f) * colliderNormal, sdir, ray.pixeli);
+                out.pushShadow = true; out.shadow = pack(shadowRay);
+            }
+        }
+        if (lightNee) {                                      // kernels.h:672-753
             uint successIdx = 0; float valid = 0.0f;
             for (uint k = 0; k < 4; k++) {
                 uint lightSource = uint(rnd(rs) * numLights) % numLights;
@@ -630,6 +666,7 @@ static void shadeOne(Oracle& o, uint i, int bounce, uint randIdx, ShadeOut& out)
                     float SA = LNL * A * invShadowLength * invShadowLength;
                     // NL * SA * size * BRDF * emission * (valid/4): left-to-right, float*uint -> float
                     state.light = state.mask * (NL * SA * numLights * BRDF * emission * (valid / 4.0f));
+                    if (pickScale != 1.0f) state.light *= pickScale;
                     const float f = LNL * LNL * LNL;
                     Ray shadowRay = mkRay(samplePoint + f * EPS * shadowDir + (1 - f) * EPS * lightNormal, shadowDir, ray.pixeli);
                     shadowRay.length = shadowLength - 2 * EPS;
@@ -812,7 +849,7 @@ static void render(Oracle& o, const pt_camera& pcam, bool shouldClear) {
             extend(o);
             shade(o, (int)bounce, o.randIdx);
             o.randIdx++;
-            if (o.HNEE) connect(o);
+            if (o.HNEE || o.sc.skySample) connect(o);
             o.rayQ.swap(o.rayQNew); o.rayQNew.clear(); o.shadowQ.clear();
         }
         if (!shouldClear && o.HCACHE && o.sampleIdx < o.cfg.guiding_frames) {   // :292-296
@@ -874,6 +911,22 @@ ORA_API void ora_update_instances(void* h, const pt_instance* inst, uint32_t n, 
 ORA_API void ora_set_toggles(void* h, int nee, int guiding) { Oracle& o = *(Oracle*)h; o.HNEE = nee != 0; o.HCACHE = guiding != 0; }
 ORA_API void ora_set_skydome(void* h, const float* rgba, uint32_t w, uint32_t hh) {
     Oracle& o = *(Oracle*)h; o.sc.sky.data = rgba; o.sc.sky.w = w; o.sc.sky.h = hh; o.sc.sky.ch = 4; o.sc.hasSky = rgba != nullptr;
+}
+ORA_API int ora_set_sky_sampling(void* h, int on) {               // builds the CDF exactly as pathtracer.h:85-122 does
+    Oracle& o = *(Oracle*)h;
+    if (on && !o.sc.hasSky) return -1;
+    if (on) {
+        const size_t n = (size_t)o.sc.sky.w * o.sc.sky.h;
+        o.sc.skyPdf.resize(n); o.sc.skyCdf.resize(n);
+        float totalEnergy = 0.0f;
+        for (size_t i = 0; i < n; i++) {
+            const float energy = fmaxf(o.sc.sky.data[4 * i], fmaxf(o.sc.sky.data[4 * i + 1], o.sc.sky.data[4 * i + 2]));
+            o.sc.skyPdf[i] = energy; totalEnergy += energy; o.sc.skyCdf[i] = totalEnergy;
+        }
+        for (size_t i = 0; i < n; i++) { o.sc.skyPdf[i] /= totalEnergy; o.sc.skyCdf[i] /= totalEnergy; }
+    }
+    o.sc.skySample = on != 0;
+    return 0;
 }
 ORA_API void ora_set_sky_constant(void* h, float r, float g, float b) { Oracle& o = *(Oracle*)h; o.sc.hasSky = false; o.sc.skyConst = mk3(r, g, b); }
 ORA_API void ora_set_blue_noise(void* h, const float* lum, uint32_t w, uint32_t hh) {

@@ -1,8 +1,10 @@
 """-m gpu: the radiance-cache exchange over peer memory (pt_peer_export / pt_peer_connect, k_peer_arrive /
 k_peer_reduce_propagate / k_peer_finish) against the plain propagate step (reference src/kernels.h:884-905).
-world 1: the fused kernel must give the SAME bits as k_rc_propagate.  world 2: two processes on the one GPU of the test
-box map each other's block through cudaIpc and run the real protocol (flags, owner ranges, broadcast); checked against
-the all-reduce hook and against one rank (tools/multi_gpu_check.py --same-gpu)."""
+world 1: the fused kernel must agree with k_rc_propagate.  world 2: two processes map each other's block through cudaIpc and
+run the real protocol (flags, owner ranges, broadcast) plus the framebuffer gather; checked against the all-reduce hook and
+against one rank (tools/multi_gpu_check.py).  The two-rank test needs two GPUs: kernels of different processes that wait on
+each other's flags must not share one GPU (nothing guarantees they are co-scheduled; B200_PROFILING.md), so on a one-GPU
+box it is skipped and the protocol is covered by tools/multi_gpu_check.py runs on 2 and 8 GPUs (profiles/scaling/)."""
 import json
 import os
 import socket
@@ -63,19 +65,28 @@ def test_peer_connect_rejects_wrong_world_and_missing_scene():
     arrays = scenes.teapot_like_scene(8).arrays()
     pt = api.Pathtracer(arrays, cfg).Init()
     h = pt.peer_export()
-    assert len(h) == 64
+    assert len(h) == 128
     with pytest.raises(api.PtError):
         pt.peer_connect([h, h])                     # world_size is 1 in the config
     pt.peer_connect([h]); pt.peer_disconnect()
     pt.close()
 
 
+def _gpu_count():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_gpu_count() < 2, reason="needs two GPUs: cross-process flag waits must not share one GPU")
 @pytest.mark.parametrize("size", ["256x144", "32x32"])          # 32x32: one tile, rank 1 has no pixels but still takes part in the exchange
-def test_two_processes_one_gpu_peer_protocol(size):
+def test_two_ranks_peer_protocol(size):
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     env = dict(os.environ, PTB200_PEER_TIMEOUT_MS="20000")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", str(port), os.path.join(ROOT, "tools", "multi_gpu_check.py"), "--same-gpu", "--frames", "20", "--size", size]
+           "--master-port", str(port), os.path.join(ROOT, "tools", "multi_gpu_check.py"), "--frames", "20", "--size", size]
     p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=420)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
     line = [l for l in p.stdout.splitlines() if l.startswith("{")][-1]

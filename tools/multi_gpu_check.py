@@ -59,13 +59,20 @@ for guiding, frames, transport in ((False, 8, "hook"), (True, args.frames, "hook
         pt.Render(cam, shouldClear=True)
         for _ in range(frames):
             pt.Render(cam)
+        gathered = None
+        if multi and transport == "peer":              # one framebuffer on rank 0: tiles over NVLink into its image ring, one copy to the host
+            host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy() if r == 0 else None
+            for _ in range(6):                          # more epochs than ring slots: exercises the slot-reuse handshake
+                t = pt.gather_image_async(host)
+            pt.wait_read(t)
+            gathered = host.copy() if r == 0 else None
         pt.Finish()
         img = pt.read_image().copy(); rc = pt.read_radiance_cache()["radianceCache"].copy()
         if multi and transport == "peer":
             disconnect_peers(pt)
         pt.close()
-        return img, rc
-    img, rc = render(rank, world, True)
+        return (img, rc, gathered) if multi else (img, rc)
+    img, rc, gathered = render(rank, world, True)
     full = gather_sum(img)
     rcs = gather_all(rc)
     if rank == 0:
@@ -77,10 +84,11 @@ for guiding, frames, transport in ((False, 8, "hook"), (True, args.frames, "hook
             "frames": frames, "bit_identical": bool(np.array_equal(full, ref)), "rel_rmse": err,
             "samples_ok": bool(np.all(full[..., 3] == frames + 1)), "caches_replicated_bitwise": replicated,
             "cache_moved": bool(np.any(rc1 != 0.1)),
+            "gathered_image_identical": None if gathered is None else bool(np.array_equal(gathered, full)),
             "cache_rel_rmse_vs_1rank": float(np.sqrt(np.mean((rcs[0] - rc1) ** 2)) / np.sqrt(np.mean(rc1 ** 2)))}
     dist.barrier()
 if rank == 0:
-    ok = out["guiding_off"]["bit_identical"] and all(out[k]["rel_rmse"] < 2e-2 and out[k]["samples_ok"] and out[k]["caches_replicated_bitwise"] and out[k]["cache_moved"]
+    ok = out["guiding_off"]["bit_identical"] and out["guiding_on_peer"]["gathered_image_identical"] and all(out[k]["rel_rmse"] < 2e-2 and out[k]["samples_ok"] and out[k]["caches_replicated_bitwise"] and out[k]["cache_moved"]
                                                      for k in ("guiding_on_hook", "guiding_on_peer"))
     print(json.dumps({"world": world, "same_gpu": args.same_gpu, "ok": bool(ok), **out}))
 dist.destroy_process_group()
