@@ -29,6 +29,10 @@ sys.path.insert(0, ROOT)
 W, H, DEPTH = 1920, 1080, 8
 METRIC = "Mrays/s on sibenik 1080p (NEE + path guiding, depth 8)"
 WORKLOAD = "sibenik-proxy (cathedral+statue+emissive cube+2 spheres, 158k tris) 1920x1080, NEE on, guiding on, MAX_RAY_DEPTH 8"
+# identical in both arms (ours and --impl reference): what is measured, not how
+CONFIG = {"workload": WORKLOAD, "resolution": "1920x1080", "max_ray_depth": 8, "nee": True, "path_guiding": True, "guiding_frames": 100,
+          "cameras": "16-camera sweep inside the nave, one camera per step", "global_pixels": W * H,
+          "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2"}
 CPU_W, CPU_H = 1920, 1080    # bounded CPU sample: the same workload, a few samples (about 10-20 s on 16 cores)
 CPU_SAMPLES = 16
 
@@ -208,7 +212,7 @@ def reference_arm(args):
     v = total_rays / total_s / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": WORKLOAD, "sample": "%dx%d pixels of the same scene/camera/depth per step" % (CPU_W, CPU_H)},
+            "data": "synthetic", "config": CONFIG,
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
                              "sample": "oracle/pt_oracle.cpp, 1 converge sample at %dx%d per step, OpenMP %d threads" % (CPU_W, CPU_H, threads)},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -217,6 +221,7 @@ def reference_arm(args):
 
 
 def gpu_arm(args):
+    import zlib
     import torch
     import torch.distributed as dist
     from cuda_pathtracer_b200 import abi, api
@@ -229,58 +234,40 @@ def gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     arrays = build_scene().arrays()
-    cfg = abi.default_config(W, H, max_ray_depth=DEPTH, interactive_depth=1, device=local, rank=rank, world_size=world)
+    flags = abi.FLAG_SORT_RAYS if args.sort else 0
+    cfg = abi.default_config(W, H, max_ray_depth=DEPTH, interactive_depth=1, device=local, rank=rank, world_size=world, flags=flags)
     pt = api.Pathtracer(arrays, cfg).Init()
     stream = torch.cuda.ExternalStream(pt.stream(), device=torch.device("cuda", local))
-    exchange = "none"
+    exchange, peers = "none", False
     if world > 1:
         # radiance-cache exchange of the training frames: the library's fused reduce + propagate + broadcast kernel over NVLink
         # peer memory; --exchange nccl (or a failed peer mapping) selects the all-reduce hook + local propagate instead
         from cuda_pathtracer_b200.distributed import make_allreduce_hook, connect_peers
         exchange = "nccl all-reduce + propagate"
         if args.exchange == "peer" and connect_peers(pt, torch.device("cuda", local)):
-            exchange = "fused reduce+propagate over NVLink peer memory"
+            exchange, peers = "fused reduce+propagate over NVLink peer memory", True
         else:
             pt.set_allreduce_hook(make_allreduce_hook(torch.device("cuda", local)))   # NCCL sum over NVLink on the stream the sample runs on
     cams = [camera_for(i, W, H) for i in range(16)]
+    warm = max(args.warmup, 3)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    pt.Render(cams[0], shouldClear=True)
-    pt.Finish()
     step = 0
-    for _ in range(max(args.warmup, 3)):
-        pt.Render(cams[step % 16]); step += 1
-    pt.Finish()
-    # ---- timed region: device time, scene + queues resident in HBM ----
-    pt.reset_stats()
-    sampler = ClockSampler(local)
-    barrier()
-    sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(args.steps):
-        pt.Render(cams[step % 16]); step += 1
-    pt.join()                  # renders run on the library's private streams: order them before the end event
-    e1.record(stream)
-    pt.Finish()
-    barrier()
-    sampler.stop_flag = True
-    ms = e0.elapsed_time(e1)
-    st = pt.stats()
-    timed_launches = int(st.kernel_launches)
-    rays = torch.tensor([st.extend_rays + st.shadow_rays, st.extend_rays, st.shadow_rays], dtype=torch.float64, device="cuda")
-    tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(rays)
-        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-    ms = float(tms.item())
-    total_rays, ext_rays, sh_rays = (float(x) for x in rays.tolist())
-    value = total_rays / (ms * 1e-3) / 1e6
-    # ---- the two phases of the reference's frame loop, separately (pathtracer.h:292: the cache trains while sampleIdx < 100) ----
+
+    def restart():
+        """Every measured pass starts from the same state: clearing frame (sampleIdx 0), then `warm` converge samples, so each
+        pass covers the same samples -- and the same radiance-cache training phase -- as the timed region."""
+        nonlocal step
+        pt.Render(cams[0], shouldClear=True)
+        step = 0
+        for _ in range(warm):
+            pt.Render(cams[step % 16]); step += 1
+        pt.Finish()
+
     def timed_pass(n):
         nonlocal step
         barrier()
@@ -288,19 +275,50 @@ def gpu_arm(args):
         a.record(stream)
         for _ in range(n):
             pt.Render(cams[step % 16]); step += 1
-        pt.join(); b.record(stream); pt.Finish(); barrier()
+        pt.join(); b.record(stream); pt.Finish(); barrier()       # renders run on the library's private streams: join orders them before the end event
         t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()) / n
+        return float(t.item())
+
+    # ---- timed region: device time, scene + queues resident in HBM ----
+    restart()
+    pt.reset_stats()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms = timed_pass(args.steps)
+    sampler.stop_flag = True
+    st = pt.stats()
+    timed_launches = int(st.kernel_launches)
+    rays = torch.tensor([st.extend_rays + st.shadow_rays, st.extend_rays, st.shadow_rays], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(rays)
+    total_rays, ext_rays, sh_rays = (float(x) for x in rays.tolist())
+    value = total_rays / (ms * 1e-3) / 1e6
+    rays_per_step = total_rays / args.steps
+    # the same window again (20 steps are tens of milliseconds: one scheduler hiccup is several percent)
+    windows = [value]
+    for _ in range(4):
+        restart()
+        windows.append(total_rays / (timed_pass(args.steps) * 1e-3) / 1e6)
+    # N > 1: every rank must hold the same radiance cache after the same frames (the exchange replicates it)
+    exchange_check = None
+    if world > 1:
+        crc = zlib.crc32(pt.read_radiance_cache()["radianceCache"].tobytes())
+        crcs = [None] * world
+        dist.all_gather_object(crcs, crc)
+        exchange_check = {"radiance_cache_crc32_per_rank": crcs, "replicated": len(set(crcs)) == 1}
+    # ---- the two phases of the reference's frame loop, separately (pathtracer.h:292: the cache trains while sampleIdx < 100) ----
     phase_steps = max(10, min(50, args.steps))
     pt.set_guiding_frames(1 << 30)
-    training_ms = timed_pass(phase_steps)          # every frame: update buckets, all-reduce over ranks, propagate
+    restart()
+    training_ms = timed_pass(phase_steps) / phase_steps          # every frame: update buckets, exchange over ranks, propagate
     pt.set_guiding_frames(0)
-    timed_pass(3)
-    steady_ms = timed_pass(phase_steps)            # cache frozen, guiding still steers the samples
-    rays_per_step = total_rays / args.steps
-    # ---- per-stage device time of the same steps (separate pass: event pairs around every launch) ----
+    timed_pass(8)
+    steady_ms = timed_pass(phase_steps) / phase_steps            # cache frozen, guiding still steers the samples; 4-8 samples in flight
+    pt.set_guiding_frames(100)                                   # back to the reference's window for everything below
+    # ---- per-stage device time of the same steps (separate pass: event pairs around every launch, samples serialised) ----
+    restart()
     pt.set_profiling(True)
     pt.reset_stats()
     for _ in range(args.steps):
@@ -309,42 +327,71 @@ def gpu_arm(args):
     prof = pt.profile()
     pst = pt.stats()
     pt.set_profiling(False)
+    # ---- what the wide layout actually requests: node steps / triangle tests counted by the traversal kernels themselves ----
+    count_steps = min(args.steps, 8)
+    restart()
+    pt.set_counting(True)
+    pt.reset_stats()
+    for _ in range(count_steps):
+        pt.Render(cams[step % 16]); step += 1
+    pt.Finish()
+    tally, cst = pt.tally(), pt.stats()
+    pt.set_counting(False)
     # ---- end to end through the public API with host buffers ----
-    # every rank ships its own tiles (1/N of the framebuffer, slot order); one rank alone ships the whole image
-    img = torch.empty((H, W, 4) if world == 1 else (pt.num_slots(), 4), dtype=torch.float32, pin_memory=True).numpy()
+    # N == 1: the whole accumulated image comes back every step.  N > 1 with connected peers: ONE framebuffer -- every rank's
+    # tiles go over NVLink into rank 0's image ring, rank 0 ships the assembled (H, W, 4) image to its host.  N > 1 without
+    # peers (--exchange nccl): every rank ships its own tiles.
+    gathered = world > 1 and peers
+    if world == 1 or gathered:
+        img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy() if rank == 0 else None
+    else:
+        img = torch.empty((pt.num_slots(), 4), dtype=torch.float32, pin_memory=True).numpy()
     inst, tlas = arrays["instances"], arrays["topBvh"]
+    restart()
     pt.reset_stats()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         pt.update_instances(inst, tlas)            # host -> device: instances + TLAS (camera rides in the launch parameters)
         pt.Render(cams[step % 16]); step += 1
-        pt.Finish()
-        if world == 1:
-            pt.read_image(0, out=img)               # device -> host: the accumulated float4 image
+        if gathered:
+            pt.wait_read(pt.gather_image_async(img))
         else:
-            pt.read_tiles(0, out=img)               # device -> host: this rank's tiles of it
+            pt.Finish()
+            if world == 1:
+                pt.read_image(0, out=img)           # device -> host: the accumulated float4 image
+            else:
+                pt.read_tiles(0, out=img)           # device -> host: this rank's tiles of it
+    pt.Finish()
     barrier()
     blocking_s = time.perf_counter() - t0
     bst = pt.stats()
     # streaming variant of the same loop (the headline e2e): the per-step host input of a converge frame is the camera
     # (the reference uploads nothing else unless the frame clears, pathtracer.h:239-246); every step's image comes back
-    # through pt_read_image_async into a ring of 4 pinned buffers while the next samples render, and the host takes
-    # delivery of image k-3 (pt_wait_read) before its buffer is reused.
-    ring = [torch.empty(img.shape, dtype=torch.float32, pin_memory=True).numpy() for _ in range(4)]
+    # asynchronously into a ring of 4 pinned buffers while the next samples render, and the host takes delivery of image
+    # k-3 (pt_wait_read) before its buffer is reused.
+    ring = [torch.empty(img.shape, dtype=torch.float32, pin_memory=True).numpy() if img is not None else None for _ in range(4)]
     tickets = []
+    restart()
     pt.reset_stats()
     barrier()
     t0 = time.perf_counter()
     for k in range(args.steps):
         pt.Render(cams[step % 16]); step += 1
-        tickets.append(pt.read_image_async(ring[k % 4], tiles=(world > 1)))
+        if gathered:
+            tickets.append(pt.gather_image_async(ring[k % 4]))
+        else:
+            tickets.append(pt.read_image_async(ring[k % 4], tiles=(world > 1)))
         if k >= 3:
             pt.wait_read(tickets[k - 3])
     pt.Finish()
     barrier()
     e2e_s = time.perf_counter() - t0
     est = pt.stats()
+    image_ok = None
+    if rank == 0 and (world == 1 or gathered):      # the last image delivered is a full framebuffer: every pixel carries all samples
+        last = ring[(args.steps - 1) % 4]
+        image_ok = bool(np.all(last[..., 3] == float(1 + warm + args.steps)) and np.isfinite(last).all())
     e2 = torch.tensor([est.extend_rays + est.shadow_rays, e2e_s, bst.extend_rays + bst.shadow_rays, blocking_s], dtype=torch.float64, device="cuda")
     if world > 1:
         r2 = e2[[0, 2]].clone(); dist.all_reduce(r2)
@@ -352,6 +399,7 @@ def gpu_arm(args):
         e2 = torch.stack([r2[0], t2[0], r2[1], t2[1]])
     e2e_blocking = float(e2[2].item()) / float(e2[3].item()) / 1e6
     e2e_value = float(e2[0].item()) / float(e2[1].item()) / 1e6
+    d2h = W * H * 16 if (world == 1 or gathered) else pt.num_slots() * 16 * world
     if rank == 0:
         l2_16, l2_32 = pt.measure_gather_bandwidth(32 << 20, 16), pt.measure_gather_bandwidth(32 << 20, 32)     # L2 gather ceiling
         ref_gpu = reference_gpu_leg(total_rays / args.steps)
@@ -363,38 +411,60 @@ def gpu_arm(args):
         ext_ms, ext_n = prof["extend"]
         # only the rays the k_trace<false> launches traced (bounces below the tail bounce); k_tail's are not in ext_ms
         achieved = (pst.wave_extend_rays * bytes_per_ext_ray) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")      # dram__bytes_read+write per launch from the committed ncu --set full capture
+        # the bytes THIS layout requests for the same rays, counted by the kernel: 80 B per wide-node step, 48 B per triangle
+        # test, 32 B per top-level node, + the 48 B/ray stream; all extension rays of the counted frames (every bounce)
+        en, et, etop = tally["extend"]
+        n_cext = max(1, int(cst.extend_rays))
+        wide_bytes_per_ray = 48.0 + (80.0 * en + 48.0 * et + 32.0 * etop) / n_cext
+        wide_achieved = (pst.wave_extend_rays * wide_bytes_per_ray) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+        ncu = {}
+        tp = os.path.join(ROOT, "profiles", "traffic.json")      # per launch, from the committed ncu --set full capture of this command
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get("k_trace<false>", {}).get("dram_bytes_per_launch")
+            ncu = json.load(open(tp)).get("k_trace<false>", {})
         tot_prof_ms = sum(v[0] for v in prof.values())
-        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        ws = sorted(windows)
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warm,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "tiles": "32x32 round-robin over ranks", "exchange": exchange, "samples_in_flight": 4 if pt.num_slots() > 1200000 else 8, "l2": "per-step working set (rays+hits+state+sample cache, ~500 MB) exceeds the 126 MB L2",
-                           "cameras": "16-camera sweep inside the nave, one camera per step", "global_pixels": W * H},
-                "spp_per_s": args.steps / (ms * 1e-3), "rays_per_step": total_rays / args.steps,
-                "phases": {"note": "timed steps follow the reference frame loop from sample %d: the radiance cache trains (update + all-reduce + propagate) while sampleIdx < 100, then stays frozen" % (1 + max(args.warmup, 3)),
-                           "training_ms_per_step": training_ms, "training_mrays_s": rays_per_step / training_ms / 1e3,
-                           "steady_ms_per_step": steady_ms, "steady_mrays_s": rays_per_step / steady_ms / 1e3},
+                "config": CONFIG,
+                "run": {"tiles": "32x32 round-robin over ranks", "exchange": exchange, "samples_in_flight": 4 if pt.num_slots() > 1200000 else 8,
+                        "ray_sorting": bool(args.sort), "phase_of_timed_steps": "samples %d..%d after a clearing frame: the radiance cache trains while sampleIdx < 100 (update + exchange + propagate every frame)" % (1 + warm, warm + args.steps)},
+                "value_windows": {"n": len(ws), "min": ws[0], "median": ws[len(ws) // 2], "max": ws[-1], "what": "the timed region repeated from the same start state"},
+                "spp_per_s": args.steps / (ms * 1e-3), "rays_per_step": rays_per_step,
+                "phases": {"training_ms_per_step": training_ms, "training_mrays_s": rays_per_step / training_ms / 1e3,
+                           "steady_ms_per_step": steady_ms, "steady_mrays_s": rays_per_step / steady_ms / 1e3,
+                           "note": "training: guiding_frames unbounded, every frame updates/exchanges/propagates the cache and cannot overlap its predecessor; steady: cache frozen, samples overlap"},
                 "clocks": sampler.summary(),
-                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": int(img.nbytes) * world,
-                        "mode": "streaming: per step Render(camera) + pt_read_image_async of the whole accumulated image into a ring of 4 pinned host buffers, the host waits for image k-3 each step; all %d images land inside the timed region" % args.steps,
-                        "blocking": {"value": e2e_blocking, "h2d_bytes_per_step": int(inst.nbytes + tlas.nbytes + 76), "d2h_bytes_per_step": int(img.nbytes) * world,
-                                     "mode": "per step update_instances (instances + TLAS H2D), Render, Finish, blocking read_image: nothing overlaps"}},
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": int(d2h),
+                        "phase": "same samples as the timed region (restart + %d warm-up + %d steps)" % (warm, args.steps),
+                        "image_complete": image_ok,
+                        "mode": ("streaming: per step Render(camera) + " + ("pt_gather_image_async: every rank's tiles over NVLink into rank 0's image ring, ONE (H,W,4) float4 image to rank 0's pinned host memory" if gathered else
+                                 "pt_read_image_async of the whole accumulated image" if world == 1 else "pt_read_tiles_async: every rank ships its own tiles (no peer mapping)") +
+                                 ", ring of 4 pinned buffers, the host waits for image k-3 each step; all %d images land inside the timed region" % args.steps),
+                        "blocking": {"value": e2e_blocking, "h2d_bytes_per_step": int(inst.nbytes + tlas.nbytes + 76), "d2h_bytes_per_step": int(d2h),
+                                     "mode": "per step update_instances (instances + TLAS H2D), Render, image delivered to the host before the next step: nothing overlaps"}},
                 "gpu_launches": timed_launches,
                 "roofline": {"bound": "hbm", "kernel": "k_trace<false> (extend)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": pst.wave_extend_rays * bytes_per_ext_ray / max(1, ext_n), "bytes_per_ray": bytes_per_ext_ray,
+                             "traffic": ncu.get("dram_bytes_per_launch"), "peak_source": peak_src,
+                             "what": "reference-layout bytes (SURVEY 8(d)): per ray 48 B stream + 64 B x BVH2 inner visits + 48 B x triangle tests as the CPU oracle counts them on the reference's BVH2; NOT a bandwidth utilisation of this kernel (its 8-wide compressed nodes request ~5x fewer bytes, mostly from L1): the kernel is issue/divergence bound",
+                             "algorithmic_bytes_per_launch": pst.wave_extend_rays * bytes_per_ext_ray / max(1, ext_n), "bytes_per_ray": bytes_per_ext_ray,
                              "avg_launch_ms": ext_ms / max(1, ext_n), "share_of_step": ext_ms / tot_prof_ms if tot_prof_ms else None,
                              "l2_gather_peak_gbs": {"16B": l2_16, "32B": l2_32, "how": "pt_measure_gather_bandwidth: random reads over a 32 MB (L2-resident) array, best of 5"},
                              "frac_of_l2_gather_peak": achieved / l2_32 if l2_32 else None,
-                             "note": "algorithmic bytes are mostly L2-resident BVH gathers (64*N_inner+48*N_tri per ray on the reference BVH2); HBM copy peak is the stated denominator, the L2 gather rate the second ceiling; ncu (profiles/) shows the kernel instruction-issue bound (issue active ~67%, 13-26 of 32 lanes per instruction), not bandwidth bound"},
+                             "stream": {"bytes_per_ray": 48.0, "achieved_gbs": (pst.wave_extend_rays * 48.0) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0,
+                                        "frac_of_hbm_peak": (pst.wave_extend_rays * 48.0) / (ext_ms * 1e-3) / 1e9 / peak if ext_ms > 0 else 0.0},
+                             "wide_layout": {"bytes_per_ray": wide_bytes_per_ray, "node_steps_per_ray": en / n_cext, "triangle_tests_per_ray": et / n_cext, "top_level_steps_per_ray": etop / n_cext,
+                                             "achieved_gbs": wide_achieved, "frac_of_l2_gather_peak": wide_achieved / l2_32 if l2_32 else None, "frac_of_hbm_peak": wide_achieved / peak,
+                                             "what": "bytes the 8-wide layout requests, counted by the traversal kernel itself (pt_set_counting: 80 B per node step, 48 B per triangle test, 32 B per top-level node, + 48 B/ray stream) over %d frames" % count_steps},
+                             "ncu": {k: ncu.get(k) for k in ("lts_bytes_per_launch", "issue_active_pct", "lanes_per_inst", "l1_hit_pct", "dram_pct_of_peak", "source") if k in ncu},
+                             "target_50pct_bandwidth": "not applicable: issue/divergence bound (see DESIGN.md 5)"},
                 "stage_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
+                "exchange_check": exchange_check,
                 "reference_on_this_gpu": ref_gpu,
                 "reference_cpu_traversal": reference_cpu_traversal_leg(os.cpu_count() or 1),
                 "cpu_baseline": {"value": cpu_v, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
                                  "sample": "oracle/pt_oracle.cpp: %d converge samples of the same scene/camera/depth at %dx%d (%.0f rays, %.1f s)" % (CPU_SAMPLES, CPU_W, CPU_H, cpu_rays, cpu_s)}}
         print(json.dumps(line), flush=True)
-    if world > 1 and exchange.startswith("fused"):
+    if world > 1 and peers:
         from cuda_pathtracer_b200.distributed import disconnect_peers
         disconnect_peers(pt)
     pt.close()
@@ -408,6 +478,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sort", action="store_true", help="ray sorting between shade and trace (pt_set_ray_sorting); results identical")
     ap.add_argument("--exchange", default=os.environ.get("PTB200_EXCHANGE", "peer"), choices=["peer", "nccl"],
                     help="N>1: radiance-cache exchange of the training frames (peer = fused kernel over NVLink peer memory)")
     args = ap.parse_args()
