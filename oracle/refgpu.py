@@ -44,8 +44,8 @@ class SceneSpec:
         self.materials.append(dict(diffuse=diffuse, emission=emission, reflect=reflect, glossy=glossy, transmit=transmit, ior=ior, absorption=absorption))
         return len(self.materials) - 1
 
-    def model(self, obj_path, material, scale=1.0):
-        self.models.append((obj_path, scale, material)); return len(self.models) - 1
+    def model(self, obj_path, material, scale=1.0, use_mtl=False):
+        self.models.append((obj_path, scale, material, use_mtl)); return len(self.models) - 1
 
     def object(self, model, material=-1, position=(0, 0, 0), rotation=(0, 0, 0), scale=(1, 1, 1)):
         self.objects.append((model, material, position, rotation, scale))
@@ -54,8 +54,8 @@ class SceneSpec:
         L = []
         for m in self.materials:
             L.append("material " + " ".join(repr(float(x)) for x in (*m["diffuse"], *m["emission"], m["reflect"], m["glossy"], m["transmit"], m["ior"], *m["absorption"])))
-        for p, s, mat in self.models:
-            L.append("model %s %r 0 0 0 0 0 0 %d 0" % (p, float(s), mat))
+        for p, s, mat, use_mtl in self.models:
+            L.append("model %s %r 0 0 0 0 0 0 %d %d" % (p, float(s), mat, int(use_mtl)))
         for mo, mat, pos, rot, sc in self.objects:
             L.append("object %d %d " % (mo, mat) + " ".join(repr(float(x)) for x in (*pos, *rot, *sc)))
         for pos, r, mat in self.spheres:
@@ -77,7 +77,7 @@ class SceneSpec:
         for m in self.materials:
             s.addMaterial(material(m["diffuse"], emission=m["emission"], reflect=m["reflect"], glossy=m["glossy"], transmit=m["transmit"],
                                    refractive_index=m["ior"], absorption=m["absorption"]))
-        ids = [s.addModel(p, sc, (0, 0, 0), (0, 0, 0), mat, False) for p, sc, mat in self.models]
+        ids = [s.addModel(p, sc, (0, 0, 0), (0, 0, 0), mat, use_mtl) for p, sc, mat, use_mtl in self.models]
         for mo, mat, pos, rot, sc in self.objects:
             s.addObject(ids[mo], material=0xFFFFFFFF if mat < 0 else mat, position=pos, rotation=rot, scale=sc)
         for pos, r, mat in self.spheres:
@@ -146,4 +146,52 @@ def sibenik_spec(workdir):
     sp.object(cube, material=cube_w, position=(0, 3, 0))
     sp.spheres.append(((-2, -1, -3), 2, white_glass))
     sp.spheres.append(((-2, -1, 3), 2, mirror))
+    return sp
+
+
+def outside_spec(workdir):
+    """BASELINE.json configs[1] (getOutsideScene, sceneBuilder.h:15-117; cuda_pathtracer_b200.scenes.outside_scene): 10 glass cubes
+    on a circle (handler positions at t = 0, sceneBuilder.h:89-100) over the checker plane, as a SceneSpec."""
+    from cuda_pathtracer_b200 import scenes
+    sp = SceneSpec()
+    sp.interactive_depth = 5
+    white = sp.material((0.4, 0.4, 0.4))
+    cube_mat = sp.material((1, 1, 1), transmit=1.0, ior=1.1, glossy=0.02, absorption=(0.1, 0.5, 0.8))
+    path = os.path.join(workdir, "cube.obj")
+    write_obj(path, scenes.cube_soup())
+    cube = sp.model(path, cube_mat)
+    f = np.float32(0)
+    for _ in range(10):
+        sp.object(cube, position=(float(np.float32(10) * np.sin(f, dtype=np.float32)), 0.0, float(np.float32(10) * np.cos(f, dtype=np.float32))), rotation=(float(f), 0.0, 0.0))
+        f = np.float32(f + np.float32(2 * 0.3141592))
+    sp.planes.append(((0, -1, 0), -3.0, white))
+    return sp
+
+
+def write_obj_uv(path, tri, uv, mtllib, usemtl):
+    """(n, 9) triangles + (n, 6) uvs -> OBJ with v / vt / f v/vt lines, one material."""
+    with open(path, "w") as f:
+        f.write("mtllib %s\n" % mtllib)
+        f.write("".join("v %r %r %r\n" % (float(a), float(b), float(c)) for a, b, c in tri.reshape(-1, 3)))
+        f.write("".join("vt %r %r\n" % (float(a), float(b)) for a, b in uv.reshape(-1, 2)))
+        f.write("usemtl %s\n" % usemtl)
+        f.write("".join("f %d/%d %d/%d %d/%d\n" % (3 * i + 1, 3 * i + 1, 3 * i + 2, 3 * i + 2, 3 * i + 3, 3 * i + 3) for i in range(len(tri))))
+
+
+def minecraft_spec(workdir, n=256):
+    """BASELINE.json configs[4] (getMinecraftScene, sceneBuilder.h:220-239) with the voxel-terrain proxy: an OBJ with uvs, an MTL
+    whose map_Kd names the atlas PNG written next to it (both renderers decode the same file), the bokeh camera of
+    scenes.minecraft_camera."""
+    from PIL import Image
+    from cuda_pathtracer_b200 import scenes
+    tri, uv = scenes.voxel_terrain_soup(n, 3)
+    atlas = np.clip(np.round(scenes.voxel_atlas(256)[..., :3] * 255.0), 0, 255).astype(np.uint8)
+    Image.fromarray(atlas, "RGB").save(os.path.join(workdir, "atlas.png"))
+    open(os.path.join(workdir, "terrain.mtl"), "w").write("newmtl terrain\nKd 1 1 1\nKs 0 0 0\nd 1\nNs 0\nNi 1\nmap_Kd atlas.png\n")
+    path = os.path.join(workdir, "terrain.obj")
+    write_obj_uv(path, tri, uv, "terrain.mtl", "terrain")
+    sp = SceneSpec()
+    white = sp.material((0.4, 0.4, 0.4))
+    m = sp.model(path, white, use_mtl=True)
+    sp.object(m)
     return sp

@@ -1,0 +1,229 @@
+"""-m gpu: scheduling features must be invisible in the results, and the opt-in samplers must match the oracle.
+  * ray sorting between shade and trace (reference experiment src/raySorting.h:1-68): bit-identical images
+  * programmatic dependent launch on / off: bit-identical images
+  * counting traversal kernels (roofline line of bench.py): same image, plausible tallies
+  * skydome importance sampling through the CDF of src/pathtracer.h:85-122 + binarySearch src/kernels.h:65-79: against the
+    CPU oracle on the same seeds, and unbiased against the unsampled estimator
+  * sample-cache handling of overlapped samples: a re-clear after overlapped samples trains the cache reproducibly
+  * host-side validation of instance / top-level records (a bad index must be an error code, not a device fault)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from cuda_pathtracer_b200 import abi, api, scenes
+from oracle.oracle_py import OracleLib
+from util import load_golden_scene
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_rmse(a, b):
+    return float(np.sqrt(np.mean((a.astype(np.float64) - b) ** 2)) / max(1e-12, np.sqrt(np.mean(b.astype(np.float64) ** 2))))
+
+
+def render(arrays, cam, w, h, frames, flags=0, nee=True, guiding=False, setup=None, depth=8):
+    cfg = abi.default_config(w, h, max_ray_depth=depth, interactive_depth=1, flags=flags)
+    pt = api.Pathtracer(arrays, cfg).Init()
+    if setup:
+        setup(pt)
+    pt.HNEE, pt.HCACHE = nee, guiding
+    pt.Render(cam, shouldClear=True)
+    for _ in range(frames):
+        pt.Render(cam)
+    pt.Finish()
+    out = pt.read_image().copy(), pt.read_image(1).copy(), pt.stats()
+    extra = pt
+    return out, extra
+
+
+@pytest.fixture(scope="module")
+def sibenik():
+    return scenes.sibenik_scene().arrays(), scenes.camera_sweep("sibenik", 320, 180, 16)[3]
+
+
+def test_ray_sorting_is_invisible(sibenik):
+    """Guiding off: ray order is result-independent (SURVEY 7 "Determinism"), so sorted and unsorted runs must agree in
+    every bit of both images and in every ray count; 9 samples = clearing frame + pipelined + wavefront + tail paths."""
+    arrays, cam = sibenik
+    (img0, alb0, st0), p0 = render(arrays, cam, 320, 180, 8)
+    p0.close()
+    for bits, bounces in ((4, 2), (5, 1), (2, 2)):
+        (img1, alb1, st1), p1 = render(arrays, cam, 320, 180, 8, setup=lambda pt: pt.set_ray_sorting(True, bits, bounces))
+        p1.close()
+        assert np.array_equal(img0, img1) and np.array_equal(alb0, alb1), "sorting changed the image (bits %d, bounces %d)" % (bits, bounces)
+        assert (st0.extend_rays, st0.shadow_rays, st0.primary_rays) == (st1.extend_rays, st1.shadow_rays, st1.primary_rays)
+    (img2, _, _), p2 = render(arrays, cam, 320, 180, 8, flags=abi.FLAG_SORT_RAYS | abi.FLAG_NO_PIPELINE)
+    p2.close()
+    assert np.array_equal(img0, img2)
+
+
+def test_ray_sorting_with_guiding_trains_the_same_way(sibenik):
+    arrays, cam = sibenik
+    (a, _, _), p = render(arrays, cam, 320, 180, 12, guiding=True); p.close()
+    (b, _, _), p = render(arrays, cam, 320, 180, 12, guiding=True, setup=lambda pt: pt.set_ray_sorting(True)); p.close()
+    assert np.array_equal(a[..., 3], b[..., 3]) and rel_rmse(b[..., :3], a[..., :3]) <= 2e-2      # float atomics: the guided bound of test_gpu_render
+
+
+def test_pdl_is_invisible(sibenik):
+    arrays, cam = sibenik
+    (a, aa, sa), p = render(arrays, cam, 320, 180, 6); p.close()
+    (b, ba, sb), p = render(arrays, cam, 320, 180, 6, flags=abi.FLAG_NO_PDL); p.close()
+    assert np.array_equal(a, b) and np.array_equal(aa, ba) and sa.extend_rays == sb.extend_rays and sa.kernel_launches == sb.kernel_launches
+
+
+def test_counting_mode_same_image_and_plausible_tally(sibenik):
+    arrays, cam = sibenik
+    (a, _, sa), p = render(arrays, cam, 320, 180, 4); p.close()
+    cfg = abi.default_config(320, 180, max_ray_depth=8, interactive_depth=1)
+    pt = api.Pathtracer(arrays, cfg).Init()
+    pt.Render(cam, shouldClear=True)
+    pt.set_counting(True)
+    for _ in range(4):
+        pt.Render(cam)
+    pt.Finish()
+    t, st = pt.tally(), pt.stats()
+    ext, sh = pt.debug_read_counters(8)
+    b = pt.read_image().copy()
+    pt.close()
+    assert np.array_equal(a, b)
+    assert st.extend_rays == sa.extend_rays and st.shadow_rays == sa.shadow_rays
+    conv_ext = st.extend_rays - 320 * 180            # the clearing frame ran before counting was switched on
+    # every extension ray inside the cathedral enters the top level and takes several wide-node steps
+    assert t["extend"][2] >= conv_ext * 0.9 and 3 * conv_ext < t["extend"][0] < 200 * conv_ext and t["extend"][1] > conv_ext
+    assert t["connect"][0] > 0 and t["connect"][1] > 0
+    assert ext[0] == 320 * 180 and ext[1] < ext[0] and np.all(np.diff(ext.astype(np.int64)) <= 0) and sh[0] > 0
+
+
+def bright_spot_sky(w=64, h=32):
+    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
+    sky = np.ones((h, w, 4), np.float32)
+    sky[..., :3] = 0.15
+    spot = np.exp(-((x - 40.0) ** 2 + (y - 9.0) ** 2) / 6.0)[..., None]       # texture rows: see skyUvToDir (v = 1 - polar angle / pi)
+    sky[..., :3] += 40.0 * spot * np.array([1.0, 0.9, 0.7], np.float32)
+    return sky
+
+
+def test_sky_sampling_matches_oracle():
+    """Same seeds, same statements (csrc/pt_shade.cuh vs oracle/pt_oracle.cpp): differences come from libm ulps and the texture
+    unit's 8-bit filter weights only, as for the unsampled path (bound of test_outside_glass_plane_textured_sky)."""
+    a = load_golden_scene("outside")
+    cfg = abi.default_config(160, 120, max_ray_depth=6, interactive_depth=1)
+    sky = bright_spot_sky()
+    pt = api.Pathtracer(a, cfg).Init()
+    ora = OracleLib(cfg)
+    desc, keep = abi.make_scene_desc(a)
+    ora.upload_scene(desc, keep)
+    pt.set_skydome(sky); ora.set_skydome(sky)
+    pt.set_sky_sampling(True); ora.set_sky_sampling(True)
+    cam = a["camera_160x120"]
+    pt.HNEE, pt.HCACHE = True, False
+    ora.set_toggles(True, False)
+    pt.Render(cam, shouldClear=True); ora.render(cam, True)
+    for _ in range(5):
+        pt.Render(cam); ora.render(cam, False)
+    pt.Finish()
+    g, r = pt.read_image(), ora.read_image()
+    st, (ost, _) = pt.stats(), ora.stats()
+    assert np.all(g[..., 3] == 6.0) and np.isfinite(g).all()
+    assert st.shadow_rays > 0 and abs(int(st.shadow_rays) - int(ost.shadow_rays)) <= 2e-3 * ost.shadow_rays
+    err = rel_rmse(g[..., :3], r[..., :3])
+    print("sky sampling vs oracle: rel RMSE %.3g, shadow rays %d" % (err, st.shadow_rays))
+    assert err <= 5e-3
+    pt.close(); ora.close()
+
+
+def test_sky_sampling_is_unbiased_and_less_noisy():
+    """The sampled and the unsampled estimator converge to the same picture; with a small bright spot in the dome the sampled one
+    gets there with far less variance (what README.md:150 says path guiding was brought in for)."""
+    # a floor under the object so that most diffuse vertices see the dome
+    from cuda_pathtracer_b200.scene import Scene, material, make_camera
+    sc = Scene()
+    m = sc.addMaterial(material((0.7, 0.7, 0.7)))
+    sc.addObject(sc.addModelSoup(scenes.statue_soup(4, 24), material=m))
+    sc.addPlane((0, -1, 0), -3, m)
+    a = sc.finalize().arrays()
+    cam = make_camera((0.0, 4.0, -9.0), (0.0, -0.35, 0.94), 1.5, 5.0, 0.0, 96, 54)
+    sky = bright_spot_sky()
+
+    def run(sample, frames):
+        cfg = abi.default_config(96, 54, max_ray_depth=4, interactive_depth=1)
+        pt = api.Pathtracer(a, cfg).Init()
+        pt.set_skydome(sky)
+        pt.set_sky_sampling(sample)
+        pt.HNEE, pt.HCACHE = True, False
+        pt.Render(cam, shouldClear=True)
+        for _ in range(frames):
+            pt.Render(cam)
+        pt.Finish()
+        img = pt.read_image().copy()
+        pt.close()
+        return img[..., :3] / img[..., 3:4]
+    ref = run(False, 4095)
+    smp = run(True, 255)
+    few = run(False, 255)
+    mean_ref, mean_smp = float(ref.mean()), float(smp.mean())
+    print("mean radiance: unsampled(4096 spp) %.4f, sampled(256 spp) %.4f; rel RMSE to the 4096-spp picture: sampled %.3f, unsampled(256) %.3f"
+          % (mean_ref, mean_smp, rel_rmse(smp, ref), rel_rmse(few, ref)))
+    assert abs(mean_smp / mean_ref - 1.0) < 0.03
+    assert rel_rmse(smp, ref) < rel_rmse(few, ref)
+
+
+def test_reclear_after_overlapped_samples_trains_reproducibly(sibenik):
+    """Overlapped (non-training) samples share nothing with the radiance-cache training: after 12 of them and a clearing frame
+    the training frames read stale sample-cache entries of the clearing / training frames only, so two identical runs train the
+    same cache (up to the last bits of the unordered float atomics), not one that depends on which sample in flight wrote last."""
+    arrays, cam = sibenik
+
+    def run():
+        cfg = abi.default_config(320, 180, max_ray_depth=8, interactive_depth=1, guiding_frames=4)
+        pt = api.Pathtracer(arrays, cfg).Init()
+        pt.HNEE, pt.HCACHE = True, True
+        pt.Render(cam, shouldClear=True)
+        for _ in range(16):                    # 4 training frames, then 12 overlapped samples
+            pt.Render(cam)
+        pt.Render(cam, shouldClear=True)
+        pt.Render(cam)                         # ONE training frame: reads stale entries where paths ended on the emitter
+        pt.Finish()
+        rc = pt.read_radiance_cache()["radianceCache"].copy()
+        pt.close()
+        return rc
+    a, b = run(), run()
+    moved = np.abs(a - 0.1) > 1e-6
+    assert moved.any()
+    # float atomics reorder sums (last-bit differences, amplified through 5 training frames); a different SET of contributing
+    # entries would move whole buckets by percents
+    assert np.mean(np.abs(a - b) > 1e-3 * np.abs(a)) < 0.002
+
+
+def test_bad_top_level_records_are_rejected(sibenik):
+    arrays, cam = sibenik
+    cfg = abi.default_config(64, 64, max_ray_depth=2, interactive_depth=1)
+    pt = api.Pathtracer(arrays, cfg).Init()
+    inst, tlas = arrays["instances"].copy(), arrays["topBvh"].copy()
+    bad = inst.copy(); bad[0]["model_id"] = 99
+    with pytest.raises(api.PtError, match="model_id"):
+        pt.update_instances(bad, tlas)
+    bad_t = tlas.copy()
+    inner = np.nonzero(bad_t["children"] != 0)[0][0]
+    bad_t[inner]["children"] = (0xFFFF << 16) | 1
+    with pytest.raises(api.PtError, match="child index"):
+        pt.update_instances(inst, bad_t)
+    bad_t = tlas.copy()
+    leaf = np.nonzero(bad_t["children"] == 0)[0][0]
+    bad_t[leaf]["leaf"] = 1000
+    with pytest.raises(api.PtError, match="leaf"):
+        pt.update_instances(inst, bad_t)
+    pt.update_instances(inst, tlas)                     # the context is still usable
+    pt.Render(cam, shouldClear=True); pt.Finish()
+    # a scene whose model range exceeds the triangle array
+    broken = dict(arrays); models = arrays["models"].copy(); models[0]["nrTriangles"] += 10; broken["models"] = models
+    with pytest.raises(api.PtError):
+        api.Pathtracer(broken, cfg).Init()
+    # replacing the scene under connected peers is refused
+    pt.peer_connect([pt.peer_export()])
+    desc, keep = abi.make_scene_desc(arrays)
+    assert pt.L.pt_upload_scene(pt.h, C.byref(desc)) == -1 and b"peer" in pt.L.pt_last_error(pt.h)
+    pt.peer_disconnect()
+    assert pt.L.pt_upload_scene(pt.h, C.byref(desc)) >= 0
+    pt.close()
