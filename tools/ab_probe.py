@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""A/B of scheduling knobs on ONE GPU: training ms/frame and steady ms/sample of the bench workload (sibenik 1080p, depth 8)
+for the whole image (world 1) and for rank 0's share of an emulated 8-rank job, one line per variant.
+usage: tools/ab_probe.py [name=ENV1=v,ENV2=v ...]   (default: a fixed list)"""
+import os, sys, json
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+from cuda_pathtracer_b200 import abi, api, scenes
+
+VARIANTS = [("base", {}), ("no_pdl", {"PTB200_NO_PDL": "1"}), ("sort4x2", {"PTB200_SORT": "4,2"}), ("sort4x1", {"PTB200_SORT": "4,1"}),
+            ("sort5x2", {"PTB200_SORT": "5,2"}), ("sort3x2", {"PTB200_SORT": "3,2"})]
+if len(sys.argv) > 1:
+    VARIANTS = []
+    for a in sys.argv[1:]:
+        name, _, rest = a.partition("=")
+        VARIANTS.append((name, dict(kv.split("=", 1) for kv in rest.split(",") if kv) if rest else {}))
+arrays = scenes.sibenik_scene().arrays()
+cams = scenes.camera_sweep("sibenik", 1920, 1080, 16)
+KNOBS = ["PTB200_NO_PDL", "PTB200_SORT", "PTB200_TAIL_BOUNCE", "PTB200_MIN_WIDTH", "PTB200_SETS", "PTB200_NO_TAIL_PAIR", "PTB200_COOP", "PTB200_TAIL_GRID"]
+
+
+def measure(world, env):
+    for k in KNOBS:
+        os.environ.pop(k, None)
+    os.environ.update(env)
+    cfg = abi.default_config(1920, 1080, max_ray_depth=8, interactive_depth=1, rank=0, world_size=world)
+    pt = api.Pathtracer(arrays, cfg).Init()
+    stream = torch.cuda.ExternalStream(pt.stream())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    pt.set_guiding_frames(1 << 30)
+    pt.Render(cams[0], shouldClear=True)
+    for i in range(5): pt.Render(cams[i % 16])
+    best_t = 1e9
+    for rep in range(3):
+        pt.join(); e0.record(stream)
+        for i in range(40): pt.Render(cams[i % 16])
+        pt.join(); e1.record(stream); pt.Finish()
+        best_t = min(best_t, e0.elapsed_time(e1) / 40)
+    pt.set_guiding_frames(0)
+    for i in range(16): pt.Render(cams[i % 16])
+    pt.Finish(); pt.reset_stats()
+    best_s = 1e9
+    for rep in range(3):
+        pt.join(); e0.record(stream)
+        for i in range(64): pt.Render(cams[i % 16])
+        pt.join(); e1.record(stream); pt.Finish()
+        best_s = min(best_s, e0.elapsed_time(e1) / 64)
+    st = pt.stats()
+    rays = (st.extend_rays + st.shadow_rays) / (3 * 64)
+    pt.close()
+    return best_t, best_s, rays
+
+
+for world in (1, 8):
+    for name, env in VARIANTS:
+        t, s, rays = measure(world, env)
+        print(json.dumps({"world": world, "variant": name, "training_ms": round(t, 4), "steady_ms": round(s, 4), "rays_per_sample": int(rays),
+                          "training_mrays_s": round(rays / t / 1e3, 1), "steady_mrays_s": round(rays / s / 1e3, 1)}), flush=True)
