@@ -82,7 +82,10 @@ struct pt_ctx {
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
+    bool knobPdlAlways = false;
+    uint32_t coop = 0;                    // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays per warp, latency mode only (PTB200_COOP)
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
+    bool pdlNow = true;                   // ... for the sample being enqueued: samples that overlap others launch plainly (see pt_render)
     bool sortOn = false; uint32_t sortBits = 4, sortBounces = PT_SORT_MAX_BOUNCES;          // pt_set_ray_sorting
     bool counting = false; unsigned long long* tally = nullptr;                            // pt_set_counting: [0..2] extend, [3..5] connect
     float *skyPdf = nullptr, *skyCdf = nullptr;                                           // pt_set_skydome builds them (pathtracer.h:85-122)
@@ -141,7 +144,7 @@ static inline void launchK(pt_ctx* ctx, void (*kernel)(KA...), dim3 grid, dim3 b
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
-    c.attrs = at; c.numAttrs = ctx->pdl ? 1u : 0u;
+    c.attrs = at; c.numAttrs = ctx->pdlNow ? 1u : 0u;
     cudaLaunchKernelEx(&c, kernel, std::forward<A>(args)...);
 }
 
@@ -347,6 +350,8 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
         ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
+        ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
+        if (const char* e = getenv("PTB200_COOP")) ctx->coop = (uint32_t)std::max(0, atoi(e));                                     // developer knob
         if (cfg->flags & PT_FLAG_SORT_RAYS) ctx->sortOn = true;
         if (const char* e = getenv("PTB200_SORT")) {                                       // developer knob: "bits[,bounces]", 0 = off
             ctx->sortOn = atoi(e) > 0;
@@ -807,6 +812,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         ctx->forked = true;
     }
     if (ctx->sortOn) { int sr = ensureSortBuffers(ctx); if (sr) return sr; }
+    ctx->pdlNow = ctx->pdl;
     if (should_clear) {
         ctx->DNEE = ctx->HNEE; ctx->DCACHE = ctx->HCACHE;                                  // :242-243
         launchK(ctx, k_clear_image, dim3((npix + 255) / 256), dim3(256), ctx->stream, ctx->image, ctx->albedo, npix);    // :248-249
@@ -830,11 +836,16 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
         if (ctx->knobMinWidth) ctx->sc.minWidth = ctx->knobMinWidth;
         ctx->sc.tailPair = (ctx->sc.minWidth < 32u && !ctx->knobNoTailPair) ? 1u : 0u;     // latency mode only: a sample that runs alone
+        ctx->sc.coop = ctx->sc.minWidth < 32u ? ctx->coop : 0u;                            // likewise: overlapped samples fill short launches with each other's rays
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
         if (pipelined && (training || ctx->prevTraining) && other.tailValid && !ctx->knobNoTailWait) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
         const bool overlapped = pipelined && !training && !ctx->prevTraining;
+        // Programmatic dependent launch pays where a sample runs alone (its launch chain is the critical path: measured 1-2 % per
+        // training frame).  Among overlapped samples an early-scheduled successor holds SM slots the other samples' kernels
+        // could use (measured: steady state 4 % slower at 1080p, 18 % on a 1/8 shard), so those launch in plain stream order.
+        ctx->pdlNow = ctx->pdl && (!overlapped || ctx->knobPdlAlways);
         const bool sorting = ctx->sortOn && !ctx->counting;
         CK(cudaMemsetAsync(S.q.cnt, 0, (CNT_TOTAL + (sorting ? (size_t)ctx->sortBounces * 2 * nbins : 0)) * sizeof(uint), s));   // :265 (+ cursors, + sort histograms)
         if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); launchK(ctx, k_primary, dim3(map.nSlots / 256), dim3(256), s, dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
@@ -1321,6 +1332,7 @@ static int debugTrace(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_
         ctx->dbgCap = n;
     }
     cudaStream_t s = ctx->stream;
+    ctx->sc.minWidth = 1u; ctx->sc.coop = ctx->coop;          // the stage hook runs alone: latency-mode scheduling, cooperative form where the queue is short
     CK(cudaMemcpyAsync(ctx->dbgRays, host_rays, (size_t)n * sizeof(pt_ray), cudaMemcpyHostToDevice, s));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));

@@ -118,6 +118,10 @@ __global__ void k_primary_debug(DCamera cam, uint W, uint H, uint randIdx, pt_ra
 #ifndef PT_TRACE_MINBLOCKS
 #define PT_TRACE_MINBLOCKS 8
 #endif
+// Short queue in latency mode: 8 lanes per ray (traceLoopCoop) instead of one.  Block-uniform.
+__device__ __forceinline__ bool useCoop(const DScene& sc, uint n) {
+    return sc.coop != 0u && n <= ((gridDim.x * blockDim.x) >> 5) * 4u * sc.coop;
+}
 template <bool ANY>
 __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
@@ -125,7 +129,9 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace(DScene sc, co
     pdlWait(); pdlLaunch();
     QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = perm;
     NoTally tally;
-    traceLoop<ANY>(sc, *count, cursor, io, tally);
+    const uint n = *count;
+    if (useCoop(sc, n)) traceLoopCoop<ANY>(sc, n, cursor, io, tally);
+    else traceLoop<ANY>(sc, n, cursor, io, tally);
 }
 // counting variant (pt_set_counting): the same traversal, plus the node steps / triangle tests / top-level steps it
 // performs, summed into tallyOut[0..2] -- the bytes the wide layout actually requests (80 B per node step, 48 B per
@@ -154,9 +160,16 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair(DScene s
     pdlWait(); pdlLaunch();
     NoTally tally;
     QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm;
-    traceLoop<false>(sc, *extCount, extCursor, e, tally);
+    const uint ne = *extCount, ns = *shCount;
+    if (useCoop(sc, ne + ns)) {
+        traceLoopCoop<false>(sc, ne, extCursor, e, tally);
+        QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
+        traceLoopCoop<true>(sc, ns, shCursor, c, tally);
+        return;
+    }
+    traceLoop<false>(sc, ne, extCursor, e, tally);
     QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
-    traceLoop<true>(sc, *shCount, shCursor, c, tally);
+    traceLoop<true>(sc, ns, shCursor, c, tally);
 }
 
 // stage-parity hook: reference-format rays in, reference-format hits out (pt_debug_trace)
@@ -164,7 +177,8 @@ template <bool ANY>
 __global__ void __launch_bounds__(128) k_trace_debug(DScene sc, const pt_ray* __restrict__ rays, uint n, uint* cursor, pt_hit* __restrict__ out) {
     DebugIO io; io.rays = rays; io.out = out;
     NoTally tally;
-    traceLoop<ANY>(sc, n, cursor, io, tally);
+    if (useCoop(sc, n)) traceLoopCoop<ANY>(sc, n, cursor, io, tally);
+    else traceLoop<ANY>(sc, n, cursor, io, tally);
 }
 
 __global__ void k_prepare_lights(DScene sc) {
@@ -273,12 +287,133 @@ __device__ __forceinline__ float4 shfl4(const float4 v, const uint src) {
 // connect(b), so the float additions into accucolor keep the wavefront's (the reference's) order: identical bits.  A lone
 // sample on a small shard is latency bound and has the lanes to spare: the per-bounce latency becomes
 // max(extend, connect) + shade instead of their sum.
+// k_tail with the cooperative traversal (pt_trace.cuh traceLoopCoop): a PATH owns a group of 8 lanes -- in pair mode 16: the
+// even group extends and shades, the odd group traces the shadow rays -- so a warp carries 4 (2) paths.  Used when the
+// surviving paths fit the machine that way (multi-GPU shards, deep bounces); every lane of a group runs the same statements on
+// the same values (shading included: it costs no extra issue slots), lane 0 of the group does the atomics and stores.
+__device__ __forceinline__ void tailCoop(const ShadeParams& P, const Queues& q, const int inBuf, const int b0, const int maxBounces, uint* cursor, const uint n) {
+    const DScene& sc = P.sc;
+    const uint lane = laneId(), group = lane >> 3, sub = lane & 7u, gmask = 0xFFu << (group * 8u);
+    const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * 2u * max(1u, sc.coop);
+    const bool isHelper = pair && (group & 1u) != 0u;
+    const uint ownerBits = pair ? 0x00010001u : 0x01010101u;                     // lane-0 bits of the groups that own paths
+    const uint width = min(pair ? 2u : 4u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    const bool writer = sub == 0u;
+    TravStack stack; stack.init();
+    NoTally tally;
+    LaneState L;
+    L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
+    int bounce = b0, buf = inBuf;
+    bool any = false, extPending = false, rayDone = false;
+    bool exhausted = n == 0;
+    const uint randIdx0 = P.randIdx;
+    auto loadCur = [&](float4& o4, float4& d4) {
+        if (any) { o4 = q.shO[L.ray]; d4 = q.shD[L.ray]; } else { o4 = q.rayO[buf][L.ray]; d4 = q.rayD[buf][L.ray]; }
+    };
+    auto addLight = [&]() {                                                     // unoccluded: kernels.h:806-809; one lane adds, the group sees it
+        if (writer) {
+            const uint slot = __float_as_uint(q.shD[L.ray].w);
+            const float4 l = P.lights[slot];
+            float4 a = P.accucolors[slot];
+            a.x += l.x; a.y += l.y; a.z += l.z;
+            P.accucolors[slot] = a;
+        }
+        __syncwarp(gmask);
+    };
+    while (true) {
+        // ---- F: idle owner groups claim new paths ----
+        const uint activeAll = __ballot_sync(0xffffffffu, L.ray != PT_NONE) & 0x01010101u;
+        const uint activeMask = activeAll & ownerBits;
+        const uint nActive = __popc(activeMask);
+        if (!exhausted && nActive < width) {
+            const uint want = width - nActive;
+            uint base = 0;
+            if (lane == 0) base = atomicAdd(cursor, want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + want >= n) exhausted = true;
+            const uint r = __popc(~activeAll & ownerBits & ((1u << (group * 8u)) - 1u));
+            if (!isHelper && L.ray == PT_NONE && r < want && base + r < n) {
+                L.ray = base + r; bounce = b0; buf = inBuf; any = false; extPending = false;
+                float4 o4, d4; loadCur(o4, d4);
+                rayDone = !beginRay(sc, L, o4, d4, false);
+            }
+        } else if (activeAll == 0u) break;
+        // ---- C: a finished ray continues its path: shade, then the shadow ray, then the next extension ray ----
+        bool helperBusy = false;
+        if (pair) {
+            if (isHelper && L.ray != PT_NONE && rayDone) {                      // the helper group's shadow ray is done
+                if (L.hitId == PT_NONE) addLight();
+                L.ray = PT_NONE; rayDone = false;
+            }
+            __syncwarp();                                                       // its accucolor update before the owner's next shade
+            helperBusy = __shfl_xor_sync(0xffffffffu, (int)(L.ray != PT_NONE), 8) != 0;
+        }
+        bool handoff = false;
+        uint hpath = PT_NONE;
+        float4 hso = make_float4(0.f, 0.f, 0.f, 0.f), hsd = hso;
+        while (!isHelper && L.ray != PT_NONE && rayDone && !helperBusy && !handoff) {
+            rayDone = false;
+            bool startExt = false;
+            if (any) {
+                if (L.hitId == PT_NONE) addLight();
+                any = false;
+                startExt = extPending;
+            } else {
+                float4 o4, d4; loadCur(o4, d4);
+                const uint slot = __float_as_uint(d4.w);
+                Hit h; h.type = L.hitType; h.id = L.hitId; h.inst = L.hitInst; h.t = L.tbest;
+                ShadeParams Pb = P; Pb.bounce = bounce; Pb.randIdx = randIdx0 + (uint)(bounce - b0);
+                ShadeOut so;
+                shadeOne(Pb, f3(o4), f3(d4), slot, h, so, gmask, writer);
+                __syncwarp(gmask);                                              // the writer's state stores before anybody of the group reads them again
+                extPending = so.pushExt && bounce + 1 < maxBounces;
+                if (so.pushExt && writer) atomicAdd(q.cnt + CNT_EXT(bounce + 1), 1u);
+                if (extPending) {                                               // every lane stores the same values and later reads back its own store
+                    q.rayO[buf ^ 1][L.ray] = make_float4(so.ext.o.x, so.ext.o.y, so.ext.o.z, so.ext.len);
+                    q.rayD[buf ^ 1][L.ray] = make_float4(so.ext.d.x, so.ext.d.y, so.ext.d.z, __uint_as_float(slot));
+                }
+                if (so.pushShadow) {
+                    if (writer) atomicAdd(q.cnt + CNT_SHADOW(bounce), 1u);
+                    const float4 so4 = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
+                    const float4 sd4 = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
+                    q.shO[L.ray] = so4; q.shD[L.ray] = sd4;
+                    if (pair) { handoff = true; hpath = L.ray; hso = so4; hsd = sd4; startExt = extPending; }
+                    else { any = true; rayDone = !beginRay(sc, L, so4, sd4, true); }
+                } else startExt = extPending;
+            }
+            if (startExt) {
+                extPending = false; bounce++; buf ^= 1;
+                float4 o4, d4; loadCur(o4, d4);
+                rayDone = !beginRay(sc, L, o4, d4, false);
+            } else if (!any) L.ray = PT_NONE;                                    // path ended
+        }
+        if (pair) {                                                             // hand the new shadow rays to the helper groups
+            const uint src = lane & ~8u;
+            const bool take = __shfl_sync(0xffffffffu, (int)handoff, src) != 0;
+            const uint path = __shfl_sync(0xffffffffu, hpath, src);
+            const float4 o4 = shfl4(hso, src), d4 = shfl4(hsd, src);
+            __syncwarp();                                                       // q.shO/shD[path] (re-read when an instance is left) written by the owner
+            if (isHelper && take) { L.ray = path; any = true; rayDone = !beginRay(sc, L, o4, d4, true); }
+        }
+        // ---- T: top level ----
+        if (L.ray != PT_NONE && !rayDone && !hasBlasWork(L)) rayDone = tlasTrip(sc, L, stack, loadCur, tally);
+        // ---- B: bottom level, cooperative ----
+        while (true) {
+            const bool work = hasBlasWork(L);
+            if (__ballot_sync(0xffffffffu, work) == 0u) break;
+            if (work && coopBlasTrip(sc, L, stack, any, sub, gmask, tally)) rayDone = true;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, Queues q, int inBuf, int b0, int maxBounces, uint* cursor) {
     pdlWait(); pdlLaunch();
     const DScene& sc = P.sc;
     const uint n = q.cnt[CNT_EXT(b0)];
     const uint lane = laneId();
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    if (sc.coop != 0u && n <= totalWarps * 4u * sc.coop) { tailCoop(P, q, inBuf, b0, maxBounces, cursor, n); return; }
     const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * 16u;
     const bool isHelper = pair && (lane & 1u) != 0u;
     const uint ownerMask = pair ? 0x55555555u : 0xffffffffu;

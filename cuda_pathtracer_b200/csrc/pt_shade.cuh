@@ -164,7 +164,9 @@ struct ShadeParams {
 
 struct ShadeOut { bool pushExt, pushShadow; ShadeRay ext, shadow; };
 
-__device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3 rd, uint slot, const Hit hit, ShadeOut& out) {
+// groupMask != 0: the call is made redundantly by the lanes named in it (k_tail_coop: 8 lanes share a path and compute identical
+// values); they are synchronised between the reads of the slot's state and its writes, and only `writer` lanes store.
+__device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3 rd, uint slot, const Hit hit, ShadeOut& out, const uint groupMask = 0u, const bool writer = true) {
     const DScene& sc = P.sc;
     out.pushExt = out.pushShadow = false;
     uint x, y; slotToPixel(P.map, slot, x, y);
@@ -367,12 +369,13 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
             } else cache.sample_type = 1;
         }
     }
-    if (writeState) {                                                          // setState, types.h:493-498
+    if (groupMask) __syncwarp(groupMask);
+    if (writeState && writer) {                                                // setState, types.h:493-498
         P.masks[slot] = make_float4(state.mask.x, state.mask.y, state.mask.z, __uint_as_float(state.fromSpecular ? 1u : 0u));
         P.accucolors[slot] = make_float4(state.accucolor.x, state.accucolor.y, state.accucolor.z, __uint_as_float(state.albedoSet ? 1u : 0u));
         P.lights[slot] = make_float4(state.light.x, state.light.y, state.light.z, 0.0f);
     }
-    if (writeCache && P.cacheWrite && P.bounce < PT_MAX_CACHE_DEPTH) P.sampleCache[(size_t)P.bounce * P.map.nSlots + slot] = cache;
+    if (writeCache && writer && P.cacheWrite && P.bounce < PT_MAX_CACHE_DEPTH) P.sampleCache[(size_t)P.bounce * P.map.nSlots + slot] = cache;
 }
 
 }  // namespace ptb

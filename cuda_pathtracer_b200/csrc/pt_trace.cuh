@@ -148,8 +148,10 @@ struct LaneState {
 struct QueueIO {                // the wavefront queues: SoA float4 streams
     const float4* rayO; const float4* rayD; float4* hits; const float4* lights; float4* accucolors;
     const uint* perm;           // ray sorting (k_sort_*): fetch position -> queue index, nullptr = queue order
+    static constexpr bool kStreams = true;      // rays are two contiguous float4 streams: a fetch window can be staged with bulk copies
     __device__ __forceinline__ uint index(uint i) const { return perm ? perm[i] : i; }
     __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const { o4 = rayO[i]; d4 = rayD[i]; }
+    __device__ __forceinline__ void window(uint base, float4*& o, float4*& d) const { o = const_cast<float4*>(rayO + base); d = const_cast<float4*>(rayD + base); }
     template <bool ANY> __device__ __forceinline__ void store(uint i, const LaneState& L) const {
         if (ANY) {
             if (L.hitId == PT_NONE) {                                         // unoccluded: kernels.h:806-809
@@ -164,10 +166,12 @@ struct QueueIO {                // the wavefront queues: SoA float4 streams
 };
 struct DebugIO {                // reference-format rays in, reference-format hits out (pt_debug_trace)
     const pt_ray* rays; pt_hit* out;
+    static constexpr bool kStreams = false;
     __device__ __forceinline__ uint index(uint i) const { return i; }
     __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const {
         o4 = *reinterpret_cast<const float4*>(&rays[i].origin); d4 = *reinterpret_cast<const float4*>(&rays[i].direction);
     }
+    __device__ __forceinline__ void window(uint, float4*& o, float4*& d) const { o = nullptr; d = nullptr; }
     template <bool ANY> __device__ __forceinline__ void store(uint i, const LaneState& L) const {
         pt_hit p; p.primitive_type = L.hitType; p.primitive_id = L.hitId; p.instance_id = L.hitInst; p.t = L.tbest;
         if (L.hitId == PT_NONE) { p.primitive_type = 0; p.instance_id = 0; }
@@ -378,6 +382,24 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     bool exhausted = n == 0;
+#if defined(PT_QUEUE_BULK)
+    // Build knob (A/B for the north star's "ray buffers staged through shared memory or TMA"): a warp's fetch window -- up to 32
+    // consecutive queue entries, 16 B each in the two streams -- is brought into shared memory by two bulk copies
+    // (cp.async.bulk, the 1-D TMA path) that complete on the warp's mbarrier, instead of one float4 load per lane and stream.
+    __shared__ __align__(16) float4 stageO[4][32];
+    __shared__ __align__(16) float4 stageD[4][32];
+    __shared__ __align__(8) unsigned long long stageBar[4];
+    const uint wib = (threadIdx.x >> 5) & 3u;
+    const uint barAddr = (uint)__cvta_generic_to_shared(&stageBar[wib]);
+    uint stagePhase = 0;
+    if (IO::kStreams) {
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
+#endif
     while (true) {
         // ---- F: fetch ----
         const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
@@ -389,9 +411,34 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base + want >= n) exhausted = true;
             const uint r = __popc(~activeMask & ((1u << lane) - 1u));          // rank among the idle lanes
+#if defined(PT_QUEUE_BULK)
+            const bool staged = IO::kStreams && io.index(0u) == 0u && io.index(1u) == 1u && base < n;      // queue order (no fetch permutation)
+            if (staged) {
+                const uint cnt = min(want, n - base);
+                __syncwarp();                                                  // every lane is done with the previous window
+                if (lane == 0) {
+                    float4* srcO; float4* srcD; io.window(base, srcO, srcD);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barAddr), "r"(cnt * 32u) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 ::"r"((uint)__cvta_generic_to_shared(&stageO[wib][0])), "l"(srcO), "r"(cnt * 16u), "r"(barAddr) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 ::"r"((uint)__cvta_generic_to_shared(&stageD[wib][0])), "l"(srcD), "r"(cnt * 16u), "r"(barAddr) : "memory");
+                }
+                uint done = 0;
+                do {
+                    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(barAddr), "r"(stagePhase) : "memory");
+                } while (!done);
+                stagePhase ^= 1u;
+            }
+#endif
             if (L.ray == PT_NONE && r < want && base + r < n) {
                 L.ray = io.index(base + r);
-                float4 o4, d4; io.load(L.ray, o4, d4);
+                float4 o4, d4;
+#if defined(PT_QUEUE_BULK)
+                if (staged) { o4 = stageO[wib][r]; d4 = stageD[wib][r]; } else
+#endif
+                io.load(L.ray, o4, d4);
                 if (!beginRay(sc, L, o4, d4, ANY)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
             }
         } else if (nActive == 0) break;
@@ -407,6 +454,124 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
             const bool work = hasBlasWork(L);
             if (__popc(__ballot_sync(0xffffffffu, work)) < minKeep) break;
             if (work && blasTrip(sc, L, stack, ANY, tally)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+        }
+    }
+}
+
+// ---- cooperative traversal: 8 lanes per ray ------------------------------------------------------------------------------
+// When a queue is much shorter than the machine is wide (deep bounces, small multi-GPU shards) most lanes of traceLoop have
+// no ray, and the launch costs the latency of its slowest ray: ~50-100 dependent steps of "fetch a node, test 8 boxes, fetch
+// triangles, test them".  Here a ray owns a GROUP of 8 lanes (4 rays per warp).  Ray state and stack are replicated in the 8
+// lanes (identical instructions on identical values, so no broadcasts are needed); the lanes split the work of a step:
+//   node step:  lane j tests child j of the 8-wide node (2 vector loads of the node header, 7 byte loads of its own
+//               quantised box and meta byte), a group-wide OR (REDUX) assembles the hit mask;
+//   triangle step: lane j tests the j-th pending triangle of the node's leaves (up to 8 per pass, up to 24 pending), a
+//               group-wide min over (t, id) picks the winner -- the same arithmetic per triangle (triIntersect) and the same
+//               selection rule as traceLoop (smallest t, lowest id among equal t inside an instance), hence the same hits.
+// A step then costs one dependent load + ~1/6 of the instructions of the one-lane form.
+__device__ __forceinline__ void coopNodeStep(const DScene& sc, LaneState& L, TravStack& stack, const uint sub, const uint gmask) {
+    uint2 ngroup = L.ngroup;
+    const uint bit = 31u - __clz(ngroup.y);
+    ngroup.y &= ~(1u << bit);
+    if (ngroup.y > 0x00FFFFFFu) { stack.push(L.sp, ngroup); }
+    const uint slot = (bit - 24u) ^ L.octinv;
+    const uint rel = __popc(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
+    const float4* np = sc.nodes + (size_t)(ngroup.x + rel) * 5;
+    const float4 n0 = ldg4(np), n1 = ldg4(np + 1);
+    const unsigned char* nb = reinterpret_cast<const unsigned char*>(np);
+    const uint meta = __ldg(nb + 24 + sub);
+    const uint qlx = __ldg(nb + 32 + sub), qly = __ldg(nb + 40 + sub), qlz = __ldg(nb + 48 + sub);
+    const uint qhx = __ldg(nb + 56 + sub), qhy = __ldg(nb + 64 + sub), qhz = __ldg(nb + 72 + sub);
+    const uint ew = __float_as_uint(n0.w);
+    const float sx = __uint_as_float((ew & 0xffu) << 23), sy = __uint_as_float(((ew >> 8) & 0xffu) << 23), sz = __uint_as_float(((ew >> 16) & 0xffu) << 23);
+    const float aix = sx * L.idir.x, aiy = sy * L.idir.y, aiz = sz * L.idir.z;
+    const float aox = (n0.x - L.o.x) * L.idir.x, aoy = (n0.y - L.o.y) * L.idir.y, aoz = (n0.z - L.o.z) * L.idir.z;
+    const bool negx = L.d.x < 0.0f, negy = L.d.y < 0.0f, negz = L.d.z < 0.0f;
+    const float tnx = __fmaf_rn((float)(negx ? qhx : qlx), aix, aox), tny = __fmaf_rn((float)(negy ? qhy : qly), aiy, aoy), tnz = __fmaf_rn((float)(negz ? qhz : qlz), aiz, aoz);
+    const float tfx = __fmaf_rn((float)(negx ? qlx : qhx), aix, aox), tfy = __fmaf_rn((float)(negy ? qly : qhy), aiy, aoy), tfz = __fmaf_rn((float)(negz ? qlz : qhz), aiz, aoz);
+    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+    const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, L.tcull));
+    const bool inner = (meta & 0x18u) == 0x18u;                      // is_inner: meta & (meta << 1) & 0x10
+    const uint bitIndex = (meta ^ (inner ? L.octinv : 0u)) & 0x1Fu;
+    const uint mine = (cmin <= cmax) ? (((meta >> 5) & 7u) << bitIndex) : 0u;
+    const uint hitmask = __reduce_or_sync(gmask, mine);
+    L.ngroup = make_uint2(__float_as_uint(n1.x), (hitmask & 0xFF000000u) | (ew >> 24));
+    L.tgroup = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
+}
+// One pass over up to 8 pending triangles of the group's ray.  Returns true when an any-hit ray found its occluder.
+template <class TALLY>
+__device__ __forceinline__ bool coopTriStep(const DScene& sc, LaneState& L, const bool ANY, const uint sub, const uint gmask, TALLY& tally) {
+    const uint pending = L.tgroup.y;
+    const uint ti = __fns(pending, 0u, sub + 1u);                    // position of this lane's triangle (the (sub+1)-th set bit), ~0u: none
+    const uint p8 = __fns(pending, 0u, 8u);
+    L.tgroup.y = (p8 >= 31u) ? 0u : (pending & (0xFFFFFFFEu << p8));  // the 8 lowest set bits are taken by this pass
+    unsigned long long key = ~0ull;
+    if (ti != 0xffffffffu) {
+        tally.tri();
+        const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
+        const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+        float t, u, v;
+        if (triIntersect(L.o, L.d, f3(a), f3(b), f3(c), t, u, v)) key = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(a.w);   // t > 0: bit order == numeric order
+    }
+#pragma unroll
+    for (uint off = 1; off < 8; off <<= 1) {
+        const unsigned long long o = __shfl_xor_sync(gmask, key, off);
+        key = o < key ? o : key;
+    }
+    if (key != ~0ull) {
+        const float t = __uint_as_float((uint)(key >> 32));
+        const uint id = (uint)key;
+        if (t < L.tbest || (!ANY && t == L.tbest && L.found && id < L.hitId)) {
+            L.tbest = t; L.hitId = id; L.hitInst = L.curInst; L.hitType = 0; L.found = true;
+            L.tcull = t * 1.000001f;
+            if (ANY) return true;
+        }
+    }
+    return false;
+}
+template <class TALLY>
+__device__ __forceinline__ bool coopBlasTrip(const DScene& sc, LaneState& L, TravStack& stack, const bool ANY, const uint sub, const uint gmask, TALLY& tally) {
+    if (L.tgroup.y == 0u) { coopNodeStep(sc, L, stack, sub, gmask); tally.node(); }
+    if (L.tgroup.y != 0u && coopTriStep(sc, L, ANY, sub, gmask, tally)) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
+    if (L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack.pop(L.sp);
+    return false;
+}
+
+// The warp loop of the cooperative form: F idle GROUPS claim queue entries (one atomic per warp), T groups in the top level
+// run TLAS steps (all 8 lanes in lockstep), B groups inside an instance run the cooperative bottom-level loop.
+template <bool ANY, class IO, class TALLY>
+__device__ __forceinline__ void traceLoopCoop(const DScene& sc, const uint n, uint* cursor, const IO io, TALLY& tally) {
+    const uint lane = laneId(), group = lane >> 3, sub = lane & 7u, gmask = 0xFFu << (group * 8u);
+    const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    const uint width = min(4u, max(1u, (n + totalWarps - 1u) / totalWarps));           // groups of a warp that take rays
+    TravStack stack; stack.init();
+    LaneState L;
+    L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
+    bool exhausted = n == 0;
+    while (true) {
+        const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE) & 0x01010101u;      // one bit per group (its lane 0)
+        const uint nActive = __popc(activeMask);
+        if (!exhausted && nActive < width) {
+            const uint want = width - nActive;
+            uint base = 0;
+            if (lane == 0) base = atomicAdd(cursor, want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + want >= n) exhausted = true;
+            const uint r = __popc(~activeMask & 0x01010101u & ((1u << (group * 8u)) - 1u));      // rank among the idle groups
+            if (L.ray == PT_NONE && r < want && base + r < n) {
+                L.ray = io.index(base + r);
+                float4 o4, d4; io.load(L.ray, o4, d4);
+                if (!beginRay(sc, L, o4, d4, ANY)) { if (sub == 0) io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+            }
+        } else if (nActive == 0) break;
+        if (L.ray != PT_NONE && !hasBlasWork(L)) {
+            const uint ray = L.ray;
+            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); }, tally)) { if (sub == 0) io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+        }
+        while (true) {
+            const bool work = hasBlasWork(L);
+            if (__ballot_sync(0xffffffffu, work) == 0u) break;
+            if (work && coopBlasTrip(sc, L, stack, ANY, sub, gmask, tally)) { if (sub == 0) io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
     }
 }

@@ -50,7 +50,7 @@ class OracleLib:
             for n in ("ora_destroy", "ora_set_threads", "ora_upload_scene", "ora_update_instances", "ora_set_toggles",
                       "ora_set_skydome", "ora_set_sky_sampling", "ora_set_sky_constant", "ora_set_blue_noise", "ora_add_texture", "ora_render",
                       "ora_read_image", "ora_read_radiance_cache", "ora_get_stats", "ora_reset_stats",
-                      "ora_get_rand_state", "ora_primary_rays", "ora_trace"):
+                      "ora_get_rand_state", "ora_primary_rays", "ora_trace", "ora_trace_stack_depth"):
                 getattr(L, n).argtypes = None
             cls._lib = L
         return cls._lib
@@ -143,6 +143,14 @@ class OracleLib:
         if counters is not None:
             counters[:] = list(cnt)
         return out
+
+
+def oracle_stack_depth(ora, rays):
+    """Deepest bottom-level BVH2 stack each ray needs in the reference's traversal order (its array holds 18 entries, kernels.h:207)."""
+    rays = np.ascontiguousarray(rays)
+    out = np.zeros(len(rays), np.uint32)
+    ora.L.ora_trace_stack_depth(ora.h, abi.ptr(rays), C.c_uint32(len(rays)), abi.ptr(out))
+    return out
 
 
 def oracle_camera(eye, view_dir, d, focal, aperture, w, h):

@@ -248,7 +248,7 @@ static inline Ray transformRay(const Ray& ray, const pt_mat4x3& m) {     // kern
     return mkRay(no, nd, ray.pixeli);
 }
 
-struct Counters { uint64_t inner, tris, tlas; };   // algorithmic-bytes counters; not in the reference
+struct Counters { uint64_t inner, tris, tlas, maxStack; };   // maxStack: deepest BVH2 stack the ray needed (the reference's array holds 18 entries, kernels.h:207)   // algorithmic-bytes counters; not in the reference
 
 // kernels.h:202-275
 template <bool ANY>
@@ -284,6 +284,7 @@ static bool traverseBVHStack(const Scene& sc, const Ray& ray, Hit& hit, const pt
                 const bool rev = tnear > tfar;
                 cur = rev ? ff : nn;
                 *sp++ = near_id + !rev;
+                if (cnt && (uint64_t)(sp - stack) > cnt->maxStack) cnt->maxStack = (uint64_t)(sp - stack);
             } else if (bnear) cur = nn;
             else if (bfar) cur = ff;
             else needPop = true;
@@ -986,6 +987,17 @@ ORA_API void ora_trace(void* h, const pt_ray* rays, uint32_t n, int any_hit, pt_
         inner += c.inner; tris += c.tris; tlas += c.tlas;
     }
     if (counters3) { counters3[0] += inner; counters3[1] += tris; counters3[2] += tlas; }
+}
+
+// Per ray: the deepest bottom-level stack the reference's traversal order needs (its own array has 18 unchecked entries).
+ORA_API void ora_trace_stack_depth(void* h, const pt_ray* rays, uint32_t n, uint32_t* depth_out) {
+    Oracle& o = *(Oracle*)h;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (uint32_t i = 0; i < n; i++) {
+        Counters c = {0, 0, 0, 0};
+        traverseTopLevel<false>(o.sc, unpack(rays[i]), &c);
+        depth_out[i] = (uint32_t)c.maxStack;
+    }
 }
 
 // ---- single-function pins (same signatures as oracle/ref_harness.cu's ref_*) -------------------------
