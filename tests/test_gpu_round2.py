@@ -77,6 +77,7 @@ def test_counting_mode_same_image_and_plausible_tally(sibenik):
     (a, _, sa), p = render(arrays, cam, 320, 180, 4); p.close()
     cfg = abi.default_config(320, 180, max_ray_depth=8, interactive_depth=1)
     pt = api.Pathtracer(arrays, cfg).Init()
+    pt.HNEE, pt.HCACHE = True, False
     pt.Render(cam, shouldClear=True)
     pt.set_counting(True)
     for _ in range(4):
@@ -99,7 +100,7 @@ def bright_spot_sky(w=64, h=32):
     y, x = np.mgrid[0:h, 0:w].astype(np.float32)
     sky = np.ones((h, w, 4), np.float32)
     sky[..., :3] = 0.15
-    spot = np.exp(-((x - 40.0) ** 2 + (y - 9.0) ** 2) / 6.0)[..., None]       # texture rows: see skyUvToDir (v = 1 - polar angle / pi)
+    spot = np.exp(-((x - 40.0) ** 2 + (y - 24.0) ** 2) / 6.0)[..., None]      # row 24 of 32: v = 0.77, 42 degrees from straight up (skyUvToDir: polar angle = pi (1 - v))
     sky[..., :3] += 40.0 * spot * np.array([1.0, 0.9, 0.7], np.float32)
     return sky
 
