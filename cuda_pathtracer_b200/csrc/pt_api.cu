@@ -83,7 +83,8 @@ struct pt_ctx {
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     bool knobPdlAlways = false;
-    uint32_t coop = 0;                    // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays per warp, latency mode only (PTB200_COOP)
+    uint32_t tailPairMax = 16;            // k_tail gives a path two lanes while the paths number <= this many per warp (PTB200_TAIL_PAIR_MAX)
+    uint32_t coop = 0, coopTail = 0;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
     bool pdlNow = true;                   // ... for the sample being enqueued: samples that overlap others launch plainly (see pt_render)
     bool sortOn = false; uint32_t sortBits = 4, sortBounces = PT_SORT_MAX_BOUNCES;          // pt_set_ray_sorting
@@ -351,7 +352,11 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
         ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
-        if (const char* e = getenv("PTB200_COOP")) ctx->coop = (uint32_t)std::max(0, atoi(e));                                     // developer knob
+        if (const char* e = getenv("PTB200_TAIL_PAIR_MAX")) ctx->tailPairMax = (uint32_t)std::max(1, atoi(e));                     // developer knob
+        if (const char* e = getenv("PTB200_COOP")) {                                                                               // developer knob
+            ctx->coop = ctx->coopTail = (uint32_t)std::max(0, atoi(e));
+            if (const char* c = strchr(e, ',')) ctx->coopTail = (uint32_t)std::max(0, atoi(c + 1));
+        }
         if (cfg->flags & PT_FLAG_SORT_RAYS) ctx->sortOn = true;
         if (const char* e = getenv("PTB200_SORT")) {                                       // developer knob: "bits[,bounces]", 0 = off
             ctx->sortOn = atoi(e) > 0;
@@ -835,8 +840,9 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // 1/8-image shard), the other samples in flight fill the machine.
         ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
         if (ctx->knobMinWidth) ctx->sc.minWidth = ctx->knobMinWidth;
-        ctx->sc.tailPair = (ctx->sc.minWidth < 32u && !ctx->knobNoTailPair) ? 1u : 0u;     // latency mode only: a sample that runs alone
+        ctx->sc.tailPair = (ctx->sc.minWidth < 32u && !ctx->knobNoTailPair) ? ctx->tailPairMax : 0u;     // latency mode only: a sample that runs alone
         ctx->sc.coop = ctx->sc.minWidth < 32u ? ctx->coop : 0u;                            // likewise: overlapped samples fill short launches with each other's rays
+        ctx->sc.coopTail = ctx->sc.minWidth < 32u ? ctx->coopTail : 0u;
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
@@ -1332,7 +1338,7 @@ static int debugTrace(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_
         ctx->dbgCap = n;
     }
     cudaStream_t s = ctx->stream;
-    ctx->sc.minWidth = 1u; ctx->sc.coop = ctx->coop;          // the stage hook runs alone: latency-mode scheduling, cooperative form where the queue is short
+    ctx->sc.minWidth = 1u; ctx->sc.coop = ctx->coop; ctx->sc.coopTail = ctx->coopTail;          // the stage hook runs alone: latency-mode scheduling, cooperative form where the queue is short
     CK(cudaMemcpyAsync(ctx->dbgRays, host_rays, (size_t)n * sizeof(pt_ray), cudaMemcpyHostToDevice, s));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));

@@ -112,7 +112,8 @@ struct DScene {
     uint tailPair;              // scheduling: k_tail may give a path two lanes (extension + shadow ray in parallel) when the queue is short
     float3 sortLo, sortScale;   // ray sorting (pt_kernels.cuh sortBin): cell = (origin - sortLo) * sortScale, clamped
     uint sortBits;              // cells per axis = 1 << sortBits
-    uint coop;                  // scheduling: a launch whose queue holds <= coop x (4 rays per warp) runs the cooperative 8-lanes-per-ray traversal; 0: never
+    uint coop;                  // scheduling: a trace launch whose queue holds <= coop x (4 rays per warp) runs the cooperative 8-lanes-per-ray traversal; 0: never
+    uint coopTail;              // the same bound for k_tail (paths instead of rays)
 };
 
 struct DCamera { float3 eye, viewDir, lt, u, v; float d, focalLength, aperture; };

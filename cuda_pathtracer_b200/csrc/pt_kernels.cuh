@@ -295,7 +295,7 @@ __device__ __forceinline__ void tailCoop(const ShadeParams& P, const Queues& q, 
     const DScene& sc = P.sc;
     const uint lane = laneId(), group = lane >> 3, sub = lane & 7u, gmask = 0xFFu << (group * 8u);
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
-    const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * 2u * max(1u, sc.coop);
+    const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * 2u * max(1u, sc.coopTail);
     const bool isHelper = pair && (group & 1u) != 0u;
     const uint ownerBits = pair ? 0x00010001u : 0x01010101u;                     // lane-0 bits of the groups that own paths
     const uint width = min(pair ? 2u : 4u, max(1u, (n + totalWarps - 1u) / totalWarps));
@@ -413,8 +413,8 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
     const uint n = q.cnt[CNT_EXT(b0)];
     const uint lane = laneId();
     const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
-    if (sc.coop != 0u && n <= totalWarps * 4u * sc.coop) { tailCoop(P, q, inBuf, b0, maxBounces, cursor, n); return; }
-    const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * 16u;
+    if (sc.coopTail != 0u && n <= totalWarps * 4u * sc.coopTail) { tailCoop(P, q, inBuf, b0, maxBounces, cursor, n); return; }
+    const bool pair = sc.tailPair != 0u && P.nee && n <= totalWarps * sc.tailPair;     // tailPair: paths per warp up to which a path gets two lanes (16 = no queueing)
     const bool isHelper = pair && (lane & 1u) != 0u;
     const uint ownerMask = pair ? 0x55555555u : 0xffffffffu;
     const uint width = min(pair ? 16u : 32u, max(max(1u, pair ? 1u : sc.minWidth), (n + totalWarps - 1u) / totalWarps));

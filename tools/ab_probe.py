@@ -17,7 +17,7 @@ if len(sys.argv) > 1:
         VARIANTS.append((name, dict(kv.split("=", 1) for kv in rest.split(",") if kv) if rest else {}))
 arrays = scenes.sibenik_scene().arrays()
 cams = scenes.camera_sweep("sibenik", 1920, 1080, 16)
-KNOBS = ["PTB200_NO_PDL", "PTB200_SORT", "PTB200_TAIL_BOUNCE", "PTB200_MIN_WIDTH", "PTB200_SETS", "PTB200_NO_TAIL_PAIR", "PTB200_COOP", "PTB200_TAIL_GRID"]
+KNOBS = ["PTB200_NO_PDL", "PTB200_SORT", "PTB200_TAIL_BOUNCE", "PTB200_MIN_WIDTH", "PTB200_SETS", "PTB200_NO_TAIL_PAIR", "PTB200_COOP", "PTB200_TAIL_GRID", "PTB200_TAIL_PAIR_MAX", "PTB200_PDL_ALWAYS"]
 
 
 def measure(world, env):
@@ -37,23 +37,33 @@ def measure(world, env):
         for i in range(40): pt.Render(cams[i % 16])
         pt.join(); e1.record(stream); pt.Finish()
         best_t = min(best_t, e0.elapsed_time(e1) / 40)
+    stages = None
+    if os.environ.get("AB_STAGES"):
+        pt.set_profiling(True)
+        for i in range(20): pt.Render(cams[i % 16])
+        pt.Finish()
+        stages = {k: round(1e3 * v[0] / 20, 1) for k, v in pt.profile().items()}
+        pt.set_profiling(False)
     pt.set_guiding_frames(0)
     for i in range(16): pt.Render(cams[i % 16])
     pt.Finish(); pt.reset_stats()
-    best_s = 1e9
-    for rep in range(3):
+    best_s, all_s = 1e9, []
+    for rep in range(5):
         pt.join(); e0.record(stream)
         for i in range(64): pt.Render(cams[i % 16])
         pt.join(); e1.record(stream); pt.Finish()
-        best_s = min(best_s, e0.elapsed_time(e1) / 64)
+        all_s.append(round(e0.elapsed_time(e1) / 64, 4))
+        best_s = min(best_s, all_s[-1])
     st = pt.stats()
-    rays = (st.extend_rays + st.shadow_rays) / (3 * 64)
+    rays = (st.extend_rays + st.shadow_rays) / (5 * 64)
     pt.close()
-    return best_t, best_s, rays
+    return best_t, best_s, rays, stages, all_s
 
 
-for world in (1, 8):
+WORLDS = [int(w) for w in os.environ.get("AB_WORLDS", "1,8").split(",")]
+for world in WORLDS:
     for name, env in VARIANTS:
-        t, s, rays = measure(world, env)
+        t, s, rays, stages, all_s = measure(world, env)
         print(json.dumps({"world": world, "variant": name, "training_ms": round(t, 4), "steady_ms": round(s, 4), "rays_per_sample": int(rays),
-                          "training_mrays_s": round(rays / t / 1e3, 1), "steady_mrays_s": round(rays / s / 1e3, 1)}), flush=True)
+                          "training_mrays_s": round(rays / t / 1e3, 1), "steady_mrays_s": round(rays / s / 1e3, 1), "steady_windows": all_s,
+                          "training_stage_us": stages}), flush=True)
