@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """A/B of scheduling knobs on ONE GPU: training ms/frame and steady ms/sample of the bench workload (sibenik 1080p, depth 8)
 for the whole image (world 1) and for rank 0's share of an emulated 8-rank job, one line per variant.
-usage: tools/ab_probe.py [name=ENV1=v,ENV2=v ...]   (default: a fixed list)"""
+usage: tools/ab_probe.py [name=ENV1=v;ENV2=v ...]   (default: a fixed list)"""
 import os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -14,7 +14,7 @@ if len(sys.argv) > 1:
     VARIANTS = []
     for a in sys.argv[1:]:
         name, _, rest = a.partition("=")
-        VARIANTS.append((name, dict(kv.split("=", 1) for kv in rest.split(",") if kv) if rest else {}))
+        VARIANTS.append((name, dict(kv.split("=", 1) for kv in rest.split(";") if kv) if rest else {}))
 arrays = scenes.sibenik_scene().arrays()
 cams = scenes.camera_sweep("sibenik", 1920, 1080, 16)
 KNOBS = ["PTB200_NO_PDL", "PTB200_SORT", "PTB200_TAIL_BOUNCE", "PTB200_MIN_WIDTH", "PTB200_SETS", "PTB200_NO_TAIL_PAIR", "PTB200_COOP", "PTB200_TAIL_GRID", "PTB200_TAIL_PAIR_MAX", "PTB200_PDL_ALWAYS"]
