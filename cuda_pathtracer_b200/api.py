@@ -209,9 +209,9 @@ class Pathtracer:
 
     def tally(self):
         """{'extend': (node steps, triangle tests, top-level steps), 'connect': (...)} since set_counting(True)."""
-        out = (C.c_uint64 * 6)()
+        out = (C.c_uint64 * 8)()
         self._ck(self.L.pt_get_tally(self.h, out), "pt_get_tally")
-        return {"extend": tuple(int(x) for x in out[0:3]), "connect": tuple(int(x) for x in out[3:6])}
+        return {"extend": tuple(int(x) for x in out[0:3]), "connect": tuple(int(x) for x in out[3:6]), "longest_ray_steps": (int(out[6]), int(out[7]))}
 
     def debug_read_counters(self, n):
         e, s = np.zeros(n, np.uint32), np.zeros(n, np.uint32)

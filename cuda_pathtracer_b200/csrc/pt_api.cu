@@ -84,7 +84,7 @@ struct pt_ctx {
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     bool knobPdlAlways = false;
     uint32_t tailPairMax = 16;            // k_tail gives a path two lanes while the paths number <= this many per warp (PTB200_TAIL_PAIR_MAX)
-    uint32_t coop = 0, coopTail = 0;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
+    uint32_t coop = 4, coopTail = 2;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
     bool pdlNow = true;                   // ... for the sample being enqueued: samples that overlap others launch plainly (see pt_render)
     bool sortOn = false; uint32_t sortBits = 4, sortBounces = PT_SORT_MAX_BOUNCES;          // pt_set_ray_sorting
@@ -453,14 +453,14 @@ PT_API int pt_set_counting(pt_ctx* ctx, int on) {
     if (on) CK(cudaMemsetAsync(ctx->tally, 0, 8 * sizeof(unsigned long long), ctx->stream));
     return PT_OK;
 }
-PT_API int pt_get_tally(pt_ctx* ctx, uint64_t* out6) {
+PT_API int pt_get_tally(pt_ctx* ctx, uint64_t* out6 /* 8 values */) {
     if (!ctx || !out6) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));
     { int jr = joinStreams(ctx); if (jr) return jr; }
     unsigned long long h[8];
     CK(cudaMemcpyAsync(h, ctx->tally, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    for (int i = 0; i < 6; i++) out6[i] = h[i];
+    for (int i = 0; i < 8; i++) out6[i] = h[i];
     return PT_OK;
 }
 // Test / measurement hook: the per-bounce queue counters of the most recent sample that ran on working set 0 (clearing,

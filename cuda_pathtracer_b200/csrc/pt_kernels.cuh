@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace(DScene sc, co
     else traceLoop<ANY>(sc, n, cursor, io, tally);
 }
 // counting variant (pt_set_counting): the same traversal, plus the node steps / triangle tests / top-level steps it
-// performs, summed into tallyOut[0..2] -- the bytes the wide layout actually requests (80 B per node step, 48 B per
+// performs, summed into tallyOut[0..2] (+ the longest single ray) -- the bytes the wide layout actually requests (80 B per node step, 48 B per
 // triangle test, 32 B per top-level node) for the roofline line of bench.py
 template <bool ANY>
 __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_count(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_count(DScene 
     QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = nullptr;
     Tally tally;
     traceLoop<ANY>(sc, *count, cursor, io, tally);
-    tally.flush(tallyOut);
+    tally.flush(tallyOut, tallyOut + (ANY ? 4 : 6));        // tally buffer: ext[0..2], conn[3..5], longest ext ray [6], longest shadow ray [7]
 }
 
 // extend(b+1) and connect(b) in ONE launch: both queues exist once shade(b) has run and neither kernel touches what the

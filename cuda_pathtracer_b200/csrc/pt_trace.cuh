@@ -220,15 +220,20 @@ struct NoTally {
     __device__ __forceinline__ void node() {}
     __device__ __forceinline__ void tri() {}
     __device__ __forceinline__ void top() {}
+    __device__ __forceinline__ void begin() {}
+    __device__ __forceinline__ void end() {}
 };
 struct Tally {
-    uint nNode = 0, nTri = 0, nTop = 0;
-    __device__ __forceinline__ void node() { nNode++; }
-    __device__ __forceinline__ void tri() { nTri++; }
+    uint nNode = 0, nTri = 0, nTop = 0, cur = 0, longest = 0;      // longest: most node steps + triangle tests any ONE ray took (what a short launch costs)
+    __device__ __forceinline__ void node() { nNode++; cur++; }
+    __device__ __forceinline__ void tri() { nTri++; cur++; }
     __device__ __forceinline__ void top() { nTop++; }
-    __device__ __forceinline__ void flush(unsigned long long* out) {
+    __device__ __forceinline__ void begin() { cur = 0; }
+    __device__ __forceinline__ void end() { longest = max(longest, cur); }
+    __device__ __forceinline__ void flush(unsigned long long* out, unsigned long long* outLongest) {
         const uint a = __reduce_add_sync(0xffffffffu, nNode), b = __reduce_add_sync(0xffffffffu, nTri), c = __reduce_add_sync(0xffffffffu, nTop);
-        if (laneId() == 0) { atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c); }
+        const uint m = __reduce_max_sync(0xffffffffu, longest);
+        if (laneId() == 0) { atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c); atomicMax(outLongest, (unsigned long long)m); }
     }
 };
 
@@ -434,6 +439,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
 #endif
             if (L.ray == PT_NONE && r < want && base + r < n) {
                 L.ray = io.index(base + r);
+                tally.begin();
                 float4 o4, d4;
 #if defined(PT_QUEUE_BULK)
                 if (staged) { o4 = stageO[wib][r]; d4 = stageD[wib][r]; } else
@@ -445,7 +451,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
         // ---- T: top level ----
         if (L.ray != PT_NONE && !hasBlasWork(L)) {
             const uint ray = L.ray;
-            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); }, tally)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); }, tally)) { tally.end(); io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
         // ---- B: bottom level ----
         const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
@@ -453,7 +459,7 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
         while (true) {
             const bool work = hasBlasWork(L);
             if (__popc(__ballot_sync(0xffffffffu, work)) < minKeep) break;
-            if (work && blasTrip(sc, L, stack, ANY, tally)) { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
+            if (work && blasTrip(sc, L, stack, ANY, tally)) { tally.end(); io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
     }
 }

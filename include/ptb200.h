@@ -264,9 +264,10 @@ PT_API int  pt_debug_read_wide_bvh(pt_ctx*, void* nodes, uint32_t* n_nodes, void
 PT_API int  pt_set_profiling(pt_ctx*, int on);                         /* also resets the accumulators */
 PT_API int  pt_get_profile(pt_ctx*, double* ms /*[PT_NUM_STAGES]*/, uint64_t* launches /*[PT_NUM_STAGES]*/);
 /* Measurement mode for the roofline line: every bounce as separate wavefront launches of counting traversal kernels;
- * pt_get_tally: node steps, triangle tests, top-level steps of the extension rays [0..2] and of the shadow rays [3..5]. */
+ * pt_get_tally (8 values): node steps, triangle tests, top-level steps of the extension rays [0..2] and of the shadow rays [3..5];
+ * [6] / [7]: the most steps (node + triangle) any single extension / shadow ray took -- what a short launch is bounded by. */
 PT_API int  pt_set_counting(pt_ctx*, int on);
-PT_API int  pt_get_tally(pt_ctx*, uint64_t* out6);
+PT_API int  pt_get_tally(pt_ctx*, uint64_t* out8);
 PT_API int  pt_debug_read_counters(pt_ctx*, uint32_t* ext_out, uint32_t* shadow_out, uint32_t n_bounces);   /* per-bounce queue sizes of the last sample on working set 0 */
 PT_API int  pt_get_stats(pt_ctx*, pt_stats* out);
 PT_API int  pt_reset_stats(pt_ctx*);
