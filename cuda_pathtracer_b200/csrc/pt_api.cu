@@ -82,7 +82,7 @@ struct pt_ctx {
     uint32_t tailBounce = 3;              // bounces >= this run in k_tail (one per-path launch) when a sample runs alone; PT_MAX_BOUNCES: never
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
-    bool knobPdlAlways = false;
+    bool knobPdlAlways = false, knobNoMix = false;
     uint32_t tailPairMax = 16;            // k_tail gives a path two lanes while the paths number <= this many per warp (PTB200_TAIL_PAIR_MAX)
     uint32_t coop = 4, coopTail = 2;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
@@ -352,6 +352,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
         ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
+        ctx->knobNoMix = getenv("PTB200_NO_MIX") != nullptr;
         if (const char* e = getenv("PTB200_TAIL_PAIR_MAX")) ctx->tailPairMax = (uint32_t)std::max(1, atoi(e));                     // developer knob
         if (const char* e = getenv("PTB200_COOP")) {                                                                               // developer knob
             ctx->coop = ctx->coopTail = (uint32_t)std::max(0, atoi(e));
@@ -843,6 +844,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         ctx->sc.tailPair = (ctx->sc.minWidth < 32u && !ctx->knobNoTailPair) ? ctx->tailPairMax : 0u;     // latency mode only: a sample that runs alone
         ctx->sc.coop = ctx->sc.minWidth < 32u ? ctx->coop : 0u;                            // likewise: overlapped samples fill short launches with each other's rays
         ctx->sc.coopTail = ctx->sc.minWidth < 32u ? ctx->coopTail : 0u;
+        ctx->sc.mixPair = (ctx->sc.minWidth < 32u && !ctx->knobNoMix) ? 1u : 0u;
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
@@ -898,7 +900,12 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
             const uint* extPerm = (bounce > 0 && sortsExt(bounce - 1)) ? S.sortPerm[0] : nullptr;
-            if (fuse && bounce > 0) {
+            if (fuse && bounce > 0 && ctx->sc.mixPair) {
+                StageTimer tm(ctx, PT_STAGE_EXTEND, s);
+                launchK(ctx, k_trace_pair_mixed, dim3(ctx->gridTraceExt), dim3(128), s, ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce), S.q.cnt + CUR_EXT(bounce), S.q.hits,
+                        S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce - 1), S.lights, S.accucolors,
+                        extPerm, sortsSh(bounce - 1) ? S.sortPerm[1] : nullptr);
+            } else if (fuse && bounce > 0) {
                 StageTimer tm(ctx, PT_STAGE_EXTEND, s);
                 launchK(ctx, k_trace_pair, dim3(ctx->gridTraceExt), dim3(128), s, ctx->sc, S.q.rayO[buf], S.q.rayD[buf], S.q.cnt + CNT_EXT(bounce), S.q.cnt + CUR_EXT(bounce), S.q.hits,
                         S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce - 1), S.q.cnt + CUR_CONN(bounce - 1), S.lights, S.accucolors,

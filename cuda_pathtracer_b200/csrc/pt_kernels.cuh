@@ -161,15 +161,31 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair(DScene s
     NoTally tally;
     QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm;
     const uint ne = *extCount, ns = *shCount;
+    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
     if (useCoop(sc, ne + ns)) {
         traceLoopCoop<false>(sc, ne, extCursor, e, tally);
-        QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
         traceLoopCoop<true>(sc, ns, shCursor, c, tally);
         return;
     }
     traceLoop<false>(sc, ne, extCursor, e, tally);
-    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
     traceLoop<true>(sc, ns, shCursor, c, tally);
+}
+
+// The same launch for a sample that runs alone (latency mode): both queues as ONE work list (traceLoopMixed), cooperative when
+// short.  A kernel of its own so that k_trace_pair's register allocation stays what it is for the throughput launches.
+__global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair_mixed(DScene sc, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+                                                    const uint* __restrict__ extCount, uint* extCursor, float4* __restrict__ hits,
+                                                    const float4* __restrict__ shO, const float4* __restrict__ shD,
+                                                    const uint* __restrict__ shCount,
+                                                    const float4* __restrict__ lights, float4* accucolors,
+                                                    const uint* __restrict__ extPerm, const uint* __restrict__ shPerm) {
+    pdlWait(); pdlLaunch();
+    NoTally tally;
+    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm;
+    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
+    const uint ne = *extCount, ns = *shCount;
+    if (useCoop(sc, ne + ns)) traceLoopCoopMixed(sc, ne, ns, extCursor, e, c, tally);
+    else traceLoopMixed(sc, ne, ns, extCursor, e, c, tally);
 }
 
 // stage-parity hook: reference-format rays in, reference-format hits out (pt_debug_trace)

@@ -582,4 +582,93 @@ __device__ __forceinline__ void traceLoopCoop(const DScene& sc, const uint n, ui
     }
 }
 
+// ---- extension and shadow queue as ONE work list (latency mode of k_trace_pair) ------------------------------------------
+// extend(b+1) and connect(b) are independent once shade(b) has run.  Draining one queue after the other costs a warp the
+// longest ray of its extension batch AND of its shadow batches; when a sample runs alone on a small shard that is most of the
+// launch.  Here both queues form one index space [0, nE + nS): entry i < nE is extension ray i, the others are shadow rays, so
+// every warp takes a few batches of whatever comes next and the two kinds are in flight side by side.  Per lane (per group)
+// `any` says which kind it carries; the per-ray work is traceLoop's (same functions), hence the same results.
+template <class TALLY>
+__device__ __forceinline__ void traceLoopMixed(const DScene& sc, const uint nE, const uint nS, uint* cursor, const QueueIO ioE, const QueueIO ioS, TALLY& tally) {
+    const uint lane = laneId();
+    const uint n = nE + nS;
+    const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    const uint width = min(32u, max(max(1u, sc.minWidth), (n + totalWarps - 1u) / totalWarps));
+    TravStack stack; stack.init();
+    LaneState L;
+    L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
+    bool any = false;
+    bool exhausted = n == 0;
+    auto finish = [&]() { if (any) ioS.template store<true>(L.ray, L); else ioE.template store<false>(L.ray, L); L.ray = PT_NONE; };
+    while (true) {
+        const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
+        const uint nActive = __popc(activeMask);
+        if (!exhausted && nActive == 0) {
+            uint base = 0;
+            if (lane == 0) base = atomicAdd(cursor, width);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + width >= n) exhausted = true;
+            const uint i = base + lane;
+            if (lane < width && i < n) {
+                any = i >= nE;
+                L.ray = any ? ioS.index(i - nE) : ioE.index(i);
+                float4 o4, d4;
+                if (any) ioS.load(L.ray, o4, d4); else ioE.load(L.ray, o4, d4);
+                if (!beginRay(sc, L, o4, d4, any)) finish();
+            }
+        } else if (nActive == 0) break;
+        if (L.ray != PT_NONE && !hasBlasWork(L)) {
+            const uint ray = L.ray;
+            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { if (any) ioS.load(ray, o4, d4); else ioE.load(ray, o4, d4); }, tally)) finish();
+        }
+        while (true) {
+            const bool work = hasBlasWork(L);
+            if (__ballot_sync(0xffffffffu, work) == 0u) break;
+            if (work && blasTrip(sc, L, stack, any, tally)) finish();
+        }
+    }
+}
+template <class TALLY>
+__device__ __forceinline__ void traceLoopCoopMixed(const DScene& sc, const uint nE, const uint nS, uint* cursor, const QueueIO ioE, const QueueIO ioS, TALLY& tally) {
+    const uint lane = laneId(), group = lane >> 3, sub = lane & 7u, gmask = 0xFFu << (group * 8u);
+    const uint n = nE + nS;
+    const uint totalWarps = (gridDim.x * blockDim.x) >> 5;
+    const uint width = min(4u, max(1u, (n + totalWarps - 1u) / totalWarps));
+    TravStack stack; stack.init();
+    LaneState L;
+    L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
+    bool any = false;
+    bool exhausted = n == 0;
+    auto finish = [&]() { if (sub == 0u) { if (any) ioS.template store<true>(L.ray, L); else ioE.template store<false>(L.ray, L); } L.ray = PT_NONE; };
+    while (true) {
+        const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE) & 0x01010101u;
+        const uint nActive = __popc(activeMask);
+        if (!exhausted && nActive < width) {
+            const uint want = width - nActive;
+            uint base = 0;
+            if (lane == 0) base = atomicAdd(cursor, want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + want >= n) exhausted = true;
+            const uint r = __popc(~activeMask & 0x01010101u & ((1u << (group * 8u)) - 1u));
+            const uint i = base + r;
+            if (L.ray == PT_NONE && r < want && i < n) {
+                any = i >= nE;
+                L.ray = any ? ioS.index(i - nE) : ioE.index(i);
+                float4 o4, d4;
+                if (any) ioS.load(L.ray, o4, d4); else ioE.load(L.ray, o4, d4);
+                if (!beginRay(sc, L, o4, d4, any)) finish();
+            }
+        } else if (nActive == 0) break;
+        if (L.ray != PT_NONE && !hasBlasWork(L)) {
+            const uint ray = L.ray;
+            if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { if (any) ioS.load(ray, o4, d4); else ioE.load(ray, o4, d4); }, tally)) finish();
+        }
+        while (true) {
+            const bool work = hasBlasWork(L);
+            if (__ballot_sync(0xffffffffu, work) == 0u) break;
+            if (work && coopBlasTrip(sc, L, stack, any, sub, gmask, tally)) finish();
+        }
+    }
+}
+
 }  // namespace ptb
