@@ -347,6 +347,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if (cfg->flags & PT_FLAG_WAVEFRONT_ONLY) ctx->tailBounce = PT_MAX_BOUNCES;
         else if ((cfg->flags >> 8) & 0xffu) { ctx->tailBounce = std::max(1u, ((cfg->flags >> 8) & 0xffu) - 1u); ctx->tailForced = true; }
         if (const char* e = getenv("PTB200_TAIL_BOUNCE")) { ctx->tailBounce = std::max(1, atoi(e)); ctx->tailForced = true; }      // developer knob (tools/tune.sh)
+        if (const char* e = getenv("PTB200_TAIL_ALONE")) ctx->tailBounce = std::max(1, atoi(e));                 // developer knob: tail bounce of samples that run alone only
         if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->knobMinWidth = (uint32_t)std::max(1, std::min(32, atoi(e)));          // developer knobs, read once
         ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
         ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
