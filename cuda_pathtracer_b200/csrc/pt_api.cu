@@ -83,6 +83,10 @@ struct pt_ctx {
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     bool knobPdlAlways = false, knobNoMix = false;
+    // Feedback for the tail bounce of samples that run alone: the per-bounce queue sizes of finished samples come back through a
+    // small pinned ring (asynchronous copies; the host never waits for one) and the next sample starts its per-path tail at the
+    // first bounce whose queue has shrunk to about one and a half paths per tail warp.
+    uint32_t* fbHost = nullptr; cudaEvent_t fbEv[8] = {}; bool fbUsed[8] = {}; uint32_t fbNext = 0; bool fbOn = true, tailFixed = false;
     uint32_t tailPairMax = 16;            // k_tail gives a path two lanes while the paths number <= this many per warp (PTB200_TAIL_PAIR_MAX)
     uint32_t coop = 4, coopTail = 2;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
@@ -224,6 +228,8 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
     if (ctx->copyReady) cudaEventDestroy(ctx->copyReady);
     if (ctx->imgFree) cudaEventDestroy(ctx->imgFree);
+    if (ctx->fbHost) cudaFreeHost(ctx->fbHost);
+    for (auto e : ctx->fbEv) if (e) cudaEventDestroy(e);
     if (ctx->gatherBlock) cudaFree(ctx->gatherBlock);
     if (ctx->skyPdf) cudaFree(ctx->skyPdf);
     if (ctx->skyCdf) cudaFree(ctx->skyCdf);
@@ -347,7 +353,12 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if (cfg->flags & PT_FLAG_WAVEFRONT_ONLY) ctx->tailBounce = PT_MAX_BOUNCES;
         else if ((cfg->flags >> 8) & 0xffu) { ctx->tailBounce = std::max(1u, ((cfg->flags >> 8) & 0xffu) - 1u); ctx->tailForced = true; }
         if (const char* e = getenv("PTB200_TAIL_BOUNCE")) { ctx->tailBounce = std::max(1, atoi(e)); ctx->tailForced = true; }      // developer knob (tools/tune.sh)
-        if (const char* e = getenv("PTB200_TAIL_ALONE")) ctx->tailBounce = std::max(1, atoi(e));                 // developer knob: tail bounce of samples that run alone only
+        if (const char* e = getenv("PTB200_TAIL_ALONE")) { ctx->tailBounce = std::max(1, atoi(e)); ctx->tailFixed = true; }   // developer knob: tail bounce of samples that run alone only
+        ctx->fbOn = !getenv("PTB200_NO_FEEDBACK") && !ctx->tailForced && !ctx->tailFixed && !(cfg->flags & PT_FLAG_WAVEFRONT_ONLY);
+        if (ctx->fbOn) {
+            CK(cudaHostAlloc((void**)&ctx->fbHost, 8 * (PT_MAX_BOUNCES + 1) * sizeof(uint32_t), cudaHostAllocDefault));
+            for (auto& e : ctx->fbEv) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        }
         if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->knobMinWidth = (uint32_t)std::max(1, std::min(32, atoi(e)));          // developer knobs, read once
         ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
         ctx->knobNoTailPair = getenv("PTB200_NO_TAIL_PAIR") != nullptr;
@@ -866,7 +877,22 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // runs alone (clearing / profiled / cache-training frames: 0.95 -> 0.72 ms on a 1/8 shard).  Samples that overlap
         // others stay wavefront to the last bounce: their short launches are filled in by the neighbours (measured
         // 1.77 -> 1.58 ms/sample at 1080p).  Either way the per-path operation order is the same: identical images.
-        const uint32_t waveBounces = ctx->counting ? max_bounces : std::min(max_bounces, (overlapped && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : ctx->tailBounce);
+        uint32_t tailFrom = ctx->tailBounce;
+        if (ctx->fbOn && !overlapped && !should_clear) {
+            // newest finished sample whose queue sizes have landed: the tail starts at the first bounce with few enough paths for the
+            // per-path kernel (measured optimum on 1/1 .. 1/8 of 1080p: where the queue has fallen to 1.2-2.5 k paths, gpurun_out/r2g_ab.log)
+            const uint32_t few = (uint32_t)ctx->gridTail * 4u * 3u / 2u;
+            for (uint32_t k = 1; k <= 8; k++) {
+                const uint32_t slot = (ctx->fbNext + 8u - k) & 7u;
+                if (!ctx->fbUsed[slot] || cudaEventQuery(ctx->fbEv[slot]) != cudaSuccess) continue;
+                const uint32_t* c = ctx->fbHost + (size_t)slot * (PT_MAX_BOUNCES + 1);
+                tailFrom = max_bounces;
+                for (uint32_t b = 1; b < max_bounces; b++) if (c[b] <= few) { tailFrom = b; break; }
+                break;
+            }
+            cudaGetLastError();                               // cudaErrorNotReady of a query is not an error
+        }
+        const uint32_t waveBounces = ctx->counting ? max_bounces : std::min(max_bounces, (overlapped && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : tailFrom);
         const bool connects = (ctx->HNEE && deviceNEE) || skyNEE;                          // :286 (no shadow rays exist when the device _NEE is false)
         const bool fuse = connects && !ctx->prof && !ctx->counting;                        // connect(b) rides in the launch of extend(b+1)
         // ray sorting: shade(b) bins the rays it pushes, the two small kernels after it turn the bins into fetch permutations
@@ -972,6 +998,12 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             }
         }
         if (!accumulated) { int ar = accumulate(); if (ar) return ar; }
+        if (ctx->fbOn && !overlapped && !should_clear && max_bounces == ctx->cfg.max_ray_depth) {
+            const uint32_t slot = ctx->fbNext & 7u;
+            CK(cudaMemcpyAsync(ctx->fbHost + (size_t)slot * (PT_MAX_BOUNCES + 1), S.q.cnt, (PT_MAX_BOUNCES + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+            CK(cudaEventRecord(ctx->fbEv[slot], s));
+            ctx->fbUsed[slot] = true; ctx->fbNext++;
+        }
         if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
         ctx->prevTraining = training;
         ctx->sampleIdx++;                                                                  // :300
