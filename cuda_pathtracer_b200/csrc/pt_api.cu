@@ -83,10 +83,11 @@ struct pt_ctx {
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     bool knobPdlAlways = false, knobNoMix = false;
+    uint32_t headAt = 3;                  // bounce at which a lone sample releases the next sample's head (PTB200_HEAD_AT)
     // Feedback for the tail bounce of samples that run alone: the per-bounce queue sizes of finished samples come back through a
     // small pinned ring (asynchronous copies; the host never waits for one) and the next sample starts its per-path tail at the
     // first bounce whose queue has shrunk to about one and a half paths per tail warp.
-    uint32_t* fbHost = nullptr; cudaEvent_t fbEv[8] = {}; bool fbUsed[8] = {}; uint32_t fbNext = 0; bool fbOn = true, tailFixed = false;
+    uint32_t* fbHost = nullptr; cudaEvent_t fbEv[8] = {}; bool fbUsed[8] = {}; uint32_t fbNext = 0, fbTail = 0; bool fbOn = true, tailFixed = false;
     uint32_t tailPairMax = 16;            // k_tail gives a path two lanes while the paths number <= this many per warp (PTB200_TAIL_PAIR_MAX)
     uint32_t coop = 4, coopTail = 2;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
@@ -365,6 +366,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
         ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
         ctx->knobNoMix = getenv("PTB200_NO_MIX") != nullptr;
+        if (const char* e = getenv("PTB200_HEAD_AT")) ctx->headAt = (uint32_t)std::max(1, atoi(e));                               // developer knob
         if (const char* e = getenv("PTB200_TAIL_PAIR_MAX")) ctx->tailPairMax = (uint32_t)std::max(1, atoi(e));                     // developer knob
         if (const char* e = getenv("PTB200_COOP")) {                                                                               // developer knob
             ctx->coop = ctx->coopTail = (uint32_t)std::max(0, atoi(e));
@@ -877,7 +879,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // runs alone (clearing / profiled / cache-training frames: 0.95 -> 0.72 ms on a 1/8 shard).  Samples that overlap
         // others stay wavefront to the last bounce: their short launches are filled in by the neighbours (measured
         // 1.77 -> 1.58 ms/sample at 1080p).  Either way the per-path operation order is the same: identical images.
-        uint32_t tailFrom = ctx->tailBounce;
+        uint32_t tailFrom = ctx->fbTail ? ctx->fbTail : ctx->tailBounce;                   // the last decision stands until newer queue sizes have landed (the host runs many samples ahead)
         if (ctx->fbOn && !overlapped && !should_clear) {
             // newest finished sample whose queue sizes have landed: the tail starts at the first bounce with few enough paths for the
             // per-path kernel (measured optimum on 1/1 .. 1/8 of 1080p: where the queue has fallen to 1.2-2.5 k paths, gpurun_out/r2g_ab.log)
@@ -888,6 +890,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
                 const uint32_t* c = ctx->fbHost + (size_t)slot * (PT_MAX_BOUNCES + 1);
                 tailFrom = max_bounces;
                 for (uint32_t b = 1; b < max_bounces; b++) if (c[b] <= few) { tailFrom = b; break; }
+                ctx->fbTail = tailFrom;
                 break;
             }
             cudaGetLastError();                               // cudaErrorNotReady of a query is not an error
@@ -924,8 +927,13 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
                 launchK(ctx, k_trace<true>, dim3(ctx->gridTraceAny), dim3(128), s, ctx->sc, S.q.shO, S.q.shD, S.q.cnt + CNT_SHADOW(bounce),
                         S.q.cnt + CUR_CONN(bounce), nullptr, S.lights, S.accucolors, sortsSh(bounce) ? S.sortPerm[1] : nullptr);
         };
+        // From here on this sample's launches are short (few rays, latency bound): the next sample's cache-independent head (primary
+        // rays + first extend) is released to fill the machine under them -- at bounce headAt, or at the tail if that comes first.
+        S.tailValid = false;
+        auto releaseHead = [&]() -> int { if (pipelined && !S.tailValid) { CK(cudaEventRecord(S.tailStart, s)); S.tailValid = true; } return PT_OK; };
         for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
+            if (bounce == ctx->headAt && !overlapped) { int hr = releaseHead(); if (hr) return hr; }
             const uint* extPerm = (bounce > 0 && sortsExt(bounce - 1)) ? S.sortPerm[0] : nullptr;
             if (fuse && bounce > 0 && ctx->sc.mixPair) {
                 StageTimer tm(ctx, PT_STAGE_EXTEND, s);
@@ -959,9 +967,8 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             ctx->randIdx++;                                                                // :283
             if (connects && (!fuse || bounce + 1 == waveBounces)) launchConnect(bounce);
         }
-        S.tailValid = false;
         if (max_bounces > waveBounces) {                                                   // the same bounces, one launch (k_tail)
-            if (pipelined) { CK(cudaEventRecord(S.tailStart, s)); S.tailValid = true; }
+            { int hr = releaseHead(); if (hr) return hr; }
             StageTimer tm(ctx, PT_STAGE_TAIL, s);
             launchK(ctx, k_tail, dim3(ctx->gridTail), dim3(128), s, shadeParams(waveBounces), S.q, (int)(waveBounces & 1), (int)waveBounces, (int)max_bounces,
                     S.q.cnt + CUR_EXT(waveBounces));
