@@ -366,6 +366,9 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
         ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
         ctx->knobNoMix = getenv("PTB200_NO_MIX") != nullptr;
+        // a whole 1080p image: the head (primary rays + first extend, ~0.3 ms) needs the launches of bounce >= 2 to hide under; on a
+        // shard it is short and only disturbs the latency-bound launches, so it waits for the tail (gpurun_out/r2i_ab.log)
+        ctx->headAt = m.nSlots > 1500000u ? 2u : (uint32_t)PT_MAX_BOUNCES;
         if (const char* e = getenv("PTB200_HEAD_AT")) ctx->headAt = (uint32_t)std::max(1, atoi(e));                               // developer knob
         if (const char* e = getenv("PTB200_TAIL_PAIR_MAX")) ctx->tailPairMax = (uint32_t)std::max(1, atoi(e));                     // developer knob
         if (const char* e = getenv("PTB200_COOP")) {                                                                               // developer knob
