@@ -87,7 +87,7 @@ struct pt_ctx {
     // Feedback for the tail bounce of samples that run alone: the per-bounce queue sizes of finished samples come back through a
     // small pinned ring (asynchronous copies; the host never waits for one) and the next sample starts its per-path tail at the
     // first bounce whose queue has shrunk to about one and a half paths per tail warp.
-    uint32_t* fbHost = nullptr; cudaEvent_t fbEv[8] = {}; bool fbUsed[8] = {}; uint32_t fbNext = 0, fbTail = 0; bool fbOn = true, tailFixed = false;
+    uint32_t* fbHost = nullptr; uint32_t* fbDev = nullptr; uint32_t fbSeen = 0, fbTail = 0; bool fbOn = true, tailFixed = false;   // mapped pinned memory: [0] sequence number, [1 + b] extension rays of bounce b
     uint32_t tailPairMax = 16;            // k_tail gives a path two lanes while the paths number <= this many per warp (PTB200_TAIL_PAIR_MAX)
     uint32_t coop = 4, coopTail = 2;      // cooperative (8 lanes per ray) traversal for queues up to coop x 4 rays (paths) per warp, latency mode only (PTB200_COOP=trace[,tail])
     bool pdl = true;                      // stage kernels are launched with programmatic stream serialization (PT_FLAG_NO_PDL / PTB200_NO_PDL: off)
@@ -230,7 +230,6 @@ PT_API void pt_destroy(pt_ctx* ctx) {
     if (ctx->copyReady) cudaEventDestroy(ctx->copyReady);
     if (ctx->imgFree) cudaEventDestroy(ctx->imgFree);
     if (ctx->fbHost) cudaFreeHost(ctx->fbHost);
-    for (auto e : ctx->fbEv) if (e) cudaEventDestroy(e);
     if (ctx->gatherBlock) cudaFree(ctx->gatherBlock);
     if (ctx->skyPdf) cudaFree(ctx->skyPdf);
     if (ctx->skyCdf) cudaFree(ctx->skyCdf);
@@ -357,8 +356,11 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         if (const char* e = getenv("PTB200_TAIL_ALONE")) { ctx->tailBounce = std::max(1, atoi(e)); ctx->tailFixed = true; }   // developer knob: tail bounce of samples that run alone only
         ctx->fbOn = !getenv("PTB200_NO_FEEDBACK") && !ctx->tailForced && !ctx->tailFixed && !(cfg->flags & PT_FLAG_WAVEFRONT_ONLY);
         if (ctx->fbOn) {
-            CK(cudaHostAlloc((void**)&ctx->fbHost, 8 * (PT_MAX_BOUNCES + 1) * sizeof(uint32_t), cudaHostAllocDefault));
-            for (auto& e : ctx->fbEv) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            // written by k_accumulate with plain stores (a copy on the sample's stream would queue behind the image read-backs on the
+            // device-to-host copy engine and stall the next sample, which waits for this one's `done`)
+            CK(cudaHostAlloc((void**)&ctx->fbHost, (PT_MAX_BOUNCES + 2) * sizeof(uint32_t), cudaHostAllocMapped));
+            memset(ctx->fbHost, 0, (PT_MAX_BOUNCES + 2) * sizeof(uint32_t));
+            CK(cudaHostGetDevicePointer((void**)&ctx->fbDev, ctx->fbHost, 0));
         }
         if (const char* e = getenv("PTB200_MIN_WIDTH")) ctx->knobMinWidth = (uint32_t)std::max(1, std::min(32, atoi(e)));          // developer knobs, read once
         ctx->knobNoTailWait = getenv("PTB200_NO_TAIL_WAIT") != nullptr;
@@ -887,16 +889,13 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             // newest finished sample whose queue sizes have landed: the tail starts at the first bounce with few enough paths for the
             // per-path kernel (measured optimum on 1/1 .. 1/8 of 1080p: where the queue has fallen to 1.2-2.5 k paths, gpurun_out/r2g_ab.log)
             const uint32_t few = (uint32_t)ctx->gridTail * 4u * 3u / 2u;
-            for (uint32_t k = 1; k <= 8; k++) {
-                const uint32_t slot = (ctx->fbNext + 8u - k) & 7u;
-                if (!ctx->fbUsed[slot] || cudaEventQuery(ctx->fbEv[slot]) != cudaSuccess) continue;
-                const uint32_t* c = ctx->fbHost + (size_t)slot * (PT_MAX_BOUNCES + 1);
+            const volatile uint32_t* c = ctx->fbHost;
+            const uint32_t seq = c[0];
+            if (seq != ctx->fbSeen) {                         // a newer sample has finished (a torn read only costs one sample a worse schedule)
                 tailFrom = max_bounces;
-                for (uint32_t b = 1; b < max_bounces; b++) if (c[b] <= few) { tailFrom = b; break; }
-                ctx->fbTail = tailFrom;
-                break;
+                for (uint32_t b = 1; b < max_bounces; b++) if (c[1 + b] <= few) { tailFrom = b; break; }
+                ctx->fbTail = tailFrom; ctx->fbSeen = seq;
             }
-            cudaGetLastError();                               // cudaErrorNotReady of a query is not an error
         }
         const uint32_t waveBounces = ctx->counting ? max_bounces : std::min(max_bounces, (overlapped && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : tailFrom);
         const bool connects = (ctx->HNEE && deviceNEE) || skyNEE;                          // :286 (no shadow rays exist when the device _NEE is false)
@@ -982,7 +981,8 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         auto accumulate = [&]() -> int {
             if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->imgFree, 0));    // a read-back in flight still reads the image
             if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
-                              launchK(ctx, k_accumulate, dim3(map.nSlots / 256), dim3(256), s, map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces); }   // :299
+                              launchK(ctx, k_accumulate, dim3(map.nSlots / 256), dim3(256), s, map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces,
+                                      (ctx->fbOn && !overlapped && !should_clear && max_bounces == ctx->cfg.max_ray_depth) ? ctx->fbDev : nullptr); }   // :299
             return PT_OK;
         };
         bool accumulated = false;
@@ -1008,12 +1008,6 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             }
         }
         if (!accumulated) { int ar = accumulate(); if (ar) return ar; }
-        if (ctx->fbOn && !overlapped && !should_clear && max_bounces == ctx->cfg.max_ray_depth) {
-            const uint32_t slot = ctx->fbNext & 7u;
-            CK(cudaMemcpyAsync(ctx->fbHost + (size_t)slot * (PT_MAX_BOUNCES + 1), S.q.cnt, (PT_MAX_BOUNCES + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-            CK(cudaEventRecord(ctx->fbEv[slot], s));
-            ctx->fbUsed[slot] = true; ctx->fbNext++;
-        }
         if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
         ctx->prevTraining = training;
         ctx->sampleIdx++;                                                                  // :300

@@ -541,7 +541,8 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
 
 // ---- accumulate + statistics -------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* __restrict__ accucolors, const float4* __restrict__ albedoSample,
-                                                    float4* image, float4* albedo, const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces, uint waveBounces) {
+                                                    float4* image, float4* albedo, const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces, uint waveBounces,
+                                                    volatile uint* feedback) {
     const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint x, y;
     pdlWait(); pdlLaunch();
@@ -562,6 +563,11 @@ __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* _
         for (uint b = 0; b < maxBounces; b++) {
             ext += cnt[CNT_EXT(b)]; sh += cnt[CNT_SHADOW(b)];
             if (b < waveBounces) { wext += cnt[CNT_EXT(b)]; wsh += cnt[CNT_SHADOW(b)]; }
+        }
+        if (feedback) {                              // per-bounce queue sizes for the host's next scheduling decision (mapped host memory)
+            for (uint b = 0; b < maxBounces; b++) feedback[1 + b] = cnt[CNT_EXT(b)];
+            __threadfence_system();
+            feedback[0] = feedback[0] + 1u;
         }
         stats[0] += cnt[CNT_EXT(0)]; stats[1] += ext; stats[2] += sh; stats[3] += ext; stats[4] += 1; stats[5] += wext; stats[6] += wsh;
     }
