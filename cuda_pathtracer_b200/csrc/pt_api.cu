@@ -83,6 +83,7 @@ struct pt_ctx {
     bool tailForced = false;              // PT_FLAG_TAIL_BOUNCE / PTB200_TAIL_BOUNCE given: use k_tail for overlapped samples too
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     bool knobPdlAlways = false, knobNoMix = false;
+    uint32_t anyFarFirst = 0;
     uint32_t headAt = 3;                  // bounce at which a lone sample releases the next sample's head (PTB200_HEAD_AT)
     // Feedback for the tail bounce of samples that run alone: the per-bounce queue sizes of finished samples come back through a
     // small pinned ring (asynchronous copies; the host never waits for one) and the next sample starts its per-path tail at the
@@ -368,6 +369,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
         ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
         ctx->knobNoMix = getenv("PTB200_NO_MIX") != nullptr;
+        ctx->anyFarFirst = getenv("PTB200_ANY_FAR_FIRST") ? (uint32_t)atoi(getenv("PTB200_ANY_FAR_FIRST")) : 0u;                   // developer knob
         // a whole 1080p image: the head (primary rays + first extend, ~0.3 ms) needs the launches of bounce >= 2 to hide under; on a
         // shard it is short and only disturbs the latency-bound launches, so it waits for the tail (gpurun_out/r2i_ab.log)
         ctx->headAt = m.nSlots > 1500000u ? 2u : (uint32_t)PT_MAX_BOUNCES;
@@ -864,6 +866,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         ctx->sc.coop = ctx->sc.minWidth < 32u ? ctx->coop : 0u;                            // likewise: overlapped samples fill short launches with each other's rays
         ctx->sc.coopTail = ctx->sc.minWidth < 32u ? ctx->coopTail : 0u;
         ctx->sc.mixPair = (ctx->sc.minWidth < 32u && !ctx->knobNoMix) ? 1u : 0u;
+        ctx->sc.anyFarFirst = ctx->anyFarFirst;
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
@@ -1382,7 +1385,7 @@ static int debugTrace(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_
         ctx->dbgCap = n;
     }
     cudaStream_t s = ctx->stream;
-    ctx->sc.minWidth = 1u; ctx->sc.coop = ctx->coop; ctx->sc.coopTail = ctx->coopTail;          // the stage hook runs alone: latency-mode scheduling, cooperative form where the queue is short
+    ctx->sc.minWidth = 1u; ctx->sc.coop = ctx->coop; ctx->sc.coopTail = ctx->coopTail; ctx->sc.anyFarFirst = ctx->anyFarFirst;          // the stage hook runs alone: latency-mode scheduling, cooperative form where the queue is short
     CK(cudaMemcpyAsync(ctx->dbgRays, host_rays, (size_t)n * sizeof(pt_ray), cudaMemcpyHostToDevice, s));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));

@@ -114,6 +114,7 @@ struct DScene {
     uint sortBits;              // cells per axis = 1 << sortBits
     uint coop;                  // scheduling: a trace launch whose queue holds <= coop x (4 rays per warp) runs the cooperative 8-lanes-per-ray traversal; 0: never
     uint coopTail;              // the same bound for k_tail (paths instead of rays)
+    uint anyFarFirst;           // any-hit rays visit the children far end first (order only: same boolean)
     uint mixPair;               // scheduling: k_trace_pair treats its two queues as one work list (latency mode)
 };
 

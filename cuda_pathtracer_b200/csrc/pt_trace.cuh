@@ -138,7 +138,7 @@ struct LaneState {
     uint hitId, hitInst, hitType;
     uint curT;                  // TLAS node to process next (PT_NONE: none)
     uint curInst;               // instance being traversed
-    uint octinv;
+    uint octinv, orderFlip;     // orderFlip: 7 reverses the child visiting order (far end first) for this ray, 0 keeps near-first
     uint2 ngroup, tgroup;
     int sp, spBase;
     bool inBLAS, found;
@@ -186,7 +186,7 @@ __device__ __forceinline__ void setModelSpaceDir(LaneState& L) {
     L.idir.x = 1.0f / (fabsf(L.d.x) > ooeps ? L.d.x : copysignf(ooeps, L.d.x));
     L.idir.y = 1.0f / (fabsf(L.d.y) > ooeps ? L.d.y : copysignf(ooeps, L.d.y));
     L.idir.z = 1.0f / (fabsf(L.d.z) > ooeps ? L.d.z : copysignf(ooeps, L.d.z));
-    L.octinv = (L.d.x < 0.0f ? 0u : 4u) | (L.d.y < 0.0f ? 0u : 2u) | (L.d.z < 0.0f ? 0u : 1u);
+    L.octinv = ((L.d.x < 0.0f ? 0u : 4u) | (L.d.y < 0.0f ? 0u : 2u) | (L.d.z < 0.0f ? 0u : 1u)) ^ L.orderFlip;
 }
 
 // Start of a ray: spheres, planes, TLAS root (kernels.h:281-318).  Returns false when the ray is already finished.
@@ -194,6 +194,9 @@ __device__ __forceinline__ bool beginRay(const DScene& sc, LaneState& L, const f
     L.o = f3(o4); L.d = f3(d4);
     L.tbest = o4.w; L.hitId = PT_NONE; L.hitType = 0; L.hitInst = 0;
     L.sp = 0; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.inBLAS = false; L.found = false;
+    // An any-hit ray only asks WHETHER something lies on the segment, so its visiting order is free.  Shadow rays start on the light
+    // (kernels.h:735-747): far-end-first starts the search at the shaded surface, where the occluders of a shadowed point tend to be.
+    L.orderFlip = (ANY && sc.anyFarFirst) ? 7u : 0u;
     float t;
     for (uint i = 0; i < sc.num_spheres; i++)
         if (raySphereIntersect(L.o, L.d, sc.spheres[i], t) && t < L.tbest) {
