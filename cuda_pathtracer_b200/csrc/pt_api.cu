@@ -371,7 +371,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->knobNoMix = getenv("PTB200_NO_MIX") != nullptr;
         ctx->anyFarFirst = getenv("PTB200_ANY_FAR_FIRST") ? (uint32_t)atoi(getenv("PTB200_ANY_FAR_FIRST")) : 0u;                   // developer knob
         // a whole 1080p image: the head (primary rays + first extend, ~0.3 ms) needs the launches of bounce >= 2 to hide under; on a
-        // shard it is short and only disturbs the latency-bound launches, so it waits for the tail (gpurun_out/r2i_ab.log)
+        // shard it is short and only disturbs the latency-bound launches, so it waits for the tail (profiles/r2/ab_r2i_ab.log)
         ctx->headAt = m.nSlots > 1500000u ? 2u : (uint32_t)PT_MAX_BOUNCES;
         if (const char* e = getenv("PTB200_HEAD_AT")) ctx->headAt = (uint32_t)std::max(1, atoi(e));                               // developer knob
         if (const char* e = getenv("PTB200_TAIL_PAIR_MAX")) ctx->tailPairMax = (uint32_t)std::max(1, atoi(e));                     // developer knob
@@ -890,7 +890,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         uint32_t tailFrom = ctx->fbTail ? ctx->fbTail : ctx->tailBounce;                   // the last decision stands until newer queue sizes have landed (the host runs many samples ahead)
         if (ctx->fbOn && !overlapped && !should_clear) {
             // newest finished sample whose queue sizes have landed: the tail starts at the first bounce with few enough paths for the
-            // per-path kernel (measured optimum on 1/1 .. 1/8 of 1080p: where the queue has fallen to 1.2-2.5 k paths, gpurun_out/r2g_ab.log)
+            // per-path kernel (measured optimum on 1/1 .. 1/8 of 1080p: where the queue has fallen to 1.2-2.5 k paths, profiles/r2/ab_r2g_ab.log)
             const uint32_t few = (uint32_t)ctx->gridTail * 4u * 3u / 2u;
             const volatile uint32_t* c = ctx->fbHost;
             const uint32_t seq = c[0];
