@@ -12,6 +12,6 @@ timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/$
 timeout 100 python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu list exit $? $(( $(date +%s)-S ))s"
-timeout 300 ncu --set full --clock-control none --import-source on -k "regex:k_trace|k_tail" -s 17 -c 6 -o gpurun_out/${TAG}_trace -f python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu2.log 2>&1
+timeout 300 ncu --set full --clock-control none --import-source on -k "regex:k_trace|k_tail" -s 8 -c 18 -o gpurun_out/${TAG}_trace -f python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu2.log 2>&1
 echo "ncu full exit $? $(( $(date +%s)-S ))s"
 ls -la gpurun_out | grep ${TAG}
