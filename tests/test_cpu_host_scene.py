@@ -151,3 +151,22 @@ def test_procedural_proxy_builds_identically_in_reference(built):
     s.addObject(s.addModelSoup(soup, material=0), position=(0, 12, 0))
     s.finalize()
     assert_scene_equal(s.arrays(), rs.arrays(), uv=True)
+
+
+def test_obj_face_indices_are_range_checked(tmp_path):
+    """A face that names a vertex / uv / normal the file does not define must be an error code, not an out-of-bounds read
+    (tinyobjloader hands such indices through; the reference would index its vectors with them, scene.h:262-291)."""
+    from cuda_pathtracer_b200.scene import Scene
+    good = "v 0 0 0\nv 1 0 0\nv 0 1 0\nvt 0 0\nvn 0 0 1\nf 1/1/1 2/1/1 3/1/1\n"
+    p = tmp_path / "ok.obj"; p.write_text(good)
+    s = Scene(); s.addObject(s.addModel(str(p))); s.finalize()
+    assert len(s.arrays()["vertices"]) == 1
+    for bad in ("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 7\n",                    # vertex past the end
+                "v 0 0 0\nv 1 0 0\nv 0 1 0\nf -9 2 3\n",                   # relative index before the first vertex
+                "v 0 0 0\nv 1 0 0\nv 0 1 0\nvt 0 0\nf 1/5 2/1 3/1\n",      # uv past the end
+                "v 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nf 1//4 2//1 3//1\n"):  # normal past the end
+        q = tmp_path / "bad.obj"; q.write_text(bad)
+        with pytest.raises(Exception, match="index"):
+            Scene().addModel(str(q))
+    fwd = tmp_path / "fwd.obj"; fwd.write_text("f 1 2 3\nv 0 0 0\nv 1 0 0\nv 0 1 0\n")     # forward references are legal OBJ
+    s2 = Scene(); s2.addModel(str(fwd))
