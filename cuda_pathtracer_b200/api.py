@@ -87,6 +87,7 @@ def load_library():
     L.pt_get_tally.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     L.pt_debug_read_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
     L.pt_gather_image_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+    L.pt_trace_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
     L.pt_debug_trace_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.POINTER(C.c_float), C.c_void_p]
     _LIB = L
     return L
@@ -366,6 +367,14 @@ class Pathtracer:
         rays = np.ascontiguousarray(rays)
         out = np.zeros(len(rays), abi.HIT)
         self._ck(self.L.pt_debug_trace(self.h, abi.ptr(rays), len(rays), int(any_hit), abi.ptr(out)), "pt_debug_trace")
+        return out
+
+    def trace_static(self, rays, any_hit=False):
+        """pt_trace_static: pt_debug_trace without any device allocation (scratch = the library's static device array;
+        at most abi.STATIC_TRACE_MAX_RAYS rays).  No counterpart in the reference."""
+        rays = np.ascontiguousarray(rays)
+        out = np.zeros(len(rays), abi.HIT)
+        self._ck(self.L.pt_trace_static(self.h, abi.ptr(rays), len(rays), int(any_hit), abi.ptr(out)), "pt_trace_static")
         return out
 
     def debug_trace_timed(self, rays, any_hit=False, repeats=5):

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <vector>
 #include <utility>
 #include <chrono>
@@ -1415,3 +1416,64 @@ PT_API int pt_debug_trace_resident(pt_ctx* ctx, const pt_ray* host_rays, uint32_
     return debugTrace(ctx, host_rays, n, any_hit, repeats, out_ms, host_out);
 }
 }  // extern "C"
+
+// ---- pt_trace_static: the traversal hook for callers that may not allocate ------------------------------------------
+// No counterpart in the reference.  Same work and same kernel as
+// pt_debug_trace (k_trace_debug: persistent-warp traversal fed by a work cursor), but the scratch it needs -- the work
+// cursor, the staged rays and the hit records -- lives in ONE file-scope device array instead of cudaMalloc'd buffers.
+// Every GPU that loads the library holds the array (PT_STATIC_SCRATCH_BYTES, about 14 MiB) until the process exits.
+// All calls share it and it keeps the last call's contents: the cursor is cleared by every call; calls that overlap on
+// the GPU (two host threads, two contexts on one device) race on it -- serialise them.
+struct StaticTraceScratch {
+    uint cursor; uint pad[63];                                   // 256 B: the cursor has a line pair to itself
+    pt_ray rays[PT_STATIC_TRACE_MAX_RAYS];
+    pt_hit hits[PT_STATIC_TRACE_MAX_RAYS];
+};
+static_assert(sizeof(StaticTraceScratch) == PT_STATIC_SCRATCH_BYTES, "PT_STATIC_SCRATCH_BYTES in ptb200.h");
+static __device__ __align__(256) unsigned char g_staticScratch[sizeof(StaticTraceScratch)];
+
+// In host code g_staticScratch is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+static constexpr int kMaxStaticDevices = 64;
+static StaticTraceScratch* g_staticScratchPtr[kMaxStaticDevices];
+static std::mutex g_staticScratchMutex;
+
+static cudaError_t staticScratchFor(int device, StaticTraceScratch** out) {
+    if (device < 0 || device >= kMaxStaticDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_staticScratchMutex);
+    if (!g_staticScratchPtr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_staticScratch);       // the caller made `device` current
+        if (e != cudaSuccess) return e;
+        g_staticScratchPtr[device] = (StaticTraceScratch*)p;
+    }
+    *out = g_staticScratchPtr[device];
+    return cudaSuccess;
+}
+
+extern "C" PT_API int pt_trace_static(pt_ctx* ctx, const pt_ray* host_rays, uint32_t n, int any_hit, pt_hit* host_out) {
+    if (!ctx) return PT_ERR_INVALID;
+    if (!host_rays || !host_out || !ctx->haveScene) { ctx->err = "pt_trace_static: needs a scene, host_rays and host_out"; return PT_ERR_INVALID; }
+    if (n > PT_STATIC_TRACE_MAX_RAYS) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "pt_trace_static: %u rays exceed the static scratch (PT_STATIC_TRACE_MAX_RAYS = %u); use pt_debug_trace", n, (unsigned)PT_STATIC_TRACE_MAX_RAYS);
+        ctx->err = buf;
+        return PT_ERR_INVALID;
+    }
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(ctx->cfg.device));
+    StaticTraceScratch* scr = nullptr;
+    CK(staticScratchFor(ctx->cfg.device, &scr));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    cudaStream_t s = ctx->stream;
+    DScene sc = ctx->sc;                                         // by value: the context's own scheduling fields stay as they are
+    sc.minWidth = 1u; sc.coop = ctx->coop; sc.coopTail = ctx->coopTail; sc.anyFarFirst = ctx->anyFarFirst;
+    CK(cudaMemsetAsync(&scr->cursor, 0, sizeof(uint), s));       // the one word that must start at zero
+    CK(cudaMemcpyAsync(scr->rays, host_rays, (size_t)n * sizeof(pt_ray), cudaMemcpyHostToDevice, s));
+    if (any_hit) k_trace_debug<true><<<ctx->gridTraceAny, 128, 0, s>>>(sc, scr->rays, n, &scr->cursor, scr->hits);
+    else k_trace_debug<false><<<ctx->gridTraceExt, 128, 0, s>>>(sc, scr->rays, n, &scr->cursor, scr->hits);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(host_out, scr->hits, (size_t)n * sizeof(pt_hit), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return PT_OK;
+}

@@ -279,6 +279,16 @@ PT_API int  pt_debug_trace(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any
 /* Device-resident variant used for kernel-only timing: rays stay in HBM, returns elapsed ms (CUDA events). */
 PT_API int  pt_debug_trace_resident(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, uint32_t repeats, float* out_ms, pt_hit* host_out);
 
+/* No counterpart in the reference.  pt_debug_trace for callers that may not
+ * allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): same kernel, same
+ * results, but its scratch (work cursor + staged rays + hit records) is a file-scope device array of
+ * PT_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Calls neither cudaMalloc nor cudaFree nor any allocating
+ * routine.  n > PT_STATIC_TRACE_MAX_RAYS (one 640x480 frame) is PT_ERR_INVALID with a message in pt_last_error.  All calls
+ * share the array (it keeps the previous call's contents; the cursor is cleared per call): calls that overlap on one GPU race. */
+#define PT_STATIC_TRACE_MAX_RAYS 307200u
+#define PT_STATIC_SCRATCH_BYTES (256u + PT_STATIC_TRACE_MAX_RAYS * 48u)
+PT_API int  pt_trace_static(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, pt_hit* host_out);
+
 PT_API void* pt_cuda_stream(pt_ctx*);
 
 /* Tile partition, host-callable without a GPU: 32x32-pixel tiles dealt round-robin to
