@@ -42,6 +42,7 @@ struct pt_ctx {
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;       // recorded after the sample's accumulate
         cudaEvent_t tailStart = nullptr;  // recorded right before the sample's k_tail launch
+        cudaEvent_t partDone = nullptr;   // split frames: this tile range's cache additions are in
         bool doneValid = false, tailValid = false;
     } set[PT_MAX_SETS];
     int nSets = 4, cur = 0;
@@ -85,6 +86,7 @@ struct pt_ctx {
     uint32_t knobMinWidth = 0; bool knobNoTailWait = false, knobNoTailPair = false;   // developer knobs (environment, read in pt_create)
     bool knobPdlAlways = false, knobNoMix = false;
     uint32_t anyFarFirst = 0;
+    uint32_t split = 1, splitWidth = 32; bool splitTail = true, splitHold = false;   // cache-training frames as `split` concurrent tile ranges (PTB200_SPLIT=parts[,width[,tail[,hold]]])
     uint32_t headAt = 3;                  // bounce at which a lone sample releases the next sample's head (PTB200_HEAD_AT)
     // Feedback for the tail bounce of samples that run alone: the per-bounce queue sizes of finished samples come back through a
     // small pinned ring (asynchronous copies; the host never waits for one) and the next sample starts its per-path tail at the
@@ -226,6 +228,7 @@ PT_API void pt_destroy(pt_ctx* ctx) {
         for (void* p : sb) if (p) cudaFree(p);
         if (S.done) cudaEventDestroy(S.done);
         if (S.tailStart) cudaEventDestroy(S.tailStart);
+        if (S.partDone) cudaEventDestroy(S.partDone);
         if (S.stream) cudaStreamDestroy(S.stream);
     }
     if (ctx->forkEv) cudaEventDestroy(ctx->forkEv);
@@ -252,6 +255,7 @@ static TileMap makeTileMap(const pt_config* cfg) {
     const uint32_t T = m.tilesX * m.tilesY;
     m.nLocalTiles = T > m.rank ? (T - m.rank + m.world - 1) / m.world : 0;
     m.nSlots = m.nLocalTiles * 1024u;
+    m.slotBase = 0;
     return m;
 }
 // Host view of the tile partition (no GPU needed): the same mapping the kernels use.
@@ -304,6 +308,7 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
             CK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
             CK(cudaEventCreateWithFlags(&S.done, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&S.tailStart, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&S.partDone, cudaEventDisableTiming));
             for (int i = 0; i < 2; i++) {
                 if ((r = devAlloc(ctx, &S.q.rayO[i], cap, false))) return r;
                 if ((r = devAlloc(ctx, &S.q.rayD[i], cap, false))) return r;
@@ -370,6 +375,11 @@ PT_API int pt_create(pt_ctx** out, const pt_config* cfg) {
         ctx->pdl = !(cfg->flags & PT_FLAG_NO_PDL) && !getenv("PTB200_NO_PDL");
         ctx->knobPdlAlways = getenv("PTB200_PDL_ALWAYS") != nullptr;
         ctx->knobNoMix = getenv("PTB200_NO_MIX") != nullptr;
+        if (const char* e = getenv("PTB200_SPLIT")) {                                     // developer knob
+            unsigned a = 1, b = 32, c = 1, d = 0;
+            sscanf(e, "%u,%u,%u,%u", &a, &b, &c, &d);
+            ctx->split = std::max(1u, std::min((unsigned)PT_MAX_SETS, a)); ctx->splitWidth = std::max(1u, std::min(32u, b)); ctx->splitTail = c != 0; ctx->splitHold = d != 0;
+        }
         ctx->anyFarFirst = getenv("PTB200_ANY_FAR_FIRST") ? (uint32_t)atoi(getenv("PTB200_ANY_FAR_FIRST")) : 0u;                   // developer knob
         // a whole 1080p image: the head (primary rays + first extend, ~0.3 ms) needs the launches of bounce >= 2 to hide under; on a
         // shard it is short and only disturbs the latency-bound launches, so it waits for the tail (profiles/r2/ab_r2i_ab.log)
@@ -852,16 +862,32 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
     const uint32_t nbins = 8u << (3 * ctx->sortBits);
     ctx->sc.sortBits = ctx->sortBits;
     for (uint32_t sample = 0; sample < nsamples; sample++) {
-        pt_ctx::SampleSet& S = ctx->set[pipelined ? ctx->cur : 0];
-        pt_ctx::SampleSet& other = ctx->set[pipelined ? (ctx->cur + ctx->nSets - 1) % ctx->nSets : 0];     // the previous sample's set
-        cudaStream_t s = pipelined ? S.stream : ctx->stream;
-        ctx->lastSet = pipelined ? ctx->cur : -1;
-        if (pipelined) ctx->cur = (ctx->cur + 1) % ctx->nSets;
         const bool training = !should_clear && ctx->HCACHE && ctx->sampleIdx < ctx->cfg.guiding_frames && ctx->sc.num_triangles;   // :292 (a rank without pixels still takes part in the exchange)
+        // A cache-training frame cannot overlap its neighbours (each reads the cache the one before it wrote), so it overlaps
+        // ITSELF: its tiles run as `parts` independent wavefront chains on the working sets' streams, each chain's short launches
+        // and drain phases filled by the others; the chains meet at the cache update.  Paths of one frame never read each other's
+        // results (additions are atomics applied by the propagate step), so per-pixel results are the unsplit frame's.
+        const uint32_t parts = (pipelined && training && ctx->split > 1u) ? std::min(std::min(ctx->split, (uint32_t)ctx->nSets), std::max(1u, (uint32_t)ctx->map.nLocalTiles)) : 1u;
+        const bool splitNow = parts > 1u;
+        const int firstSet = pipelined ? ctx->cur : 0;
+        pt_ctx::SampleSet& other = ctx->set[pipelined ? (ctx->cur + ctx->nSets - 1) % ctx->nSets : 0];     // the previous sample's (last) set
+        if (pipelined) ctx->cur = (ctx->cur + (int)parts) % ctx->nSets;
+        ctx->lastSet = pipelined ? (firstSet + (int)parts - 1) % ctx->nSets : -1;
+        const uint32_t randIdx0 = ctx->randIdx;
+      for (uint32_t part = 0; part < parts; part++) {
+        pt_ctx::SampleSet& S = ctx->set[pipelined ? (firstSet + (int)part) % ctx->nSets : 0];
+        cudaStream_t s = pipelined ? S.stream : ctx->stream;
+        const bool lastPart = part + 1 == parts;
+        TileMap map = ctx->map;                                                            // this part's tile range
+        const uint32_t tile0 = (uint32_t)((uint64_t)map.nLocalTiles * part / parts), tile1 = (uint32_t)((uint64_t)map.nLocalTiles * (part + 1) / parts);
+        map.slotBase = tile0 * 1024u;
+        const uint32_t partSlots = (tile1 - tile0) * 1024u;
+        ctx->randIdx = randIdx0;                                                           // every part draws the frame's numbers
         // Short queues: a sample that runs alone (clearing / profiled / cache-training frames) spreads its rays over all
         // warps (latency); samples that overlap others keep their warps full (throughput: 0.41 -> 0.32 ms/sample on a
         // 1/8-image shard), the other samples in flight fill the machine.
         ctx->sc.minWidth = (pipelined && !training && !ctx->prevTraining) ? 32u : 1u;
+        if (splitNow) ctx->sc.minWidth = ctx->splitWidth;
         if (ctx->knobMinWidth) ctx->sc.minWidth = ctx->knobMinWidth;
         ctx->sc.tailPair = (ctx->sc.minWidth < 32u && !ctx->knobNoTailPair) ? ctx->tailPairMax : 0u;     // latency mode only: a sample that runs alone
         ctx->sc.coop = ctx->sc.minWidth < 32u ? ctx->coop : 0u;                            // likewise: overlapped samples fill short launches with each other's rays
@@ -871,15 +897,16 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         // A sample that cannot overlap the previous one's shading (cache training) holds its cache-independent head (primary
         // rays + first extend) back until the previous sample reaches its tail, whose low occupancy it then fills, instead
         // of competing with the previous sample's wide launches.
-        if (pipelined && (training || ctx->prevTraining) && other.tailValid && !ctx->knobNoTailWait) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
+        if (pipelined && (training || ctx->prevTraining) && other.tailValid && !ctx->knobNoTailWait && (!splitNow || ctx->splitHold)) CK(cudaStreamWaitEvent(s, other.tailStart, 0));
         const bool overlapped = pipelined && !training && !ctx->prevTraining;
+        const bool crowded = overlapped || splitNow;                                       // other launches of this or other samples are in flight: schedule for throughput
         // Programmatic dependent launch pays where a sample runs alone (its launch chain is the critical path: measured 1-2 % per
         // training frame).  Among overlapped samples an early-scheduled successor holds SM slots the other samples' kernels
         // could use (measured: steady state 4 % slower at 1080p, 18 % on a 1/8 shard), so those launch in plain stream order.
-        ctx->pdlNow = ctx->pdl && (!overlapped || ctx->knobPdlAlways);
+        ctx->pdlNow = ctx->pdl && (!crowded || ctx->knobPdlAlways);
         const bool sorting = ctx->sortOn && !ctx->counting;
         CK(cudaMemsetAsync(S.q.cnt, 0, (CNT_TOTAL + (sorting ? (size_t)ctx->sortBounces * 2 * nbins : 0)) * sizeof(uint), s));   // :265 (+ cursors, + sort histograms)
-        if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); launchK(ctx, k_primary, dim3(map.nSlots / 256), dim3(256), s, dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
+        if (partSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s); launchK(ctx, k_primary, dim3(partSlots / 256), dim3(256), s, dcam, map, ctx->randIdx, S.q, S.masks, S.accucolors); }   // :258,:266
         ctx->randIdx++;                                                                    // :267
         uint32_t max_bounces;                                                              // :270-274 (host _NEE == HNEE)
         if (ctx->HNEE) max_bounces = should_clear ? ctx->cfg.interactive_depth : ctx->cfg.max_ray_depth;
@@ -901,7 +928,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
                 ctx->fbTail = tailFrom; ctx->fbSeen = seq;
             }
         }
-        const uint32_t waveBounces = ctx->counting ? max_bounces : std::min(max_bounces, (overlapped && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : tailFrom);
+        const uint32_t waveBounces = ctx->counting ? max_bounces : std::min(max_bounces, (((overlapped || (splitNow && !ctx->splitTail))) && !ctx->tailForced) ? (uint32_t)PT_MAX_BOUNCES : tailFrom);
         const bool connects = (ctx->HNEE && deviceNEE) || skyNEE;                          // :286 (no shadow rays exist when the device _NEE is false)
         const bool fuse = connects && !ctx->prof && !ctx->counting;                        // connect(b) rides in the launch of extend(b+1)
         // ray sorting: shade(b) bins the rays it pushes, the two small kernels after it turn the bins into fetch permutations
@@ -939,7 +966,7 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         auto releaseHead = [&]() -> int { if (pipelined && !S.tailValid) { CK(cudaEventRecord(S.tailStart, s)); S.tailValid = true; } return PT_OK; };
         for (uint32_t bounce = 0; bounce < waveBounces; bounce++) {                        // :276-290
             const int buf = bounce & 1;
-            if (bounce == ctx->headAt && !overlapped) { int hr = releaseHead(); if (hr) return hr; }
+            if (bounce == ctx->headAt && !overlapped && lastPart) { int hr = releaseHead(); if (hr) return hr; }
             const uint* extPerm = (bounce > 0 && sortsExt(bounce - 1)) ? S.sortPerm[0] : nullptr;
             if (fuse && bounce > 0 && ctx->sc.mixPair) {
                 StageTimer tm(ctx, PT_STAGE_EXTEND, s);
@@ -984,15 +1011,22 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
         if (pipelined && other.doneValid) CK(cudaStreamWaitEvent(s, other.done, 0));
         auto accumulate = [&]() -> int {
             if (ctx->copyPending && pipelined) CK(cudaStreamWaitEvent(s, ctx->imgFree, 0));    // a read-back in flight still reads the image
-            if (map.nSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
-                              launchK(ctx, k_accumulate, dim3(map.nSlots / 256), dim3(256), s, map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces,
-                                      (ctx->fbOn && !overlapped && !should_clear && max_bounces == ctx->cfg.max_ray_depth) ? ctx->fbDev : nullptr); }   // :299
+            if (partSlots) { StageTimer tm(ctx, PT_STAGE_OTHER, s);
+                              launchK(ctx, k_accumulate, dim3(partSlots / 256), dim3(256), s, map, S.accucolors, S.albedoSample, ctx->image, ctx->albedo, S.q.cnt, ctx->stats, max_bounces, waveBounces,
+                                      (ctx->fbOn && !overlapped && !should_clear && part == 0 && max_bounces == ctx->cfg.max_ray_depth) ? ctx->fbDev : nullptr); }   // :299
             return PT_OK;
         };
         bool accumulated = false;
         if (training) {                                                                    // :292-296
             StageTimer tm(ctx, PT_STAGE_GUIDING, s);
-            if (map.nSlots) launchK(ctx, k_rc_update, dim3(map.nSlots / 256), dim3(256), s, map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            if (partSlots) launchK(ctx, k_rc_update, dim3(partSlots / 256), dim3(256), s, map, S.accucolors, S.sampleCache, ctx->sc.rcAdditions, ctx->sc.num_triangles);
+            if (splitNow && !lastPart) {                                                   // the last part's stream collects the others and runs the exchange
+                CK(cudaEventRecord(S.partDone, s));
+                int ar = accumulate(); if (ar) return ar;
+                CK(cudaEventRecord(S.done, s)); S.doneValid = true;
+                continue;
+            }
+            if (splitNow) for (uint32_t p = 0; p + 1 < parts; p++) CK(cudaStreamWaitEvent(s, ctx->set[(firstSet + (int)p) % ctx->nSets].partDone, 0));
             if (ctx->peer.on) {
                 // reduce + propagate + broadcast over peer memory (pt_kernels.cuh): the owner of a triangle range sums every
                 // rank's additions out of their HBM, propagates once and stores the result into every rank's cache
@@ -1012,7 +1046,9 @@ PT_API int pt_render(pt_ctx* ctx, const pt_camera* cam, int should_clear) {
             }
         }
         if (!accumulated) { int ar = accumulate(); if (ar) return ar; }
+        if (splitNow) for (uint32_t p = 0; p + 1 < parts; p++) CK(cudaStreamWaitEvent(s, ctx->set[(firstSet + (int)p) % ctx->nSets].done, 0));   // their image updates
         if (pipelined) { CK(cudaEventRecord(S.done, s)); S.doneValid = true; }
+      }   // parts
         ctx->prevTraining = training;
         ctx->sampleIdx++;                                                                  // :300
     }

@@ -79,7 +79,7 @@ __device__ __forceinline__ float rnd(RandState& rs) {          // device branch 
 // ---- pixel <-> slot mapping (tile partition) ---------------------------------------
 // The image is cut into 32x32 tiles (row-major tile id t); rank r of `world` owns tiles with
 // t % world == r.  A local slot is (local tile, 8x4 block, lane): one warp = one 8x4 pixel block.
-struct TileMap { uint W, H, tilesX, tilesY, rank, world, nLocalTiles, nSlots; };
+struct TileMap { uint W, H, tilesX, tilesY, rank, world, nLocalTiles, nSlots, slotBase; };   // slotBase: first slot of a launch that covers a range of this rank's tiles (split frames)
 __host__ __device__ __forceinline__ bool slotToPixel(const TileMap& m, uint slot, uint& x, uint& y) {
     uint lt = slot >> 10, j = slot & 1023u;
     uint gt = lt * m.world + m.rank;

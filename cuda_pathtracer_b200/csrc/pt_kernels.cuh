@@ -82,7 +82,7 @@ __device__ __forceinline__ void camGetRay(const DCamera& c, uint x, uint y, uint
 }
 
 __global__ void __launch_bounds__(256) k_primary(DCamera cam, TileMap map, uint randIdx, Queues q, float4* masks, float4* accucolors) {
-    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;      // grid covers nSlots exactly (multiple of 1024)
+    const uint slot = map.slotBase + blockIdx.x * blockDim.x + threadIdx.x;      // grid covers whole tiles (multiples of 1024 slots)
     uint x, y;
     const bool valid = slotToPixel(map, slot, x, y);
     float3 o = f3(0), d = f3(0);
@@ -543,7 +543,7 @@ __global__ void __launch_bounds__(128, PT_TAIL_MINBLOCKS) k_tail(ShadeParams P, 
 __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* __restrict__ accucolors, const float4* __restrict__ albedoSample,
                                                     float4* image, float4* albedo, const uint* __restrict__ cnt, unsigned long long* stats, uint maxBounces, uint waveBounces,
                                                     volatile uint* feedback) {
-    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint slot = map.slotBase + blockIdx.x * blockDim.x + threadIdx.x;
     uint x, y;
     pdlWait(); pdlLaunch();
     if (slotToPixel(map, slot, x, y)) {
@@ -557,7 +557,7 @@ __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* _
             albedo[pix] = make_float4(fmaxf(0.0f, a.x) + nv.x, fmaxf(0.0f, a.y) + nv.y, fmaxf(0.0f, a.z) + nv.z, a.w + 1.0f);
         }
     }
-    if (slot == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {           // one thread per launch; launches of one sample's tile ranges run concurrently: atomics
         unsigned long long ext = 0, sh = 0;
         unsigned long long wext = 0, wsh = 0;
         for (uint b = 0; b < maxBounces; b++) {
@@ -569,7 +569,9 @@ __global__ void __launch_bounds__(256) k_accumulate(TileMap map, const float4* _
             __threadfence_system();
             feedback[0] = feedback[0] + 1u;
         }
-        stats[0] += cnt[CNT_EXT(0)]; stats[1] += ext; stats[2] += sh; stats[3] += ext; stats[4] += 1; stats[5] += wext; stats[6] += wsh;
+        atomicAdd(stats + 0, (unsigned long long)cnt[CNT_EXT(0)]); atomicAdd(stats + 1, ext); atomicAdd(stats + 2, sh); atomicAdd(stats + 3, ext);
+        if (map.slotBase == 0u) atomicAdd(stats + 4, 1ull);
+        atomicAdd(stats + 5, wext); atomicAdd(stats + 6, wsh);
     }
 }
 // this rank's pixels in slot order (the tile partition): what a rank ships to the host / to rank 0
@@ -700,7 +702,7 @@ __global__ void k_rc_init(float4* rc, float* add, uint T) {                     
 }
 __global__ void __launch_bounds__(256) k_rc_update(TileMap map, const float4* __restrict__ accucolors,
                                                    const pt_sample_cache* __restrict__ sampleCache, float* add, uint T) {   // kernels.h:863-882
-    const uint slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint slot = map.slotBase + blockIdx.x * blockDim.x + threadIdx.x;
     uint x, y;
     pdlWait(); pdlLaunch();
     if (!slotToPixel(map, slot, x, y)) return;
