@@ -380,6 +380,100 @@ __device__ __forceinline__ bool tlasTrip(const DScene& sc, LaneState& L, TravSta
 // instance the lowest reference triangle id wins, which makes the result independent of visit order.
 __device__ __forceinline__ bool hasBlasWork(const LaneState& L) { return L.ray != PT_NONE && (L.tgroup.y | (L.ngroup.y & 0xFF000000u)) != 0u; }
 
+// ---- bottom-level phase with a warp-wide triangle queue (build knob PT_TRI_QUEUE) --------------------------------------------
+// In blasTrip a lane tests its own triangles right after the node step that found them: on incoherent rays 4-5 of 32 lanes run
+// the Moeller-Trumbore section, which then takes a third of the warp's issue slots.  Here the lanes only PUSH (owner lane,
+// triangle) pairs into a per-warp queue in shared memory and go on with node steps; once 32 pairs are waiting the whole warp
+// tests one pair per lane (the owner's model-space ray comes over with six shuffles) and merges the hits into the owner's slot
+// with a 64-bit atomicMin on (t bits, triangle id).  That key order IS the selection rule of triStep: smallest t, lowest id among
+// equal t inside an instance; the slot starts at (tbest, 0) when the ray has no hit in this instance yet, so a tie with a hit
+// of an earlier instance loses exactly as the strict < does.  Same hits, different schedule.  The queue is drained before the
+// phase ends, so no pair outlives the instance its ray was in.
+#if defined(PT_TRI_QUEUE)
+#ifndef PT_TQ_PUSH
+#define PT_TQ_PUSH 3                                   /* pairs a lane pushes per trip; the rest of its triangle group waits */
+#endif
+#ifndef PT_TQ_MIN
+#define PT_TQ_MIN 32                                   /* a test round starts once this many pairs are waiting */
+#endif
+#define PT_TQ_CAP (32 + 32 * PT_TQ_PUSH)
+struct TriQueue {
+    uint* q; unsigned long long* best; uint n;
+    __device__ __forceinline__ void init() {
+        __shared__ uint qs[4][PT_TQ_CAP];
+        __shared__ unsigned long long bs[4][32];
+        const uint w = (threadIdx.x >> 5) & 3u;
+        q = qs[w]; best = bs[w]; n = 0;
+    }
+};
+__device__ __forceinline__ unsigned long long hitKey(const LaneState& L) {
+    return ((unsigned long long)__float_as_uint(L.tbest) << 32) | (L.found ? L.hitId : 0u);
+}
+// one test round: up to 32 queued pairs, one per lane.  All 32 lanes must call it.
+template <class TALLY>
+__device__ __forceinline__ void triQueueRound(const DScene& sc, const LaneState& L, TriQueue& Q, const uint lane, TALLY& tally) {
+    __syncwarp();
+    const uint take = min(Q.n, 32u);
+    Q.n -= take;
+    const bool valid = lane < take;
+    const uint e = valid ? Q.q[Q.n + lane] : (lane << 27);
+    const uint owner = e >> 27;
+    const float ox = __shfl_sync(0xffffffffu, L.o.x, owner), oy = __shfl_sync(0xffffffffu, L.o.y, owner), oz = __shfl_sync(0xffffffffu, L.o.z, owner);
+    const float dx = __shfl_sync(0xffffffffu, L.d.x, owner), dy = __shfl_sync(0xffffffffu, L.d.y, owner), dz = __shfl_sync(0xffffffffu, L.d.z, owner);
+    if (valid) {
+        tally.tri();
+        const float4* tp = sc.wtris + (size_t)(e & 0x07FFFFFFu) * 3;
+        const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+        float t, u, v;
+        if (triIntersect(f3(ox, oy, oz), f3(dx, dy, dz), f3(a), f3(b), f3(c), t, u, v))
+            atomicMin(Q.best + owner, ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(a.w));
+    }
+    __syncwarp();
+}
+// The owner takes over what the rounds found for it.  Returns true when an any-hit ray is finished (occluded).
+__device__ __forceinline__ bool triQueueRefresh(LaneState& L, const TriQueue& Q, const uint lane, const bool any) {
+    if (L.ray == PT_NONE || !L.inBLAS) return false;
+    const unsigned long long k = Q.best[lane];
+    if (k == hitKey(L)) return false;
+    L.tbest = __uint_as_float((uint)(k >> 32)); L.hitId = (uint)k; L.hitInst = L.curInst; L.hitType = 0; L.found = true;
+    L.tcull = L.tbest * 1.000001f;
+    if (any) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
+    return false;
+}
+template <class Finish, class TALLY>
+__device__ __forceinline__ void blasPhaseQueued(const DScene& sc, LaneState& L, TravStack& stack, TriQueue& Q, const uint lane, const bool any, const Finish& finish, TALLY& tally) {
+    if (__ballot_sync(0xffffffffu, hasBlasWork(L)) == 0u) return;
+    if (L.ray != PT_NONE && L.inBLAS) Q.best[lane] = hitKey(L);
+    const uint below = (1u << lane) - 1u;
+    while (true) {
+        const bool work = hasBlasWork(L);
+        if (__ballot_sync(0xffffffffu, work) == 0u) {
+            if (Q.n == 0u) break;
+            while (Q.n > 0u) triQueueRound(sc, L, Q, lane, tally);
+            if (triQueueRefresh(L, Q, lane, any)) { tally.end(); finish(); }
+            break;
+        }
+        if (work && L.tgroup.y == 0u) { blasNodeStep(sc, L, stack); tally.node(); }
+        const uint c = work ? min((uint)__popc(L.tgroup.y), (uint)PT_TQ_PUSH) : 0u;
+#pragma unroll
+        for (uint k = 0; k < PT_TQ_PUSH; k++) {
+            const uint m = __ballot_sync(0xffffffffu, c > k);
+            if (c > k) {
+                const uint ti = 31u - __clz(L.tgroup.y);
+                L.tgroup.y &= ~(1u << ti);
+                Q.q[Q.n + __popc(m & below)] = (lane << 27) | (L.tgroup.x + ti);
+            }
+            Q.n += __popc(m);
+        }
+        if (work && L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack.pop(L.sp);
+        if (Q.n >= (uint)PT_TQ_MIN) {
+            do triQueueRound(sc, L, Q, lane, tally); while (Q.n >= 32u);
+            if (triQueueRefresh(L, Q, lane, any)) { tally.end(); finish(); }
+        }
+    }
+}
+#endif
+
 template <bool ANY, class IO, class TALLY>
 __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* cursor, const IO io, TALLY& tally) {
     const uint lane = laneId();
@@ -390,6 +484,9 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
     LaneState L;
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     bool exhausted = n == 0;
+#if defined(PT_TRI_QUEUE)
+    TriQueue triQ; triQ.init();
+#endif
 #if defined(PT_QUEUE_BULK)
     // Build knob (A/B for the north star's "ray buffers staged through shared memory or TMA"): a warp's fetch window -- up to 32
     // consecutive queue entries, 16 B each in the two streams -- is brought into shared memory by two bulk copies
@@ -457,6 +554,10 @@ __device__ __forceinline__ void traceLoop(const DScene& sc, const uint n, uint* 
             if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { io.load(ray, o4, d4); }, tally)) { tally.end(); io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }
         }
         // ---- B: bottom level ----
+#if defined(PT_TRI_QUEUE)
+        blasPhaseQueued(sc, L, stack, triQ, lane, ANY, [&]() { io.template store<ANY>(L.ray, L); L.ray = PT_NONE; }, tally);
+        continue;
+#endif
         const uint nB = __popc(__ballot_sync(0xffffffffu, hasBlasWork(L)));
         const uint minKeep = max(1u, (nB * PT_KEEP_NUM + PT_KEEP_DEN - 1u) / PT_KEEP_DEN);
         while (true) {
@@ -602,6 +703,9 @@ __device__ __forceinline__ void traceLoopMixed(const DScene& sc, const uint nE, 
     L.ray = PT_NONE; L.ngroup = make_uint2(0u, 0u); L.tgroup = make_uint2(0u, 0u); L.curT = PT_NONE; L.sp = 0; L.spBase = 0; L.inBLAS = false;
     bool any = false;
     bool exhausted = n == 0;
+#if defined(PT_TRI_QUEUE)
+    TriQueue triQ; triQ.init();
+#endif
     auto finish = [&]() { if (any) ioS.template store<true>(L.ray, L); else ioE.template store<false>(L.ray, L); L.ray = PT_NONE; };
     while (true) {
         const uint activeMask = __ballot_sync(0xffffffffu, L.ray != PT_NONE);
@@ -624,6 +728,10 @@ __device__ __forceinline__ void traceLoopMixed(const DScene& sc, const uint nE, 
             const uint ray = L.ray;
             if (tlasTrip(sc, L, stack, [&](float4& o4, float4& d4) { if (any) ioS.load(ray, o4, d4); else ioE.load(ray, o4, d4); }, tally)) finish();
         }
+#if defined(PT_TRI_QUEUE)
+        blasPhaseQueued(sc, L, stack, triQ, lane, any, finish, tally);
+        continue;
+#endif
         while (true) {
             const bool work = hasBlasWork(L);
             if (__ballot_sync(0xffffffffu, work) == 0u) break;

@@ -56,6 +56,14 @@ def measure(world, env):
         best_s = min(best_s, all_s[-1])
     st = pt.stats()
     rays = (st.extend_rays + st.shadow_rays) / (5 * 64)
+    if os.environ.get("AB_TALLY"):            # work per ray as the counting kernels see it
+        pt.Finish(); pt.reset_stats(); pt.set_counting(True)
+        for i in range(4): pt.Render(cams[i % 16])
+        pt.Finish()
+        t, s2 = pt.tally(), pt.stats()
+        stages = dict(stages or {}, tally_per_extend_ray=[round(float(x) / max(1, s2.extend_rays), 3) for x in t["extend"]],
+                      tally_per_shadow_ray=[round(float(x) / max(1, s2.shadow_rays), 3) for x in t["connect"]])
+        pt.set_counting(False)
     pt.close()
     return best_t, best_s, rays, stages, all_s
 
