@@ -72,6 +72,7 @@ ALLREDUCE_HOOK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_vo
 
 
 FLAG_WAVEFRONT_ONLY, FLAG_NO_PIPELINE, FLAG_HOST_WIDE_BVH, FLAG_NO_PDL, FLAG_SORT_RAYS = 1, 2, 4, 8, 16      # PT_FLAG_* (include/ptb200.h)
+HOST_RING_HEADER_BYTES = 4096          # PT_HOST_RING_HEADER_BYTES (include/ptb200.h)
 STATIC_TRACE_MAX_RAYS = 307200            # PT_STATIC_TRACE_MAX_RAYS (include/ptb200.h): the static scratch of pt_trace_static
 
 

@@ -88,6 +88,11 @@ def load_library():
     L.pt_debug_read_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
     L.pt_gather_image_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
     L.pt_trace_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+    L.pt_host_ring_attach.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]
+    L.pt_host_ring_detach.argtypes = [C.c_void_p]
+    L.pt_deliver_image_async.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+    L.pt_host_ring_wait.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(C.c_float))]
+    L.pt_host_ring_release.argtypes = [C.c_void_p, C.c_uint64]
     L.pt_debug_trace_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.POINTER(C.c_float), C.c_void_p]
     _LIB = L
     return L
@@ -225,6 +230,32 @@ class Pathtracer:
         t = C.c_uint64()
         self._ck(self.L.pt_gather_image_async(self.h, abi.ptr(out) if out is not None else None, int(which), C.byref(t)), "pt_gather_image_async")
         return t.value
+
+    # -- one framebuffer in shared host memory, every rank through its own PCIe link (pt_host_ring_*) --
+    def host_ring_attach(self, block, slots):
+        """block: writable uint8 buffer over process-shared host memory (distributed.HostRing creates one per job),
+        abi.HOST_RING_HEADER_BYTES + slots * H * W * 16 bytes, zero-filled by its creator."""
+        self._ring_block = block                       # keep the mapping alive while the GPU writes into it
+        self._ck(self.L.pt_host_ring_attach(self.h, abi.ptr(block), block.nbytes, int(slots)), "pt_host_ring_attach")
+
+    def host_ring_detach(self):
+        self._ck(self.L.pt_host_ring_detach(self.h), "pt_host_ring_detach")
+        self._ring_block = None
+
+    def deliver_image_async(self, which=0):
+        """Every rank: this rank's tiles of the accumulated image into the ring slot of the next epoch; returns the epoch."""
+        e = C.c_uint64()
+        self._ck(self.L.pt_deliver_image_async(self.h, int(which), C.byref(e)), "pt_deliver_image_async")
+        return e.value
+
+    def host_ring_wait(self, epoch):
+        """Consumer: the (H, W, 4) framebuffer of `epoch` as a view into the shared block, once all ranks have delivered."""
+        p = C.POINTER(C.c_float)()
+        self._ck(self.L.pt_host_ring_wait(self.h, int(epoch), C.byref(p)), "pt_host_ring_wait")
+        return np.ctypeslib.as_array(p, shape=(self.cfg.height, self.cfg.width, 4))
+
+    def host_ring_release(self, epoch):
+        self._ck(self.L.pt_host_ring_release(self.h, int(epoch)), "pt_host_ring_release")
 
     def set_guiding_frames(self, frames):
         """Frames during which the radiance cache trains (reference pathtracer.h:292 hard-codes 100)."""

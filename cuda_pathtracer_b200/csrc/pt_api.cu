@@ -7,6 +7,8 @@
 #include <cstring>
 #include <string>
 #include <mutex>
+#include <thread>
+#include <atomic>
 #include <vector>
 #include <utility>
 #include <chrono>
@@ -25,6 +27,7 @@ static thread_local std::string g_createError;
 #define PT_GATHER_ARRIVE 256        /* flag words (uint[16]) in the radiance-cache block header: rank r pushed its tiles of this epoch */
 #define PT_GATHER_CONSUMED 320      /* rank 0 has shipped epoch e to the host: the slot of e may be overwritten by e + PT_GATHER_RING */
 #define PT_GATHER_COUNTER 321
+#define PT_GATHER_BANDDONE 384      /* uint[16]: rank r has copied its band of epoch e from rank 0's slot to the host framebuffer */
 struct pt_ctx {
     pt_config cfg;
     std::string err;
@@ -100,6 +103,7 @@ struct pt_ctx {
     bool counting = false; unsigned long long* tally = nullptr;                            // pt_set_counting: [0..2] extend, [3..5] connect
     float *skyPdf = nullptr, *skyCdf = nullptr;                                           // pt_set_skydome builds them (pathtracer.h:85-122)
     // N-rank framebuffer gather (pt_gather_image_async): image ring on rank 0, flags in the radiance-cache block header
+    struct HostRing { unsigned char* host = nullptr; unsigned char* dev = nullptr; uint64_t bytes = 0; uint32_t slots = 0; uint64_t epoch = 0; } ring;   // pt_host_ring_attach
     unsigned char* gatherBlock = nullptr; size_t gatherBytes = 0; void* gatherOpened = nullptr; float4* gatherRoot = nullptr; uint32_t gatherEpoch = 0;
     // per-stage timing (pt_set_profiling): CUDA event pairs around every stage launch, resolved in pt_finish
     bool prof = false;
@@ -210,6 +214,7 @@ static void peerClose(pt_ctx* ctx) {
 }
 
 PT_API void pt_destroy(pt_ctx* ctx) {
+    if (ctx && ctx->ring.host) { cudaSetDevice(ctx->cfg.device); cudaDeviceSynchronize(); cudaHostUnregister(ctx->ring.host); ctx->ring.host = nullptr; }
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     for (auto& S : ctx->set) if (S.stream) cudaStreamSynchronize(S.stream);
@@ -1235,6 +1240,125 @@ PT_API int pt_gather_image_async(pt_ctx* ctx, float* host_full, int which, uint6
     if (ticket) *ticket = ctx->copyTickets;
     ctx->copyTickets++;
     ctx->copyPending = true;
+    return PT_OK;
+}
+// ---- N ranks, one framebuffer in host memory, every rank through its own PCIe link ----------------------------------------------
+// pt_gather_image_async assembles the image in rank 0's HBM and ships 16 B/pixel through ONE link (33 MB per 1080p image: ~0.7 ms,
+// more than an 8-rank frame takes to render).  Here the framebuffer lives in a block of process-shared host memory (a file in
+// /dev/shm mapped by every rank's process): header + `slots` images of W*H float4.  Every rank maps it into its GPU's address space
+// (cudaHostRegister) and stores its own tiles into slot epoch % slots with a kernel, then publishes the epoch in the header; whoever
+// consumes the frames (normally rank 0's process) waits until all ranks have published an epoch, reads the image in place and
+// releases it.  Header: uint32 arrived[rank] at byte 4*rank (rank < 64), uint32 consumed at byte 256; images from byte 4096.
+static volatile uint32_t* ringWord(pt_ctx* ctx, size_t byteOffset) { return reinterpret_cast<volatile uint32_t*>(ctx->ring.host + byteOffset); }
+PT_API int pt_host_ring_attach(pt_ctx* ctx, void* base, uint64_t bytes, uint32_t slots) {
+    if (!ctx || !base || slots == 0) return PT_ERR_INVALID;
+    if (ctx->ring.host) return fail(ctx, PT_ERR_INVALID, "pt_host_ring_attach: already attached");
+    if (ctx->cfg.world_size > 64) return fail(ctx, PT_ERR_INVALID, "pt_host_ring_attach: at most 64 ranks");
+    const uint64_t need = PT_HOST_RING_HEADER_BYTES + (uint64_t)slots * ctx->map.W * ctx->map.H * sizeof(float4);
+    if (bytes < need) return fail(ctx, PT_ERR_INVALID, "pt_host_ring_attach: block smaller than header + slots * width * height * 16");
+    CK(cudaSetDevice(ctx->cfg.device));
+    CK(cudaHostRegister(base, need, cudaHostRegisterPortable | cudaHostRegisterMapped));
+    void* dev = nullptr;
+    cudaError_t e = cudaHostGetDevicePointer(&dev, base, 0);
+    if (e != cudaSuccess) { cudaHostUnregister(base); CK(e); }
+    ctx->ring.host = (unsigned char*)base; ctx->ring.dev = (unsigned char*)dev; ctx->ring.bytes = need; ctx->ring.slots = slots;
+    ctx->ring.epoch = *ringWord(ctx, 4 * ctx->cfg.rank);                 // a block that was used before: carry on from its epoch
+    return PT_OK;
+}
+PT_API int pt_host_ring_detach(pt_ctx* ctx) {
+    if (!ctx) return PT_ERR_INVALID;
+    if (!ctx->ring.host) return PT_OK;
+    CK(cudaSetDevice(ctx->cfg.device));
+    { int jr = joinStreams(ctx); if (jr) return jr; }
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->copyStream) CK(cudaStreamSynchronize(ctx->copyStream));
+    CK(cudaHostUnregister(ctx->ring.host));
+    ctx->ring.host = nullptr; ctx->ring.dev = nullptr; ctx->ring.slots = 0;
+    return PT_OK;
+}
+// Every rank, after the same Render calls: this rank's tiles of the accumulated image go into the ring slot of the next epoch.
+// Asynchronous like pt_read_image_async.  The host waits (bounded) until the consumer has released the image that occupied the slot.
+PT_API int pt_deliver_image_async(pt_ctx* ctx, int which, uint64_t* epoch_out) {
+    if (!ctx) return PT_ERR_INVALID;
+    if (!ctx->ring.host) return fail(ctx, PT_ERR_INVALID, "pt_deliver_image_async: no host ring attached (pt_host_ring_attach)");
+    CK(cudaSetDevice(ctx->cfg.device));
+    const uint64_t epoch = ctx->ring.epoch + 1;
+    if (epoch > ctx->ring.slots) {                                         // flow control: slot reuse waits for the consumer
+        const double t0 = wallMs(), limit = (double)ctx->peer.timeoutNs * 1e-6;
+        while ((uint64_t)*ringWord(ctx, 256) + ctx->ring.slots < epoch) {
+            if (wallMs() - t0 > limit) return fail(ctx, PT_ERR_INVALID, "pt_deliver_image_async: the consumer did not release a ring slot in time");
+            std::this_thread::yield();
+        }
+    }
+    if (!ctx->copyStream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->copyReady, cudaEventDisableTiming));
+        for (auto& e : ctx->copyEv) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    if (ctx->forked && ctx->lastSet >= 0 && ctx->set[ctx->lastSet].doneValid) CK(cudaStreamWaitEvent(ctx->copyStream, ctx->set[ctx->lastSet].done, 0));
+    else { CK(cudaEventRecord(ctx->copyReady, ctx->stream)); CK(cudaStreamWaitEvent(ctx->copyStream, ctx->copyReady, 0)); }
+    const size_t npix = (size_t)ctx->map.W * ctx->map.H;
+    const float4* src = which == 0 ? ctx->image : ctx->albedo;
+    float4* hostSlot = reinterpret_cast<float4*>(ctx->ring.host + PT_HOST_RING_HEADER_BYTES) + (size_t)(epoch % ctx->ring.slots) * npix;
+    volatile uint* devArrived = reinterpret_cast<volatile uint*>(ctx->ring.dev);
+    if (ctx->cfg.world_size == 1) {
+        CK(cudaMemcpyAsync(hostSlot, src, npix * sizeof(float4), cudaMemcpyDeviceToHost, ctx->copyStream));
+        CK(cudaEventRecord(ctx->imgFree, ctx->copyStream));
+        k_publish_host<<<1, 1, 0, ctx->copyStream>>>(devArrived, 0u, (uint)epoch);
+    } else if (ctx->peer.on && ctx->gatherRoot) {
+        // assemble in rank 0's HBM ring (as pt_gather_image_async), then every rank ships one band of the assembled frame
+        const uint32_t ge = ++ctx->gatherEpoch;
+        float4* rootSlot = ctx->gatherRoot + (size_t)(ge % PT_GATHER_RING) * npix;
+        const PeerSet& ps = ctx->peer.ps;
+        k_gather_push<<<std::max(1u, ctx->map.nSlots / 256), 256, 0, ctx->copyStream>>>(ps, ctx->map, src, rootSlot, ge, PT_GATHER_RING,
+                                                                                      PT_GATHER_ARRIVE, PT_GATHER_CONSUMED, PT_GATHER_COUNTER, ctx->peer.timeoutNs);
+        CK(cudaEventRecord(ctx->imgFree, ctx->copyStream));
+        k_flags_wait<<<1, 32, 0, ctx->copyStream>>>(ps, 0u, PT_GATHER_ARRIVE, ge, ctx->peer.timeoutNs);
+        const uint32_t H = ctx->map.H, world = ctx->cfg.world_size, rank = ctx->cfg.rank;
+        const size_t row0 = (size_t)H * rank / world, row1 = (size_t)H * (rank + 1) / world;
+        if (row1 > row0) CK(cudaMemcpyAsync(hostSlot + row0 * ctx->map.W, rootSlot + row0 * ctx->map.W, (row1 - row0) * ctx->map.W * sizeof(float4), cudaMemcpyDefault, ctx->copyStream));
+        k_band_done<<<1, 1, 0, ctx->copyStream>>>(ps, PT_GATHER_BANDDONE, ge, devArrived, (uint)epoch);
+        if (rank == 0) {
+            k_flags_wait<<<1, 32, 0, ctx->copyStream>>>(ps, 0u, PT_GATHER_BANDDONE, ge, ctx->peer.timeoutNs);
+            k_gather_release<<<1, 32, 0, ctx->copyStream>>>(ps, ge, PT_GATHER_CONSUMED);
+        }
+    } else {
+        // no peer mapping: every rank stores its own tiles into the host image from a kernel (zero-copy stores, slower than a copy engine)
+        float4* slot = reinterpret_cast<float4*>(ctx->ring.dev + PT_HOST_RING_HEADER_BYTES) + (size_t)(epoch % ctx->ring.slots) * npix;
+        const uint32_t n = ctx->map.nSlots;
+        if (n) {
+            if (!ctx->packBuf) CK(cudaMalloc((void**)&ctx->packBuf, (size_t)n * sizeof(float4)));
+            k_pack_tiles<<<n / 256, 256, 0, ctx->copyStream>>>(ctx->map, src, ctx->packBuf);
+        }
+        CK(cudaEventRecord(ctx->imgFree, ctx->copyStream));                  // later samples may accumulate again; the PCIe stores read the copy
+        if (n) k_push_host<<<ctx->map.nLocalTiles, 256, 0, ctx->copyStream>>>(ctx->map, ctx->packBuf, slot);
+        k_publish_host<<<1, 1, 0, ctx->copyStream>>>(devArrived, ctx->cfg.rank, (uint)epoch);
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->copyEv[ctx->copyTickets & 7], ctx->copyStream));
+    ctx->copyTickets++;
+    ctx->copyPending = true;
+    ctx->ring.epoch = epoch;
+    if (epoch_out) *epoch_out = epoch;
+    return PT_OK;
+}
+// Consumer: blocks (bounded) until every rank has published `epoch`; *image = the W*H float4 framebuffer in the shared block.
+PT_API int pt_host_ring_wait(pt_ctx* ctx, uint64_t epoch, const float** image) {
+    if (!ctx || !ctx->ring.host || epoch == 0) return PT_ERR_INVALID;
+    const double t0 = wallMs(), limit = (double)ctx->peer.timeoutNs * 1e-6;
+    for (uint32_t r = 0; r < ctx->cfg.world_size; r++)
+        while ((uint64_t)*ringWord(ctx, 4 * r) < epoch) {
+            if (wallMs() - t0 > limit) return fail(ctx, PT_ERR_INVALID, "pt_host_ring_wait: a rank did not deliver its tiles in time");
+            std::this_thread::yield();
+        }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    if (image) *image = reinterpret_cast<const float*>(ctx->ring.host + PT_HOST_RING_HEADER_BYTES) + (size_t)(epoch % ctx->ring.slots) * ctx->map.W * ctx->map.H * 4;
+    return PT_OK;
+}
+PT_API int pt_host_ring_release(pt_ctx* ctx, uint64_t epoch) {
+    if (!ctx || !ctx->ring.host) return PT_ERR_INVALID;
+    std::atomic_thread_fence(std::memory_order_release);
+    *ringWord(ctx, 256) = (uint32_t)epoch;
     return PT_OK;
 }
 PT_API int pt_read_image_async(pt_ctx* ctx, float* host_rgbw, int which, uint64_t* ticket) { return readAsync(ctx, host_rgbw, which, false, ticket); }

@@ -920,6 +920,47 @@ __global__ void k_gather_wait(PeerSet ps, uint epoch, uint arriveWord, unsigned 
         }
     }
 }
+// N ranks, one framebuffer in HOST memory, every rank through its own PCIe link (pt_deliver_image_async).  `packed` holds this
+// rank's pixels in slot order (k_pack_tiles: the image itself is free again right after that copy).  One block per local tile;
+// a warp stores whole tile rows (32 pixels = 512 contiguous bytes) straight into the mapped, process-shared host image.  The
+// epoch is published by k_publish_host, a separate launch behind this one in the stream: a kernel boundary makes the stores
+// visible at system scope, so a consumer that sees the epoch sees the pixels, without a fence per block.
+__global__ void __launch_bounds__(256) k_push_host(TileMap map, const float4* __restrict__ packed, float4* hostImage) {
+    const uint lt = blockIdx.x, w = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint gt = lt * map.world + map.rank;
+    const uint ty = gt / map.tilesX, tx = gt - ty * map.tilesX;
+    const uint x = tx * 32u + lane;
+#pragma unroll
+    for (uint k = 0; k < 4u; k++) {
+        const uint py = w + 8u * k, y = ty * 32u + py;
+        const uint j = (((py >> 2) * 4u + (lane >> 3)) << 5) | ((py & 3u) << 3) | (lane & 7u);      // slot of pixel (lane, py) inside the tile (slotToPixel)
+        if (x < map.W && y < map.H) hostImage[(size_t)y * map.W + x] = packed[(size_t)lt * 1024u + j];
+    }
+}
+// Band delivery (pt_deliver_image_async with connected peers): the frame is assembled in rank 0's HBM ring as for the gather, then
+// every rank copies ONE contiguous band of it (rows [r H / N, (r+1) H / N)) to the shared host framebuffer with its own copy
+// engine -- NVLink in, its own PCIe link out.  k_flags_wait: all ranks' flags `word` on rank `onRank` have reached the epoch
+// (any rank may poll rank 0's header through the mapped block); k_band_done: this rank's band has landed -- tells rank 0 (which
+// hands the HBM slot back once all bands have left) and publishes the epoch in the host header.
+__global__ void k_flags_wait(PeerSet ps, uint onRank, uint word, uint epoch, unsigned long long timeoutNs) {
+    if (threadIdx.x < ps.world) {
+        uint* f = peerFlags(ps, onRank);
+        const unsigned long long t0 = globalTimerNs();
+        while ((int)(ldAcquireSys(f + word + threadIdx.x) - epoch) < 0) {
+            if (globalTimerNs() - t0 > timeoutNs) { atomicExch_system(peerFlags(ps, ps.rank) + PT_PEER_ERROR, 3000u + word + threadIdx.x); break; }
+            __nanosleep(64);
+        }
+    }
+}
+__global__ void k_band_done(PeerSet ps, uint word, uint epoch, volatile uint* hostArrived, uint hostEpoch) {
+    __threadfence_system();
+    stReleaseSys(peerFlags(ps, 0) + word + ps.rank, epoch);
+    hostArrived[ps.rank] = hostEpoch;
+}
+__global__ void k_publish_host(volatile uint* arrived, uint rank, uint epoch) {
+    __threadfence_system();
+    arrived[rank] = epoch;
+}
 __global__ void k_gather_release(PeerSet ps, uint epoch, uint consumedWord) {                                 // rank 0, after the copy to the host
     if (threadIdx.x < ps.world) stReleaseSys(peerFlags(ps, threadIdx.x) + consumedWord, epoch);
 }

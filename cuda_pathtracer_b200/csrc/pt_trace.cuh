@@ -118,11 +118,13 @@ struct TravStack {
     }
     __device__ __forceinline__ void push(int& sp, const uint2 v) { if (sp < PT_SMEM_STACK) sh[sp * 128] = v; else loc[sp - PT_SMEM_STACK] = v; sp++; }
     __device__ __forceinline__ uint2 pop(int& sp) { --sp; return sp < PT_SMEM_STACK ? sh[sp * 128] : loc[sp - PT_SMEM_STACK]; }
+    __device__ __forceinline__ uint2 peek(int sp) const { --sp; return sp < PT_SMEM_STACK ? sh[sp * 128] : loc[sp - PT_SMEM_STACK]; }
 #else
     uint2 loc[PT_STACK];
     __device__ __forceinline__ void init() {}
     __device__ __forceinline__ void push(int& sp, const uint2 v) { loc[sp++] = v; }
     __device__ __forceinline__ uint2 pop(int& sp) { return loc[--sp]; }
+    __device__ __forceinline__ uint2 peek(int sp) const { return loc[sp - 1]; }
 #endif
 };
 
@@ -639,9 +641,25 @@ __device__ __forceinline__ bool coopTriStep(const DScene& sc, LaneState& L, cons
     }
     return false;
 }
+// Build knob PT_COOP_PREFETCH: while the group tests the triangles a node step found, the node it will visit next (nearest
+// pending child, else the top of the stack) is already on its way into L1 -- in the cooperative form the chain of dependent
+// loads IS the launch time, and a step with triangles otherwise pays two of them (triangles, then the next node).
+__device__ __forceinline__ void coopPrefetchNext(const DScene& sc, const LaneState& L, const TravStack& stack, const uint sub) {
+    uint2 g = L.ngroup;
+    if (g.y <= 0x00FFFFFFu) { if (L.sp <= L.spBase) return; g = stack.peek(L.sp); }
+    const uint bit = 31u - __clz(g.y);
+    const uint rest = g.y & ~(1u << bit);
+    const uint slot = (bit - 24u) ^ L.octinv;
+    const uint rel = __popc(rest & ~(0xFFFFFFFFu << slot) & 0xFFu);
+    const float4* np = sc.nodes + (size_t)(g.x + rel) * 5;
+    if (sub < 2u) asm volatile("prefetch.global.L1 [%0];" ::"l"(np + sub * 4u));
+}
 template <class TALLY>
 __device__ __forceinline__ bool coopBlasTrip(const DScene& sc, LaneState& L, TravStack& stack, const bool ANY, const uint sub, const uint gmask, TALLY& tally) {
     if (L.tgroup.y == 0u) { coopNodeStep(sc, L, stack, sub, gmask); tally.node(); }
+#if defined(PT_COOP_PREFETCH)
+    if (L.tgroup.y != 0u) coopPrefetchNext(sc, L, stack, sub);
+#endif
     if (L.tgroup.y != 0u && coopTriStep(sc, L, ANY, sub, gmask, tally)) { L.sp = 0; L.tgroup.y = 0u; L.ngroup.y = 0u; return true; }
     if (L.tgroup.y == 0u && L.ngroup.y <= 0x00FFFFFFu && L.sp > L.spBase) L.ngroup = stack.pop(L.sp);
     return false;

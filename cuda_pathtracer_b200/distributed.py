@@ -6,8 +6,11 @@ connect_peers() -- the library's own fused reduce + propagate + broadcast kernel
 one box); make_allreduce_hook() -- an in-place SUM all-reduce through torch.distributed (NCCL on GPUs, gloo in the
 CPU tests) followed by the local propagate kernel."""
 import ctypes as C
+import os
 
 import numpy as np
+
+from . import abi
 
 
 class _DevBuf:
@@ -88,3 +91,57 @@ def gather_image(local_image, group=None):
     t = local_image if isinstance(local_image, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(local_image))
     dist.all_reduce(t, group=group)
     return t
+
+
+class HostRing:
+    """The process-shared host framebuffer ring of pt_host_ring_* for one job: rank 0 creates a file in /dev/shm (zero-filled:
+    header + `slots` images of H*W float4), every rank maps it and attaches it to its Pathtracer.  After that each rank's
+    deliver_image_async() writes its own tiles through its own PCIe link and the consumer (rank 0) reads whole frames in place.
+    Works without torch.distributed for a single rank."""
+
+    def __init__(self, pt, slots=4, group=None, name=None):
+        import mmap
+        self.pt, self.slots = pt, int(slots)
+        nbytes = abi.HOST_RING_HEADER_BYTES + self.slots * pt.cfg.height * pt.cfg.width * 16
+        world = pt.cfg.world_size
+        dist = None
+        if world > 1:
+            import torch.distributed as dist
+        self.owner = pt.cfg.rank == 0
+        names = [name or ("/dev/shm/ptb200_ring_%d_%d" % (os.getpid(), id(self) & 0xffff))]
+        if world > 1:
+            dist.broadcast_object_list(names, src=0, group=group)
+        self.path = names[0]
+        if self.owner:
+            with open(self.path, "wb") as f:
+                f.truncate(nbytes)                     # sparse file of zeros: header and images start at 0
+        if world > 1:
+            dist.barrier(group=group)
+        self._f = open(self.path, "r+b")
+        self._map = mmap.mmap(self._f.fileno(), nbytes)
+        self.block = np.frombuffer(self._map, dtype=np.uint8)
+        pt.host_ring_attach(self.block, self.slots)
+        if world > 1:
+            dist.barrier(group=group)
+        self._group, self._dist = group, dist
+
+    def close(self):
+        if self.pt is None:
+            return
+        if self._dist is not None:
+            self._dist.barrier(group=self._group)
+        self.pt.host_ring_detach()
+        self.block = None
+        try:
+            self._map.close()
+        except BufferError:                           # a consumer still holds a view: the mapping goes with the process
+            pass
+        self._f.close()
+        if self._dist is not None:
+            self._dist.barrier(group=self._group)
+        if self.owner:
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass
+        self.pt = None

@@ -235,6 +235,19 @@ PT_API int  pt_wait_read(pt_ctx*, uint64_t ticket);
  * over the connected peers.  Every rank's tiles travel over NVLink into an image ring in rank 0's HBM, rank 0 ships the
  * assembled W*H float4 image to host_full (pinned; ignored on other ranks) with one copy.  Asynchronous, tickets as above. */
 PT_API int  pt_gather_image_async(pt_ctx*, float* host_full, int which, uint64_t* ticket);
+/* N ranks, one framebuffer in HOST memory, every rank through its own PCIe link (the gather above funnels 16 B/pixel through rank
+ * 0's link).  The caller provides a block of process-shared host memory (e.g. a /dev/shm file mapped by every rank's process),
+ * zero-filled by its creator: PT_HOST_RING_HEADER_BYTES of header (uint32 arrived[rank] at byte 4*rank, uint32 consumed at byte
+ * 256) followed by `slots` images of width*height float4.  attach maps it into this rank's GPU (cudaHostRegister); deliver (every
+ * rank, collective in the sense that all ranks call it after the same Render calls) stores this rank's tiles into slot
+ * epoch % slots and publishes the epoch; wait (the consumer, any attached context) returns the assembled image once all ranks
+ * have published it; release hands the slot back.  deliver blocks (bounded) while the slot it needs is unreleased. */
+#define PT_HOST_RING_HEADER_BYTES 4096u
+PT_API int  pt_host_ring_attach(pt_ctx*, void* base, uint64_t bytes, uint32_t slots);
+PT_API int  pt_host_ring_detach(pt_ctx*);
+PT_API int  pt_deliver_image_async(pt_ctx*, int which, uint64_t* epoch);
+PT_API int  pt_host_ring_wait(pt_ctx*, uint64_t epoch, const float** image);
+PT_API int  pt_host_ring_release(pt_ctx*, uint64_t epoch);
 PT_API int  pt_write_pfm(pt_ctx*, const char* path, int which);        /* headless render-to-PFM (display value rgb / w, main.cpp:58-62) in place of the GLFW window */
 /* Display post-process (main.cpp:46-171,316-376: demodulated separable Gaussian, remodulate, gamma 2, vignette) as CUDA
  * kernels; host float4 in (or NULL, NULL = the context's accumulators), host float4 RGBA out. */

@@ -94,3 +94,49 @@ def test_two_ranks_peer_protocol(size):
     assert r["ok"], r
     assert r["guiding_off"]["bit_identical"]
     assert r["guiding_on_peer"]["caches_replicated_bitwise"] and r["guiding_on_peer"]["rel_rmse"] < 2e-2
+
+
+def test_host_ring_delivers_the_framebuffer_in_place():
+    """pt_host_ring_* with one rank: the frame a consumer finds in the shared host block is the accumulated image of exactly
+    the samples rendered before the deliver call (later samples keep rendering), through more epochs than the ring has slots.
+    N ranks writing into one block: tools/multi_gpu_check.py (host_ring_image_identical)."""
+    from cuda_pathtracer_b200.distributed import HostRing
+    W, H = 200, 120                                        # not a multiple of the 32-pixel tile: clipped tile rows
+    arrays = scenes.sibenik_scene().arrays()
+    cam = scenes.camera_sweep("sibenik", W, H, 16)[2]
+    cfg = abi.default_config(W, H, max_ray_depth=4, interactive_depth=1)
+    pt = api.Pathtracer(arrays, cfg).Init()
+    pt.HNEE, pt.HCACHE = True, False
+    ring = HostRing(pt, slots=3)
+    assert os.path.exists(ring.path)
+    pt.Render(cam, shouldClear=True)
+    snaps, epochs = [], []
+    for k in range(7):
+        pt.Render(cam)
+        epochs.append(pt.deliver_image_async())
+        pt.Render(cam)                                     # in flight behind the delivery: must not leak into it
+        if k >= 2:                                         # the consumer runs two frames behind, as bench.py's loop does
+            e = epochs[k - 2]
+            view = pt.host_ring_wait(e)
+            snaps.append(view.copy())
+            pt.host_ring_release(e)
+    for e in epochs[-2:]:
+        snaps.append(pt.host_ring_wait(e).copy()); pt.host_ring_release(e)
+    pt.Finish()
+    assert epochs == list(range(1, 8))
+    for k, s in enumerate(snaps):
+        assert np.all(s[..., 3] == 2.0 + 2 * k), "frame %d carries %s samples" % (k, np.unique(s[..., 3]))
+        assert np.isfinite(s).all()
+    # the same schedule with blocking read-backs gives the same pictures (guiding off: results do not depend on overlap)
+    pt.Render(cam, shouldClear=True)
+    for k in range(7):
+        pt.Render(cam); pt.Finish()
+        assert np.array_equal(pt.read_image(), snaps[k]), "frame %d" % k
+        pt.Render(cam)
+    pt.Finish()
+    path = ring.path
+    ring.close()
+    assert not os.path.exists(path)
+    with pytest.raises(api.PtError):
+        pt.deliver_image_async()                           # detached: an error code, not a fault
+    pt.close()

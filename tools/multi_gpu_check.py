@@ -13,7 +13,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 from cuda_pathtracer_b200 import abi, api, scenes
-from cuda_pathtracer_b200.distributed import make_allreduce_hook, connect_peers, disconnect_peers
+from cuda_pathtracer_b200.distributed import make_allreduce_hook, connect_peers, disconnect_peers, HostRing
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--same-gpu", action="store_true")
@@ -66,6 +66,16 @@ for guiding, frames, transport in ((False, 8, "hook"), (True, args.frames, "hook
                 t = pt.gather_image_async(host)
             pt.wait_read(t)
             gathered = host.copy() if r == 0 else None
+            # the same framebuffer through the shared host ring: every rank writes its tiles through its own PCIe link
+            hr = HostRing(pt, slots=3)
+            for k in range(7):                          # more epochs than slots: the consumer's release gates slot reuse
+                e = pt.deliver_image_async()
+                if r == 0:
+                    view = pt.host_ring_wait(e)
+                    delivered = view.copy()
+                    pt.host_ring_release(e)
+            gathered = (gathered, delivered) if r == 0 else None
+            hr.close()
         pt.Finish()
         img = pt.read_image().copy(); rc = pt.read_radiance_cache()["radianceCache"].copy()
         if multi and transport == "peer":
@@ -84,11 +94,12 @@ for guiding, frames, transport in ((False, 8, "hook"), (True, args.frames, "hook
             "frames": frames, "bit_identical": bool(np.array_equal(full, ref)), "rel_rmse": err,
             "samples_ok": bool(np.all(full[..., 3] == frames + 1)), "caches_replicated_bitwise": replicated,
             "cache_moved": bool(np.any(rc1 != 0.1)),
-            "gathered_image_identical": None if gathered is None else bool(np.array_equal(gathered, full)),
+            "gathered_image_identical": None if gathered is None else bool(np.array_equal(gathered[0], full)),
+            "host_ring_image_identical": None if gathered is None else bool(np.array_equal(gathered[1], full)),
             "cache_rel_rmse_vs_1rank": float(np.sqrt(np.mean((rcs[0] - rc1) ** 2)) / np.sqrt(np.mean(rc1 ** 2)))}
     dist.barrier()
 if rank == 0:
-    ok = out["guiding_off"]["bit_identical"] and out["guiding_on_peer"]["gathered_image_identical"] and all(out[k]["rel_rmse"] < 2e-2 and out[k]["samples_ok"] and out[k]["caches_replicated_bitwise"] and out[k]["cache_moved"]
+    ok = out["guiding_off"]["bit_identical"] and out["guiding_on_peer"]["gathered_image_identical"] and out["guiding_on_peer"]["host_ring_image_identical"] and all(out[k]["rel_rmse"] < 2e-2 and out[k]["samples_ok"] and out[k]["caches_replicated_bitwise"] and out[k]["cache_moved"]
                                                      for k in ("guiding_on_hook", "guiding_on_peer"))
     print(json.dumps({"world": world, "same_gpu": args.same_gpu, "ok": bool(ok), **out}))
 dist.destroy_process_group()

@@ -13,7 +13,7 @@ import json
 for f in ("gpurun_out/${TAG}_bench_n$N.json", "gpurun_out/${TAG}_bench200_n$N.json"):
     try:
         d = json.loads([l for l in open(f) if l.startswith("{")][-1])
-        print(f, "value %.0f e2e %.0f blocking %.0f training %.4f steady %.4f" % (d["value"], d["e2e"]["value"], d["e2e"]["blocking"]["value"], d["phases"]["training_ms_per_step"], d["phases"]["steady_ms_per_step"]), d["exchange_check"], d["e2e"]["image_complete"], d["value_windows"])
+        print(f, "value %.0f e2e %.0f blocking %.0f training %.4f steady %.4f" % (d["value"], d["e2e"]["value"], d["e2e"]["blocking"]["value"], d["phases"]["training_ms_per_step"], d["phases"]["steady_ms_per_step"]), d["exchange_check"], d["e2e"]["image_complete"], d["value_windows"], d["e2e"].get("delivery"))
     except Exception as e:
         print(f, "unreadable", e)
 P
