@@ -13,5 +13,21 @@ pt.Render(cam, shouldClear=True)
 for _ in range(6): pt.Render(cam)
 pt.Finish()
 img = pt.read_image(); post = pt.postprocess(True); tiles = pt.read_tiles()
+# round 2: cooperative traversal + mixed pair work list (a lone training frame on a small image), ray sorting, sky sampling,
+# the static-scratch trace entry, the host framebuffer ring (one rank), the counting kernels
+from cuda_pathtracer_b200.distributed import HostRing
+pt.set_skydome(np.ones((16, 32, 4), np.float32)); pt.set_ray_sorting(True, 3, 2); pt.set_sky_sampling(True)
+pt.HCACHE = True
+pt.Render(cam, shouldClear=True)
+for _ in range(4): pt.Render(cam)
+pt.set_ray_sorting(False)
+rays = pt.debug_primary_rays(cam, 0)
+h0, h1 = pt.debug_trace(rays, False), pt.trace_static(rays, False)
+assert np.array_equal(h0["primitive_id"], h1["primitive_id"])
+ring = HostRing(pt, slots=2)
+for _ in range(3):
+    pt.Render(cam); e = pt.deliver_image_async(); v = pt.host_ring_wait(e); assert np.isfinite(v).all(); pt.host_ring_release(e)
+ring.close()
+pt.set_counting(True); pt.Render(cam); pt.Finish(); print("tally", pt.tally()); pt.set_counting(False)
 print("ok", float(img[..., 3].min()), np.isfinite(img).all(), post.shape, tiles.shape, pt.stats().extend_rays)
 pt.close()
