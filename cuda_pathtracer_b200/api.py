@@ -93,6 +93,7 @@ def load_library():
     L.pt_deliver_image_async.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
     L.pt_host_ring_wait.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(C.c_float))]
     L.pt_host_ring_release.argtypes = [C.c_void_p, C.c_uint64]
+    L.pt_debug_check_report.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
     L.pt_debug_trace_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.POINTER(C.c_float), C.c_void_p]
     _LIB = L
     return L
@@ -447,3 +448,19 @@ def build_bvh(triangles, tri_offset=0, device=0):
     if r != 0:
         raise PtError("pt_build_bvh failed (%d): %s" % (r, (L.pt_build_bvh_last_error() or b"").decode()))
     return nodes[:used.value].copy(), order, ms.value, levels.value
+
+
+def bounds_checked_build():
+    """True when the loaded library was built with -DPT_BOUNDS_CHECK (pt_version says so)."""
+    return b"bounds-checked" in load_library().pt_version()
+
+
+def check_report():
+    """(failures, code, index, limit) of the bounds-checked build since the last call; None for other builds."""
+    if not bounds_checked_build():
+        return None
+    out = (C.c_uint32 * 4)()
+    r = load_library().pt_debug_check_report(None, out)
+    if r != 0:
+        raise PtError("pt_debug_check_report failed (%d)" % r)
+    return tuple(int(x) for x in out)

@@ -179,6 +179,18 @@ static int devUpload(pt_ctx* ctx, T** p, const T* host, size_t n, bool sceneOwne
 
 // Work enqueued by pt_render lives on the private streams of the sample sets.  joinStreams() orders everything
 // enqueued so far before whatever comes next on the context's public stream (pt_cuda_stream()).
+// Bounds-checked build: the extents the kernels compare their indices with (pt_device.cuh PT_IDX).
+static int setCheckLimits(pt_ctx* ctx, uint32_t numTlas, uint32_t numModels, uint32_t numMaterials) {
+#if defined(PT_BOUNDS_CHECK)
+    CheckLimits& l = ctx->sc.chk;
+    l.numNodes = ctx->numWideNodes; l.numWtris = ctx->numWideTris; l.numTlas = numTlas; l.numModels = numModels; l.numMaterials = numMaterials;
+    l.queueCap = std::max<uint32_t>(ctx->map.nSlots, 1024u); l.nSlots = std::max<uint32_t>(ctx->map.nSlots, 1024u); l.stack = PT_STACK;
+    if (getenv("PTB200_CHK_SHRINK")) l.numWtris = 1;          // positive control of the checks themselves (tests/test_zy_bounds_checked.py); a shrunk NODE extent would turn the substituted index 0 into an endless traversal
+#else
+    (void)ctx; (void)numTlas; (void)numModels; (void)numMaterials;
+#endif
+    return PT_OK;
+}
 static int joinStreams(pt_ctx* ctx) {
     if (ctx->copyPending) { CK(cudaStreamWaitEvent(ctx->stream, ctx->copyEv[(ctx->copyTickets - 1) & 7], 0)); ctx->copyPending = false; }
     if (!ctx->forked) return PT_OK;
@@ -192,7 +204,11 @@ static int joinStreams(pt_ctx* ctx) {
 
 extern "C" {
 
+#if defined(PT_BOUNDS_CHECK)
+PT_API const char* pt_version(void) { return "ptb200 0.1 (sm_100a, bounds-checked build)"; }
+#else
 PT_API const char* pt_version(void) { return "ptb200 0.1 (sm_100a)"; }
+#endif
 
 PT_API void pt_default_config(pt_config* c) {
     memset(c, 0, sizeof(*c));
@@ -559,6 +575,21 @@ PT_API int pt_set_toggles(pt_ctx* ctx, int nee, int guiding) {
     ctx->HNEE = nee != 0; ctx->HCACHE = guiding != 0;
     return PT_OK;
 }
+// out4: failures since the last report, code of the first one (PT_CHK_*), its index, its limit; a build without PT_BOUNDS_CHECK
+// answers PT_ERR_INVALID.  Synchronises the device.  The counters restart at zero.
+PT_API int pt_debug_check_report(pt_ctx* ctx, uint32_t* out4) {        // ctx may be NULL: the current device
+    if (!out4) return PT_ERR_INVALID;
+#if defined(PT_BOUNDS_CHECK)
+    if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PT_ERR_CUDA;
+    const uint32_t zero[4] = {0, 0, 0, 0};
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpyFromSymbol(out4, g_chkFail, 4 * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMemcpyToSymbol(g_chkFail, zero, sizeof(zero)) != cudaSuccess) return PT_ERR_CUDA;
+    return PT_OK;
+#else
+    if (ctx) ctx->err = "pt_debug_check_report: not a bounds-checked build (make variant DEFS=-DPT_BOUNDS_CHECK)";
+    return PT_ERR_INVALID;
+#endif
+}
 PT_API void* pt_cuda_stream(pt_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 PT_API int pt_join(pt_ctx* ctx) {
     if (!ctx) return PT_ERR_INVALID;
@@ -737,6 +768,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     sc.num_triangles = d->num_triangles; sc.num_instances = d->num_instances; sc.num_spheres = d->num_spheres;
     sc.num_planes = d->num_planes; sc.num_lights = (uint)lights.size();
     ctx->numInstancesCap = d->num_instances; ctx->numTlasCap = d->num_tlas_nodes; ctx->numModels = d->num_models;
+    { int cr = setCheckLimits(ctx, d->num_tlas_nodes, d->num_models, d->num_materials); if (cr) return cr; }
     {   // ray-sorting cells span the top-level root box and the spheres (planes are unbounded: origins outside are clamped)
         float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
         if (d->num_instances && d->num_tlas_nodes) {

@@ -90,6 +90,29 @@ __host__ __device__ __forceinline__ bool slotToPixel(const TileMap& m, uint slot
     return x < m.W && y < m.H;
 }
 
+// ---- bounds-checked build (make variant NAME=_chk DEFS=-DPT_BOUNDS_CHECK) ------------------------------------------------------
+// compute-sanitizer is closed on the GPU pool, so out-of-range indices are looked for with checks of our own: every index the
+// kernels form into the node / triangle / instance / material / queue / per-slot arrays and every traversal-stack push goes
+// through PT_IDX, which in this build compares it with the array's extent (DScene::chk, set by the host per context), records the first failure in
+// g_chkFail and substitutes index 0 so that the run goes on and the report can be read (pt_debug_check_report).  In the
+// default build PT_IDX(i, ...) is i.
+#if defined(PT_BOUNDS_CHECK)
+struct CheckLimits { uint numNodes, numWtris, numTlas, numModels, numMaterials, queueCap, nSlots, stack; };
+static __device__ unsigned int g_chkFail[4];        // [0] failures, [1] code of the first, [2] its index, [3] its limit
+__device__ __forceinline__ uint ptCheckedIndex(uint i, uint limit, uint code) {
+    if (i < limit) return i;
+    if (atomicAdd(&g_chkFail[0], 1u) == 0u) { g_chkFail[1] = code; g_chkFail[2] = i; g_chkFail[3] = limit; }
+    return 0u;
+}
+#define PT_IDX(i, limit, code) ptCheckedIndex((uint)(i), (uint)(limit), (uint)(code))
+#define PT_LIMS(scene, field) ((scene).chk.field)
+#else
+#define PT_IDX(i, limit, code) (i)
+#define PT_LIMS(scene, field) 0u
+#endif
+#define PT_LIM(field) PT_LIMS(sc, field)
+enum { PT_CHK_STACK = 1, PT_CHK_NODE, PT_CHK_WTRI, PT_CHK_TLAS, PT_CHK_INSTANCE, PT_CHK_MODEL, PT_CHK_QUEUE, PT_CHK_SLOT, PT_CHK_TRIANGLE, PT_CHK_MATERIAL, PT_CHK_CACHE, PT_CHK_LIGHT };
+
 // ---- device views ------------------------------------------------------------------------------------
 struct DModel { uint rootNode; uint triangleStart, nrTriangles, pad; };
 struct DScene {
@@ -116,6 +139,9 @@ struct DScene {
     uint coopTail;              // the same bound for k_tail (paths instead of rays)
     uint anyFarFirst;           // any-hit rays visit the children far end first (order only: same boolean)
     uint mixPair;               // scheduling: k_trace_pair treats its two queues as one work list (latency mode)
+#if defined(PT_BOUNDS_CHECK)
+    CheckLimits chk;            // extents for PT_IDX
+#endif
 };
 
 struct DCamera { float3 eye, viewDir, lt, u, v; float d, focalLength, aperture; };

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace(DScene sc, co
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
                                                const float4* __restrict__ lights, float4* accucolors, const uint* __restrict__ perm) {
     pdlWait(); pdlLaunch();
-    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = perm;
+    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = perm; io.limits(sc);
     NoTally tally;
     const uint n = *count;
     if (useCoop(sc, n)) traceLoopCoop<ANY>(sc, n, cursor, io, tally);
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_count(DScene 
                                                const uint* __restrict__ count, uint* cursor, float4* __restrict__ hits,
                                                const float4* __restrict__ lights, float4* accucolors, unsigned long long* tallyOut) {
     pdlWait(); pdlLaunch();
-    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = nullptr;
+    QueueIO io; io.rayO = rayO; io.rayD = rayD; io.hits = hits; io.lights = lights; io.accucolors = accucolors; io.perm = nullptr; io.limits(sc);
     Tally tally;
     traceLoop<ANY>(sc, *count, cursor, io, tally);
     tally.flush(tallyOut, tallyOut + (ANY ? 4 : 6));        // tally buffer: ext[0..2], conn[3..5], longest ext ray [6], longest shadow ray [7]
@@ -159,9 +159,9 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair(DScene s
                                                     const uint* __restrict__ extPerm, const uint* __restrict__ shPerm) {
     pdlWait(); pdlLaunch();
     NoTally tally;
-    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm;
+    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm; e.limits(sc);
     const uint ne = *extCount, ns = *shCount;
-    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
+    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm; c.limits(sc);
     if (useCoop(sc, ne + ns)) {
         traceLoopCoop<false>(sc, ne, extCursor, e, tally);
         traceLoopCoop<true>(sc, ns, shCursor, c, tally);
@@ -181,8 +181,8 @@ __global__ void __launch_bounds__(128, PT_TRACE_MINBLOCKS) k_trace_pair_mixed(DS
                                                     const uint* __restrict__ extPerm, const uint* __restrict__ shPerm) {
     pdlWait(); pdlLaunch();
     NoTally tally;
-    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm;
-    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm;
+    QueueIO e; e.rayO = rayO; e.rayD = rayD; e.hits = hits; e.lights = nullptr; e.accucolors = nullptr; e.perm = extPerm; e.limits(sc);
+    QueueIO c; c.rayO = shO; c.rayD = shD; c.hits = nullptr; c.lights = lights; c.accucolors = accucolors; c.perm = shPerm; c.limits(sc);
     const uint ne = *extCount, ns = *shCount;
     if (useCoop(sc, ne + ns)) traceLoopCoopMixed(sc, ne, ns, extCursor, e, c, tally);
     else traceLoopMixed(sc, ne, ns, extCursor, e, c, tally);
@@ -261,19 +261,21 @@ __global__ void __launch_bounds__(128, PT_SHADE_MINBLOCKS) k_shade(ShadeParams P
         ShadeOut so; so.pushExt = so.pushShadow = false;
         uint slot = 0;
         if (i < n) {
-            const float4 o4 = rayO[i], d4 = rayD[i], h4 = q.hits[i];
+            const float4 o4 = rayO[PT_IDX(i, PT_LIMS(P.sc, queueCap), PT_CHK_QUEUE)], d4 = rayD[PT_IDX(i, PT_LIMS(P.sc, queueCap), PT_CHK_QUEUE)], h4 = q.hits[PT_IDX(i, PT_LIMS(P.sc, queueCap), PT_CHK_QUEUE)];
             slot = __float_as_uint(d4.w);
             Hit h; h.type = __float_as_uint(h4.x); h.id = __float_as_uint(h4.y); h.inst = __float_as_uint(h4.z); h.t = h4.w;
             shadeOne(P, f3(o4), f3(d4), slot, h, so);
         }
-        const uint si = blockAppend(so.pushShadow, q.cnt + CNT_SHADOW(P.bounce), sm);
+        uint si = blockAppend(so.pushShadow, q.cnt + CNT_SHADOW(P.bounce), sm);
         if (so.pushShadow) {
+            si = PT_IDX(si, PT_LIMS(P.sc, queueCap), PT_CHK_QUEUE);
             q.shO[si] = make_float4(so.shadow.o.x, so.shadow.o.y, so.shadow.o.z, so.shadow.len);
             q.shD[si] = make_float4(so.shadow.d.x, so.shadow.d.y, so.shadow.d.z, __uint_as_float(slot));
             if (P.sortKeys[1]) { const uint bin = sortBin(P.sc, so.shadow.o, so.shadow.d); P.sortKeys[1][si] = bin; atomicAdd(P.sortHist[1] + bin, 1u); }
         }
-        const uint ei = blockAppend(so.pushExt, q.cnt + CNT_EXT(P.bounce + 1), sm);
+        uint ei = blockAppend(so.pushExt, q.cnt + CNT_EXT(P.bounce + 1), sm);
         if (so.pushExt) {
+            ei = PT_IDX(ei, PT_LIMS(P.sc, queueCap), PT_CHK_QUEUE);
             outO[ei] = make_float4(so.ext.o.x, so.ext.o.y, so.ext.o.z, so.ext.len);
             outD[ei] = make_float4(so.ext.d.x, so.ext.d.y, so.ext.d.z, __uint_as_float(slot));
             if (P.sortKeys[0]) { const uint bin = sortBin(P.sc, so.ext.o, so.ext.d); P.sortKeys[0][ei] = bin; atomicAdd(P.sortHist[0] + bin, 1u); }
@@ -712,8 +714,9 @@ __global__ void __launch_bounds__(256) k_rc_update(TileMap map, const float4* __
         if (c.sample_type == 1) return;
         if (c.sample_type == 0) continue;
         const float energy = fminf(100.0f, luminance(totalEnergy / f3(c.cum_mask.x, c.cum_mask.y, c.cum_mask.z)));
-        atomicAdd(add + (size_t)c.cache_bucket_id * T + c.triangle_id, energy);          // RED.ADD.F32, no return value used
-        atomicAdd(add + (size_t)(8 + c.cache_bucket_id) * T + c.triangle_id, 1.0f);
+        const uint bk = PT_IDX(c.cache_bucket_id, 8u, PT_CHK_CACHE), tr = PT_IDX(c.triangle_id, T, PT_CHK_CACHE);
+        atomicAdd(add + (size_t)bk * T + tr, energy);          // RED.ADD.F32, no return value used
+        atomicAdd(add + (size_t)(8 + bk) * T + tr, 1.0f);
     }
 }
 __global__ void __launch_bounds__(256) k_rc_propagate(float4* rc, float* add, uint T) {                                   // kernels.h:884-905

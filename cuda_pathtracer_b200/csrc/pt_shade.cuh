@@ -166,8 +166,17 @@ struct ShadeOut { bool pushExt, pushShadow; ShadeRay ext, shadow; };
 
 // groupMask != 0: the call is made redundantly by the lanes named in it (k_tail_coop: 8 lanes share a path and compute identical
 // values); they are synchronised between the reads of the slot's state and its writes, and only `writer` lanes store.
-__device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3 rd, uint slot, const Hit hit, ShadeOut& out, const uint groupMask = 0u, const bool writer = true) {
+__device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3 rd, uint slot, const Hit hitIn, ShadeOut& out, const uint groupMask = 0u, const bool writer = true) {
     const DScene& sc = P.sc;
+    Hit hit = hitIn;
+#if defined(PT_BOUNDS_CHECK)
+    slot = PT_IDX(slot, PT_LIM(nSlots), PT_CHK_SLOT);
+    if (hit.id != 0xffffffffu) {
+        if (hit.type == 0) { hit.id = PT_IDX(hit.id, sc.num_triangles, PT_CHK_TRIANGLE); hit.inst = PT_IDX(hit.inst, sc.num_instances, PT_CHK_INSTANCE); }
+        else if (hit.type == 1) hit.id = PT_IDX(hit.id, sc.num_spheres, PT_CHK_TRIANGLE);
+        else hit.id = PT_IDX(hit.id, sc.num_planes, PT_CHK_TRIANGLE);
+    }
+#endif
     out.pushExt = out.pushShadow = false;
     uint x, y; slotToPixel(P.map, slot, x, y);
     TraceState state;
@@ -212,7 +221,7 @@ __device__ __forceinline__ void shadeOne(const ShadeParams& P, float3 ro, float3
             const pt_plane p = sc.planes[hit.id];
             material_id = p.material; originalNormal = f3(p.normal.x, p.normal.y, p.normal.z);
         }
-        const pt_material material = sc.materials[material_id];
+        const pt_material material = sc.materials[PT_IDX(material_id, PT_LIM(numMaterials), PT_CHK_MATERIAL)];
         const bool inside = dot(rd, originalNormal) > 0;
         const float3 surfaceNormal = inside ? -originalNormal : originalNormal;
         float3 colliderNormal = surfaceNormal;

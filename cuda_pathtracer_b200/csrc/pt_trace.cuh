@@ -122,7 +122,7 @@ struct TravStack {
 #else
     uint2 loc[PT_STACK];
     __device__ __forceinline__ void init() {}
-    __device__ __forceinline__ void push(int& sp, const uint2 v) { loc[sp++] = v; }
+    __device__ __forceinline__ void push(int& sp, const uint2 v) { loc[PT_IDX(sp, PT_STACK, PT_CHK_STACK)] = v; sp++; }
     __device__ __forceinline__ uint2 pop(int& sp) { return loc[--sp]; }
     __device__ __forceinline__ uint2 peek(int sp) const { return loc[sp - 1]; }
 #endif
@@ -150,20 +150,30 @@ struct LaneState {
 struct QueueIO {                // the wavefront queues: SoA float4 streams
     const float4* rayO; const float4* rayD; float4* hits; const float4* lights; float4* accucolors;
     const uint* perm;           // ray sorting (k_sort_*): fetch position -> queue index, nullptr = queue order
+#if defined(PT_BOUNDS_CHECK)
+    struct { struct { uint queueCap, nSlots; } chk; } sc;      // what PT_LIM looks at inside this struct
+#endif
+    __device__ __forceinline__ void limits(const DScene& scene) {
+#if defined(PT_BOUNDS_CHECK)
+        sc.chk.queueCap = scene.chk.queueCap; sc.chk.nSlots = scene.chk.nSlots;
+#else
+        (void)scene;
+#endif
+    }
     static constexpr bool kStreams = true;      // rays are two contiguous float4 streams: a fetch window can be staged with bulk copies
     __device__ __forceinline__ uint index(uint i) const { return perm ? perm[i] : i; }
-    __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const { o4 = rayO[i]; d4 = rayD[i]; }
+    __device__ __forceinline__ void load(uint i, float4& o4, float4& d4) const { i = PT_IDX(i, PT_LIM(queueCap), PT_CHK_QUEUE); o4 = rayO[i]; d4 = rayD[i]; }
     __device__ __forceinline__ void window(uint base, float4*& o, float4*& d) const { o = const_cast<float4*>(rayO + base); d = const_cast<float4*>(rayD + base); }
     template <bool ANY> __device__ __forceinline__ void store(uint i, const LaneState& L) const {
         if (ANY) {
             if (L.hitId == PT_NONE) {                                         // unoccluded: kernels.h:806-809
-                const uint slot = __float_as_uint(rayD[i].w);
+                const uint slot = PT_IDX(__float_as_uint(rayD[PT_IDX(i, PT_LIM(queueCap), PT_CHK_QUEUE)].w), PT_LIM(nSlots), PT_CHK_SLOT);
                 const float4 l = lights[slot];
                 float4 a = accucolors[slot];
                 a.x += l.x; a.y += l.y; a.z += l.z;
                 accucolors[slot] = a;
             }
-        } else hits[i] = make_float4(__uint_as_float(L.hitType), __uint_as_float(L.hitId), __uint_as_float(L.hitInst), L.tbest);
+        } else hits[PT_IDX(i, PT_LIM(queueCap), PT_CHK_QUEUE)] = make_float4(__uint_as_float(L.hitType), __uint_as_float(L.hitId), __uint_as_float(L.hitInst), L.tbest);
     }
 };
 struct DebugIO {                // reference-format rays in, reference-format hits out (pt_debug_trace)
@@ -245,21 +255,21 @@ struct Tally {
 // One top-level step for the TLAS node L.curT (kernels.h:320-386): a leaf enters its instance
 // (transformRay, kernels.h:81-86), an inner node tests both children in the reference's order.
 __device__ __forceinline__ void tlasStep(const DScene& sc, LaneState& L, TravStack& stack) {
-    const pt_tlas_node cur = sc.tlas[L.curT];
+    const pt_tlas_node cur = sc.tlas[PT_IDX(L.curT, PT_LIM(numTlas), PT_CHK_TLAS)];
     L.curT = PT_NONE;
     if (cur.children == 0) {
-        const pt_instance& inst = sc.instances[cur.leaf];
+        const pt_instance& inst = sc.instances[PT_IDX(cur.leaf, sc.num_instances, PT_CHK_INSTANCE)];
         const float3 nd = normalize(matmul(inst.invTransform, L.d, 0.0f));
         const float3 no = matmul(inst.invTransform, L.o, 1.0f);
         L.o = no; L.d = nd;
         setModelSpaceDir(L);
         L.tcull = L.tbest * 1.000001f;      // slack: box distances are not computed like triangle distances
         L.curInst = cur.leaf; L.inBLAS = true; L.found = false; L.spBase = L.sp;
-        L.ngroup = make_uint2(sc.models[inst.model_id].rootNode, 0x80000000u);
+        L.ngroup = make_uint2(sc.models[PT_IDX(inst.model_id, PT_LIM(numModels), PT_CHK_MODEL)].rootNode, 0x80000000u);
     } else {
         const uint near_id = cur.children & 0xffffu, far_id = (cur.children >> 16) & 0xffffu;
-        const pt_tlas_node nn = sc.tlas[near_id];
-        const pt_tlas_node ff = sc.tlas[far_id];
+        const pt_tlas_node nn = sc.tlas[PT_IDX(near_id, PT_LIM(numTlas), PT_CHK_TLAS)];
+        const pt_tlas_node ff = sc.tlas[PT_IDX(far_id, PT_LIM(numTlas), PT_CHK_TLAS)];
         float tnear, tfar;
         const bool bnear = slabTestRef(L.o, L.idir, &nn.vmin.x, &nn.vmax.x, tnear) && tnear < L.tbest;
         const bool bfar = slabTestRef(L.o, L.idir, &ff.vmin.x, &ff.vmax.x, tfar) && tfar < L.tbest;
@@ -281,7 +291,7 @@ __device__ __forceinline__ void blasNodeStep(const DScene& sc, LaneState& L, Tra
     if (ngroup.y > 0x00FFFFFFu) { stack.push(L.sp, ngroup); }
     const uint slot = (bit - 24u) ^ L.octinv;
     const uint rel = __popc(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
-    const float4* np = sc.nodes + (size_t)(ngroup.x + rel) * 5;
+    const float4* np = sc.nodes + (size_t)PT_IDX(ngroup.x + rel, PT_LIM(numNodes), PT_CHK_NODE) * 5;
     const float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
     const uint ew = __float_as_uint(n0.w);
     const float sx = __uint_as_float((ew & 0xffu) << 23), sy = __uint_as_float(((ew >> 8) & 0xffu) << 23), sz = __uint_as_float(((ew >> 16) & 0xffu) << 23);
@@ -328,7 +338,7 @@ __device__ __forceinline__ bool triStep(const DScene& sc, LaneState& L, const bo
         tally.tri();
         const uint ti = 31u - __clz(L.tgroup.y);
         L.tgroup.y &= ~(1u << ti);
-        const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
+        const float4* tp = sc.wtris + (size_t)PT_IDX(L.tgroup.x + ti, PT_LIM(numWtris), PT_CHK_WTRI) * 3;
         const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
         float t, u, v;
         if (triIntersect(L.o, L.d, f3(a), f3(b), f3(c), t, u, v)) {
@@ -424,7 +434,7 @@ __device__ __forceinline__ void triQueueRound(const DScene& sc, const LaneState&
     const float dx = __shfl_sync(0xffffffffu, L.d.x, owner), dy = __shfl_sync(0xffffffffu, L.d.y, owner), dz = __shfl_sync(0xffffffffu, L.d.z, owner);
     if (valid) {
         tally.tri();
-        const float4* tp = sc.wtris + (size_t)(e & 0x07FFFFFFu) * 3;
+        const float4* tp = sc.wtris + (size_t)PT_IDX(e & 0x07FFFFFFu, PT_LIM(numWtris), PT_CHK_WTRI) * 3;
         const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
         float t, u, v;
         if (triIntersect(f3(ox, oy, oz), f3(dx, dy, dz), f3(a), f3(b), f3(c), t, u, v))
@@ -588,7 +598,7 @@ __device__ __forceinline__ void coopNodeStep(const DScene& sc, LaneState& L, Tra
     if (ngroup.y > 0x00FFFFFFu) { stack.push(L.sp, ngroup); }
     const uint slot = (bit - 24u) ^ L.octinv;
     const uint rel = __popc(ngroup.y & ~(0xFFFFFFFFu << slot) & 0xFFu);
-    const float4* np = sc.nodes + (size_t)(ngroup.x + rel) * 5;
+    const float4* np = sc.nodes + (size_t)PT_IDX(ngroup.x + rel, PT_LIM(numNodes), PT_CHK_NODE) * 5;
     const float4 n0 = ldg4(np), n1 = ldg4(np + 1);
     const unsigned char* nb = reinterpret_cast<const unsigned char*>(np);
     const uint meta = __ldg(nb + 24 + sub);
@@ -620,7 +630,7 @@ __device__ __forceinline__ bool coopTriStep(const DScene& sc, LaneState& L, cons
     unsigned long long key = ~0ull;
     if (ti != 0xffffffffu) {
         tally.tri();
-        const float4* tp = sc.wtris + (size_t)(L.tgroup.x + ti) * 3;
+        const float4* tp = sc.wtris + (size_t)PT_IDX(L.tgroup.x + ti, PT_LIM(numWtris), PT_CHK_WTRI) * 3;
         const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
         float t, u, v;
         if (triIntersect(L.o, L.d, f3(a), f3(b), f3(c), t, u, v)) key = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(a.w);   // t > 0: bit order == numeric order

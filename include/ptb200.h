@@ -302,6 +302,11 @@ PT_API int  pt_debug_trace_resident(pt_ctx*, const pt_ray* host_rays, uint32_t n
 #define PT_STATIC_SCRATCH_BYTES (256u + PT_STATIC_TRACE_MAX_RAYS * 48u)
 PT_API int  pt_trace_static(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, pt_hit* host_out);
 
+/* Bounds-checked build only (make -C cuda_pathtracer_b200/csrc variant NAME=_chk DEFS=-DPT_BOUNDS_CHECK; compute-sanitizer is not
+ * available on the GPU pool): every index the kernels form is compared with its array's extent; out4 = failures since the last
+ * report, code / index / limit of the first.  Other builds answer PT_ERR_INVALID.  pt_version() names the build. */
+PT_API int  pt_debug_check_report(pt_ctx*, uint32_t* out4);
+
 PT_API void* pt_cuda_stream(pt_ctx*);
 
 /* Tile partition, host-callable without a GPU: 32x32-pixel tiles dealt round-robin to
