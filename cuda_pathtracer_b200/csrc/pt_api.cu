@@ -656,6 +656,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
     std::vector<WideNode> nodes; std::vector<WideTri> wtris; std::vector<DModel> models(d->num_models);
     uint32_t maxWide = 0;
     const bool hostWide = (ctx->cfg.flags & PT_FLAG_HOST_WIDE_BVH) || getenv("PTB200_HOST_WIDE_BVH");
+    const bool wideGreedy = getenv("PTB200_WIDE_GREEDY") != nullptr;          // developer knob: round 1's largest-area collapse instead of the SAH-optimal one (A/B)
     float4 *dn = nullptr, *dt = nullptr; pt_triangle_v* dv = nullptr;
     int r;
     for (uint32_t m = 0; m < d->num_models; m++)
@@ -667,7 +668,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
         for (uint32_t m = 0; m < d->num_models; m++) {
             const pt_model& pm = d->models[m];
             WideBuildStats st;
-            models[m].rootNode = buildWideBVH(pm.bvh, pm.nrBvhNodes, d->vertices, nodes, wtris, &st);
+            models[m].rootNode = buildWideBVH(pm.bvh, pm.nrBvhNodes, d->vertices, nodes, wtris, &st, !wideGreedy);
             models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;
             maxWide = std::max(maxWide, st.max_depth);
             if (st.tris != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
@@ -684,7 +685,8 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
         const size_t tmpBytes = wideScanTempBytes(maxBound + 1);
         struct Scratch { std::vector<void*> p; ~Scratch() { for (void* q : p) cudaFree(q); } } scratch;
         auto scratchAlloc = [&](void** out, size_t bytes) { cudaError_t e = cudaMalloc(out, std::max<size_t>(bytes, 256)); if (e == cudaSuccess) scratch.p.push_back(*out); return e; };
-        void *tmpNodes, *refs, *counts, *scan, *tmp, *dBvh2;
+        void *tmpNodes, *refs, *counts, *scan, *tmp, *dBvh2, *dpScratch = nullptr;
+        if (!wideGreedy) CK(scratchAlloc(&dpScratch, wideDpScratchBytes((uint32_t)maxBvh2)));
         CK(scratchAlloc(&tmpNodes, nodeCap * sizeof(WideNode))); CK(scratchAlloc(&refs, maxBound * 8)); CK(scratchAlloc(&counts, (maxBound + 1) * 8));
         CK(scratchAlloc(&scan, (maxBound + 1) * 8)); CK(scratchAlloc(&tmp, tmpBytes)); CK(scratchAlloc(&dBvh2, maxBvh2 * sizeof(pt_bvh_node)));
         if ((r = devAlloc(ctx, (WideTri**)&dt, triCap, true))) return r;
@@ -694,7 +696,7 @@ PT_API int pt_upload_scene(pt_ctx* ctx, const pt_scene_desc* d) {
             CK(cudaMemcpyAsync(dBvh2, pm.bvh, (size_t)pm.nrBvhNodes * sizeof(pt_bvh_node), cudaMemcpyHostToDevice, ctx->stream));
             uint32_t nUsed = 0, tUsed = 0, depth = 0; const char* err = "";
             r = buildWideBVHDevice(ctx->stream, (const pt_bvh_node*)dBvh2, pm.nrBvhNodes, dv, (WideNode*)tmpNodes, nodeCursor, (WideTri*)dt, triCursor,
-                                   refs, counts, scan, tmp, tmpBytes, &nUsed, &tUsed, &depth, &err);
+                                   refs, counts, scan, tmp, tmpBytes, &nUsed, &tUsed, &depth, &err, dpScratch);
             if (r) return fail(ctx, r, err);
             if (tUsed != pm.nrTriangles) return fail(ctx, PT_ERR_INVALID, "pt_upload_scene: BVH leaves do not cover the model's triangles");
             models[m].rootNode = nodeCursor; models[m].triangleStart = pm.triangleStart; models[m].nrTriangles = pm.nrTriangles; models[m].pad = 0;

@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include <deque>
+#include <utility>
 
 namespace ptb {
 namespace {
@@ -21,7 +22,7 @@ struct Box3 {
 
 // Temporary binary tree: the reference BVH2 with every leaf cut down to <= 3 triangles (the wide node
 // encodes a leaf's triangle count in 3 unary bits).  Triangle ranges stay in reference order.
-struct TNode { Box3 box; int left, right; uint32_t first, count; };
+struct TNode { Box3 box; int left, right; uint32_t first, count; bool virt; };   // virt: made by cutting a reference leaf (not a node of the reference tree)
 
 static Box3 triBounds(const pt_triangle_v* tris, uint32_t first, uint32_t count) {
     Box3 b; b.reset();
@@ -30,7 +31,7 @@ static Box3 triBounds(const pt_triangle_v* tris, uint32_t first, uint32_t count)
 }
 
 static int splitLeaf(std::vector<TNode>& t, const pt_triangle_v* tris, uint32_t first, uint32_t count, const Box3* known) {
-    TNode n; n.left = n.right = -1; n.first = first; n.count = count;
+    TNode n; n.left = n.right = -1; n.first = first; n.count = count; n.virt = true;
     n.box = known ? *known : triBounds(tris, first, count);
     int idx = (int)t.size(); t.push_back(n);
     if (count > 3) {
@@ -55,7 +56,7 @@ static int convert(std::vector<TNode>& t, const pt_bvh_node* bvh2, const pt_tria
         int idx;
         if (count > 0) idx = splitLeaf(t, tris, first, count, &box);
         else {
-            TNode n; n.box = box; n.left = n.right = -1; n.first = 0; n.count = 0;
+            TNode n; n.box = box; n.left = n.right = -1; n.first = 0; n.count = 0; n.virt = false;
             idx = (int)t.size(); t.push_back(n);
             stack.push_back({first + 1, idx, true});
             stack.push_back({first, idx, false});
@@ -67,13 +68,22 @@ static int convert(std::vector<TNode>& t, const pt_bvh_node* bvh2, const pt_tria
     return rootIdx;
 }
 
+// table of a cut reference leaf, looked at `depthLeft` cuts deep (wide_bvh.h WB_DP_RANGE_DEPTH; the device converter's rangeTable)
+static void virtTable(const std::vector<TNode>& t, int n, int depthLeft, WideDP& out) {
+    if (t[n].left < 0) { wdpLeaf(out); return; }
+    if (depthLeft == 0) { wdpOpaque(out, t[n].box.area()); return; }
+    WideDP L, R;
+    virtTable(t, t[n].left, depthLeft - 1, L); virtTable(t, t[n].right, depthLeft - 1, R);
+    wdpCombine(out, L, R, t[n].box.area());
+}
+
 static inline uint32_t fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 static inline float bitsf(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
 }  // namespace
 
 uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangle_v* triangles,
-                      std::vector<WideNode>& nodes, std::vector<WideTri>& tris, WideBuildStats* stats) {
+                      std::vector<WideNode>& nodes, std::vector<WideTri>& tris, WideBuildStats* stats, bool optimal) {
     (void)n_bvh2;
     std::vector<TNode> t;
     t.reserve(n_bvh2 * 2);
@@ -88,6 +98,42 @@ uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangl
     double sah = 0.0;
     const float rootArea = std::max(t[troot].box.area(), 1e-30f);
 
+    // ---- SAH-optimal collapse (wide_bvh.h): tables of the reference tree's nodes, children before parents ----
+    std::vector<WideDP> D;
+    bool dp = optimal;
+    if (dp) {
+        std::vector<int> order; order.reserve(t.size());
+        std::vector<std::pair<int, uint32_t>> st; st.push_back({troot, 0});
+        uint32_t deepest = 0;
+        while (!st.empty()) {                                  // reference-tree nodes only: a cut leaf is one unit here
+            const int n = st.back().first; const uint32_t lvl = st.back().second; st.pop_back();
+            order.push_back(n); deepest = std::max(deepest, lvl);
+            if (!t[n].virt && t[n].left >= 0) { st.push_back({t[n].left, lvl + 1}); st.push_back({t[n].right, lvl + 1}); }
+        }
+        if (deepest >= WB_DP_MAX_LEVELS) dp = false;           // the device converter walks a bounded number of levels: same rule here
+        else {
+            D.resize(t.size());
+            for (size_t q = order.size(); q-- > 0;) {
+                const int n = order[q];
+                if (t[n].virt || t[n].left < 0) virtTable(t, n, WB_DP_RANGE_DEPTH, D[n]);
+                else wdpCombine(D[n], D[t[n].left], D[t[n].right], t[n].box.area());
+            }
+        }
+    }
+    // children of the wide node rooted at a subtree: depth-first, left before right, each subtree within its budget
+    struct Cover {
+        const std::vector<TNode>& t; const std::vector<WideDP>& D; int* ch; int& nch;
+        void table(int n, WideDP& out) const { if (t[n].virt) virtTable(t, n, WB_DP_RANGE_DEPTH, out); else out = D[n]; }
+        void run(int n, int budget) {
+            if (t[n].left < 0) { ch[nch++] = n; return; }
+            WideDP d; table(n, d);
+            const int b = wdpEffective(d, budget);
+            if (b == 1) { ch[nch++] = n; return; }
+            const int k = d.k[b - 1];
+            run(t[n].left, k); run(t[n].right, b - k);
+        }
+    };
+
     while (!queue.empty()) {
         Work w = queue.front(); queue.pop_front();
         maxDepth = std::max(maxDepth, w.depth);
@@ -95,8 +141,9 @@ uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangl
         // ---- collapse: open the child with the largest surface area until 8 children ----
         int ch[8]; int nch = 0;
         if (r.left < 0) ch[nch++] = w.tnode;                 // degenerate model: the root itself is a leaf
+        else if (dp) { Cover cov{t, D, ch, nch}; WideDP d; cov.table(w.tnode, d); const int k = d.k[7]; cov.run(r.left, k); cov.run(r.right, 8 - k); }
         else { ch[nch++] = r.left; ch[nch++] = r.right; }
-        while (nch < 8) {
+        while (!dp && nch < 8) {
             int best = -1; float bestArea = -1.0f;
             for (int i = 0; i < nch; i++)
                 if (t[ch[i]].left >= 0) { float a = t[ch[i]].box.area(); if (a > bestArea) { bestArea = a; best = i; } }

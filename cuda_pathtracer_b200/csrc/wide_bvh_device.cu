@@ -60,15 +60,86 @@ __device__ __forceinline__ float boxArea(const TInfo& t) {
     return (x < 0 || y < 0 || z < 0) ? 0.0f : 2.0f * (x * y + x * z + y * z);
 }
 
+// ---- SAH-optimal collapse (wide_bvh.h): tables ------------------------------------------------------------------------------
+__device__ __forceinline__ float rangeArea(const pt_triangle_v* tris, uint first, uint count) {
+    float lo[3], hi[3]; rangeBounds(tris, first, count, lo, hi);
+    const float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+    return (x < 0 || y < 0 || z < 0) ? 0.0f : 2.0f * (x * y + x * z + y * z);
+}
+// table of the triangle range of a cut reference leaf (wide_bvh.cpp virtTable); `area` = surface area of the range's own box
+template <int DEPTH>
+__device__ void rangeTable(const pt_triangle_v* tris, uint first, uint count, float area, WideDP& out) {
+    if (count <= 3) { wdpLeaf(out); return; }
+    if constexpr (DEPTH == 0) { wdpOpaque(out, area); }
+    else {
+        const uint lc = count / 2;
+        WideDP L, R;
+        rangeTable<DEPTH - 1>(tris, first, lc, lc > 3 ? rangeArea(tris, first, lc) : 0.0f, L);
+        rangeTable<DEPTH - 1>(tris, first + lc, count - lc, count - lc > 3 ? rangeArea(tris, first + lc, count - lc) : 0.0f, R);
+        wdpCombine(out, L, R, area);
+    }
+}
+struct DPView { const WideDP* table; };      // table == nullptr: greedy collapse
+__device__ void tableOf(const DPView& dp, const pt_triangle_v* tris, const TInfo& t, WideDP& out) {
+    if (t.self.b == 0) out = dp.table[t.self.a];
+    else rangeTable<WB_DP_RANGE_DEPTH>(tris, t.first, t.count, boxArea(t), out);
+}
+// one level of the reference tree, children before parents (k_dp_level runs the levels bottom-up)
+__global__ void __launch_bounds__(WB_THREADS) k_dp_expand(const float4* bvh2, uint* order, uint* lvl, uint level, uint maxNodes) {
+    const uint begin = lvl[level], end = lvl[level + 1];
+    for (uint i = begin + blockIdx.x * WB_THREADS + threadIdx.x; i < end; i += gridDim.x * WB_THREADS) {
+        const uint n = order[i];
+        const float4 lo = bvh2[2 * (size_t)n], hi = bvh2[2 * (size_t)n + 1];
+        if (__float_as_uint(hi.w) != 0u) continue;                     // leaf
+        const uint first = __float_as_uint(lo.w);
+        const uint pos = atomicAdd(&lvl[WB_DP_MAX_LEVELS + 2], 2u);    // running end of the list (order inside a level is free)
+        if (pos + 1 < maxNodes) { order[pos] = first; order[pos + 1] = first + 1; }
+    }
+}
+__global__ void k_dp_close(uint* lvl, uint level, uint maxNodes) { lvl[level + 2] = min(lvl[WB_DP_MAX_LEVELS + 2], maxNodes); }
+__global__ void __launch_bounds__(WB_THREADS) k_dp_level(const float4* bvh2, const pt_triangle_v* tris, const uint* order, const uint* lvl, uint level, WideDP* table) {
+    const uint begin = lvl[level], end = lvl[level + 1];
+    for (uint i = begin + blockIdx.x * WB_THREADS + threadIdx.x; i < end; i += gridDim.x * WB_THREADS) {
+        const uint n = order[i];
+        const float4 lo = bvh2[2 * (size_t)n], hi = bvh2[2 * (size_t)n + 1];
+        const float x = hi.x - lo.x, y = hi.y - lo.y, z = hi.z - lo.z;
+        const float area = (x < 0 || y < 0 || z < 0) ? 0.0f : 2.0f * (x * y + x * z + y * z);
+        const uint first = __float_as_uint(lo.w), count = __float_as_uint(hi.w);
+        WideDP d;
+        if (count == 0) wdpCombine(d, table[first], table[first + 1], area);
+        else rangeTable<WB_DP_RANGE_DEPTH>(tris, first, count, area, d);
+        table[n] = d;
+    }
+}
+
 // collapse + slot assignment of one wide node (wide_bvh.cpp "collapse" and "assign children to slots")
 struct Collapsed { TInfo root; TInfo ch[8]; int childIn[8]; int nch; };
 
-__device__ void collapse(const float4* bvh2, const pt_triangle_v* tris, TRef ref, Collapsed& c) {
+__device__ void collapse(const float4* bvh2, const pt_triangle_v* tris, TRef ref, Collapsed& c, const DPView dp) {
     loadRef(bvh2, tris, ref, c.root);
     c.nch = 0;
     if (!c.root.internal) c.ch[c.nch++] = c.root;                      // degenerate model: the root itself is a leaf
+    else if (dp.table) {
+        // optimal cover (wide_bvh.cpp Cover::run): depth-first, left before right, every subtree within its budget
+        WideDP d; tableOf(dp, tris, c.root, d);
+        const int k = d.k[7];
+        TRef stackRef[8]; int stackBudget[8]; int sp = 0;
+        stackRef[sp] = c.root.right; stackBudget[sp++] = 8 - k;
+        stackRef[sp] = c.root.left; stackBudget[sp++] = k;
+        while (sp > 0) {
+            --sp;
+            const int budget = stackBudget[sp];
+            TInfo t; loadRef(bvh2, tris, stackRef[sp], t);
+            int b = 1;
+            if (t.internal) { tableOf(dp, tris, t, d); b = wdpEffective(d, budget); }
+            if (b == 1) { c.ch[c.nch++] = t; continue; }
+            const int kl = d.k[b - 1];
+            stackRef[sp] = t.right; stackBudget[sp++] = b - kl;
+            stackRef[sp] = t.left; stackBudget[sp++] = kl;
+        }
+    }
     else { loadRef(bvh2, tris, c.root.left, c.ch[0]); loadRef(bvh2, tris, c.root.right, c.ch[1]); c.nch = 2; }
-    while (c.nch < 8) {
+    while (!dp.table && c.nch < 8) {
         int best = -1; float bestArea = -1.0f;
         for (int i = 0; i < c.nch; i++)
             if (c.ch[i].internal) { const float a = boxArea(c.ch[i]); if (a > bestArea) { bestArea = a; best = i; } }
@@ -98,12 +169,12 @@ __device__ void collapse(const float4* bvh2, const pt_triangle_v* tris, TRef ref
 }
 
 // pass 1 of a level: how many internal children / leaf triangles each wide node will emit
-__global__ void __launch_bounds__(WB_THREADS) k_wide_count(const float4* bvh2, const pt_triangle_v* tris, const TRef* refs, uint levelBegin, uint levelSize, u64* counts) {
+__global__ void __launch_bounds__(WB_THREADS) k_wide_count(const float4* bvh2, const pt_triangle_v* tris, const TRef* refs, uint levelBegin, uint levelSize, u64* counts, const DPView dp) {
     const uint i = blockIdx.x * WB_THREADS + threadIdx.x;
     if (i > levelSize) return;
     if (i == levelSize) { counts[i] = 0; return; }
     Collapsed c;
-    collapse(bvh2, tris, refs[levelBegin + i], c);
+    collapse(bvh2, tris, refs[levelBegin + i], c, dp);
     uint nInternal = 0, nTris = 0;
     for (int s = 0; s < 8; s++) {
         if (c.childIn[s] < 0) continue;
@@ -115,11 +186,11 @@ __global__ void __launch_bounds__(WB_THREADS) k_wide_count(const float4* bvh2, c
 
 // pass 2: write the node, its triangle records and the references of its internal children
 __global__ void __launch_bounds__(WB_THREADS) k_wide_emit(const float4* bvh2, const pt_triangle_v* tris, TRef* refs, uint levelBegin, uint levelSize, const u64* scan,
-                                                           uint nodeBase, uint triCursor, WideNode* nodes, WideTri* wtris) {
+                                                           uint nodeBase, uint triCursor, WideNode* nodes, WideTri* wtris, const DPView dp) {
     const uint i = blockIdx.x * WB_THREADS + threadIdx.x;
     if (i >= levelSize) return;
     Collapsed c;
-    collapse(bvh2, tris, refs[levelBegin + i], c);
+    collapse(bvh2, tris, refs[levelBegin + i], c, dp);
     const TInfo& r = c.root;
     uint ebyte[3]; float scale[3];
     for (int a = 0; a < 3; a++) {                                                           // quantisation frame
@@ -187,20 +258,45 @@ size_t wideNodeBound(uint32_t n_bvh2, uint32_t n_tris) { return (size_t)(n_bvh2 
 // `refs` (wideNodeBound entries of 8 bytes), `counts` and `scan` (wideNodeBound + 1 u64 each) and `tmp` are scratch.
 int buildWideBVHDevice(cudaStream_t st, const pt_bvh_node* d_bvh2, uint32_t n_bvh2, const pt_triangle_v* d_tris, WideNode* d_nodes, uint32_t nodeBase,
                        WideTri* d_wtris, uint32_t triBase, void* refsScratch, void* countsScratch, void* scanScratch, void* tmp, size_t tmpBytes,
-                       uint32_t* nodesUsed, uint32_t* trisUsed, uint32_t* maxDepth, const char** err) {
-    (void)n_bvh2;
+                       uint32_t* nodesUsed, uint32_t* trisUsed, uint32_t* maxDepth, const char** err, void* dpScratch) {
     TRef* refs = (TRef*)refsScratch; u64* counts = (u64*)countsScratch; u64* scan = (u64*)scanScratch;
     const TRef root{0, 0};
     cudaError_t e;
 #define WCK(call) do { e = (call); if (e != cudaSuccess) { *err = cudaGetErrorString(e); return PT_ERR_CUDA; } } while (0)
     WCK(cudaMemcpyAsync(refs, &root, sizeof root, cudaMemcpyHostToDevice, st));
+    // ---- SAH-optimal collapse: the reference tree level by level (lists), then the tables from the deepest level up ----
+    DPView dp{nullptr};
+    if (dpScratch && n_bvh2) {
+        // scratch: [table n_bvh2 x 36 B][order n_bvh2 x 4 B][lvl (WB_DP_MAX_LEVELS + 3) x 4 B: level starts, then the running end]
+        WideDP* table = (WideDP*)dpScratch;
+        uint* order = (uint*)((char*)dpScratch + (((size_t)n_bvh2 * sizeof(WideDP) + 255) & ~(size_t)255));
+        uint* lvl = order + (((size_t)n_bvh2 + 63) & ~(size_t)63);
+        uint head[WB_DP_MAX_LEVELS + 3];
+        for (int i = 0; i < WB_DP_MAX_LEVELS + 3; i++) head[i] = 0;
+        head[1] = 1; head[WB_DP_MAX_LEVELS + 2] = 1;                       // level 0 = [0, 1): the root, order[0] = 0
+        WCK(cudaMemcpyAsync(lvl, head, sizeof head, cudaMemcpyHostToDevice, st));
+        WCK(cudaMemsetAsync(order, 0, sizeof(uint), st));
+        const uint grid = std::max(1u, std::min((n_bvh2 + WB_THREADS - 1) / WB_THREADS, 1184u));
+        for (uint l = 0; l < WB_DP_MAX_LEVELS; l++) {
+            k_dp_expand<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, order, lvl, l, n_bvh2);
+            k_dp_close<<<1, 1, 0, st>>>(lvl, l, n_bvh2);
+        }
+        uint tailLevel[2] = {0, 0};                                         // lvl[MAX], lvl[MAX + 1]: nodes on level WB_DP_MAX_LEVELS = the tree is too deep
+        WCK(cudaMemcpyAsync(tailLevel, lvl + WB_DP_MAX_LEVELS, sizeof tailLevel, cudaMemcpyDeviceToHost, st));
+        WCK(cudaStreamSynchronize(st));
+        if (tailLevel[1] == tailLevel[0]) {
+            for (int l = WB_DP_MAX_LEVELS - 1; l >= 0; l--)
+                k_dp_level<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, order, lvl, (uint)l, table);
+            dp.table = table;
+        }
+    }
     uint levelBegin = 0, levelSize = 1, triCursor = triBase, depth = 0;
     while (levelSize) {
         const uint grid1 = (levelSize + 1 + WB_THREADS - 1) / WB_THREADS, grid = (levelSize + WB_THREADS - 1) / WB_THREADS;
-        k_wide_count<<<grid1, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, refs, levelBegin, levelSize, counts);
+        k_wide_count<<<grid1, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, refs, levelBegin, levelSize, counts, dp);
         size_t need = tmpBytes;
         WCK(cub::DeviceScan::ExclusiveSum(tmp, need, counts, scan, (int)(levelSize + 1), st));
-        k_wide_emit<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, refs, levelBegin, levelSize, scan, nodeBase, triCursor, d_nodes, d_wtris);
+        k_wide_emit<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, refs, levelBegin, levelSize, scan, nodeBase, triCursor, d_nodes, d_wtris, dp);
         u64 totals = 0;
         WCK(cudaMemcpyAsync(&totals, scan + levelSize, sizeof totals, cudaMemcpyDeviceToHost, st));
         WCK(cudaStreamSynchronize(st));
@@ -210,6 +306,10 @@ int buildWideBVHDevice(cudaStream_t st, const pt_bvh_node* d_bvh2, uint32_t n_bv
 #undef WCK
     *nodesUsed = levelBegin; *trisUsed = triCursor - triBase; *maxDepth = depth;
     return PT_OK;
+}
+
+size_t wideDpScratchBytes(uint32_t n_bvh2) {
+    return (((size_t)n_bvh2 * sizeof(WideDP) + 255) & ~(size_t)255) + ((((size_t)n_bvh2 + 63) & ~(size_t)63) + WB_DP_MAX_LEVELS + 3) * sizeof(uint32_t);
 }
 
 size_t wideScanTempBytes(size_t maxItems) {
