@@ -1,6 +1,6 @@
 #!/bin/bash
 # One-GPU evidence session of round 2: parity suite, smoke, the bench line as the driver runs it (+ a long run), the ncu launch list
-# of the same command and full captures of the traversal kernels.  gpurun --timeout 1500 -- 'bash tools/r2_final1.sh TAG'
+# of the same command (full captures: tools/r2_ncu.sh, tools/r2_ncu_shade.sh, one ncu pass per call).  gpurun --timeout 1500 -- 'bash tools/r2_final1.sh TAG'
 TAG=${1:-r2g}
 mkdir -p gpurun_out
 S=$(date +%s)
@@ -12,6 +12,4 @@ timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/$
 timeout 100 python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu list exit $? $(( $(date +%s)-S ))s"
-timeout 300 ncu --set full --clock-control none --import-source on -k "regex:k_trace|k_tail" -s 8 -c 18 -o gpurun_out/${TAG}_trace -f python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu2.log 2>&1
-echo "ncu full exit $? $(( $(date +%s)-S ))s"
 ls -la gpurun_out | grep ${TAG}
