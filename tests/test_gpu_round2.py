@@ -228,3 +228,39 @@ def test_bad_top_level_records_are_rejected(sibenik):
     pt.peer_disconnect()
     assert pt.L.pt_upload_scene(pt.h, C.byref(desc)) >= 0
     pt.close()
+
+
+def test_optimal_wide_collapse_same_hits_every_triangle_once_less_work(sibenik, monkeypatch):
+    """The SAH-optimal collapse (csrc/wide_bvh.h) only changes how the reference's BVH2 is cut into 8-wide nodes: the same
+    triangles, each exactly once, the same hits bit for bit -- and fewer node steps than round 1's largest-area rule
+    (PTB200_WIDE_GREEDY), counted by the traversal kernel itself."""
+    arrays, cam = sibenik
+    cfg = abi.default_config(320, 180, max_ray_depth=8, interactive_depth=1)
+    got = {}
+    for rule in ("greedy", "optimal"):
+        if rule == "greedy":
+            monkeypatch.setenv("PTB200_WIDE_GREEDY", "1")
+        else:
+            monkeypatch.delenv("PTB200_WIDE_GREEDY", raising=False)
+        pt = api.Pathtracer(arrays, cfg).Init()
+        nodes, tris = pt.debug_read_wide_bvh()
+        rays = pt.debug_primary_rays(cam, 0)
+        hits = pt.debug_trace(rays, False)
+        occl = pt.debug_trace(rays, True)
+        pt.HNEE, pt.HCACHE = True, False
+        pt.Render(cam, shouldClear=True)
+        pt.set_counting(True)
+        for _ in range(3):
+            pt.Render(cam)
+        pt.Finish()
+        got[rule] = dict(nodes=len(nodes), ids=np.sort(tris.view(np.uint32).reshape(len(tris), -1)[:, 3]), hits=hits, occl=occl["primitive_id"] != 0xFFFFFFFF,
+                         tally=pt.tally(), img=pt.read_image().copy())
+        pt.close()
+    g, o = got["greedy"], got["optimal"]
+    n_tri = len(arrays["vertices"])
+    assert np.array_equal(o["ids"], np.arange(n_tri, dtype=np.uint32)) and np.array_equal(g["ids"], o["ids"])
+    assert o["hits"].tobytes() == g["hits"].tobytes() and np.array_equal(o["occl"], g["occl"])
+    assert np.array_equal(o["img"], g["img"])
+    print("wide nodes greedy %d optimal %d; node steps of the extension rays %d -> %d, shadow rays %d -> %d" %
+          (g["nodes"], o["nodes"], g["tally"]["extend"][0], o["tally"]["extend"][0], g["tally"]["connect"][0], o["tally"]["connect"][0]))
+    assert o["tally"]["extend"][0] < 0.98 * g["tally"]["extend"][0] and o["tally"]["connect"][0] < 0.98 * g["tally"]["connect"][0]
