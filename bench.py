@@ -395,10 +395,14 @@ def gpu_arm(args):
     # N > 1: the same loop with the framebuffer in process-shared HOST memory (pt_host_ring_*): every rank stores its own tiles
     # through its own PCIe link, rank 0's process takes delivery of whole (H, W, 4) frames in place -- rank 0's link no longer
     # carries all 33 MB of every frame.
-    ring_s, ring_rays, ring_ok = None, None, None
+    ring_s, ring_rays, ring_ok, ring_note, hr = None, None, None, None, None
     if gathered:
         from cuda_pathtracer_b200.distributed import HostRing
-        hr = HostRing(pt, slots=4)
+        try:
+            hr = HostRing(pt, slots=4)                 # raises on EVERY rank when /dev/shm cannot hold the ring (decided by rank 0)
+        except RuntimeError as ex:
+            hr, ring_note = None, str(ex)
+    if gathered and hr is not None:
         epochs = []
         restart()
         pt.reset_stats()
@@ -426,7 +430,7 @@ def gpu_arm(args):
         hr.close()
     e2 = torch.tensor([est.extend_rays + est.shadow_rays, e2e_s, bst.extend_rays + bst.shadow_rays, blocking_s], dtype=torch.float64, device="cuda")
     ring_value = None
-    if gathered:
+    if gathered and hr is not None:
         rr = torch.tensor([ring_rays], dtype=torch.float64, device="cuda"); dist.all_reduce(rr)
         rt = torch.tensor([ring_s], dtype=torch.float64, device="cuda"); dist.all_reduce(rt, op=dist.ReduceOp.MAX)
         ring_value = float(rr.item()) / float(rt.item()) / 1e6
@@ -478,7 +482,7 @@ def gpu_arm(args):
                         "image_complete": image_ok if not use_ring else ring_ok,
                         "delivery": None if not gathered else {
                             "through_rank0_link": {"value": e2e_value, "image_complete": image_ok, "how": "pt_gather_image_async: tiles over NVLink into rank 0's HBM image ring, one D2H copy per frame through rank 0's PCIe link"},
-                            "through_all_links": {"value": ring_value, "image_complete": ring_ok, "how": "pt_host_ring_* (distributed.HostRing): the framebuffer ring lives in process-shared host memory, every rank stores its own tiles through its own PCIe link, rank 0's process takes delivery of frame k-3 each step in place"},
+                            "through_all_links": {"value": ring_value, "image_complete": ring_ok, "skipped": ring_note, "how": "pt_host_ring_* (distributed.HostRing): the framebuffer ring lives in process-shared host memory, every rank stores its own tiles through its own PCIe link, rank 0's process takes delivery of frame k-3 each step in place"},
                             "value_is": "through_all_links" if use_ring else "through_rank0_link"},
                         "mode": ("streaming: per step Render(camera) + " + ("pt_deliver_image_async: every rank's tiles through its own PCIe link into ONE (H,W,4) float4 framebuffer in process-shared host memory, taken in place by rank 0's process" if use_ring else
                                  "pt_gather_image_async: every rank's tiles over NVLink into rank 0's image ring, ONE (H,W,4) float4 image to rank 0's pinned host memory" if gathered else

@@ -236,8 +236,8 @@ class Pathtracer:
     def host_ring_attach(self, block, slots):
         """block: writable uint8 buffer over process-shared host memory (distributed.HostRing creates one per job),
         abi.HOST_RING_HEADER_BYTES + slots * H * W * 16 bytes, zero-filled by its creator."""
-        self._ring_block = block                       # keep the mapping alive while the GPU writes into it
         self._ck(self.L.pt_host_ring_attach(self.h, abi.ptr(block), block.nbytes, int(slots)), "pt_host_ring_attach")
+        self._ring_block = block                       # keep the mapping alive while the GPU writes into it
 
     def host_ring_detach(self):
         self._ck(self.L.pt_host_ring_detach(self.h), "pt_host_ring_detach")

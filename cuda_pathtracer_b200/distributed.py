@@ -108,10 +108,19 @@ class HostRing:
         if world > 1:
             import torch.distributed as dist
         self.owner = pt.cfg.rank == 0
-        names = [name or ("/dev/shm/ptb200_ring_%d_%d" % (os.getpid(), id(self) & 0xffff))]
+        names = [name or ("/dev/shm/ptb200_ring_%d_%d" % (os.getpid(), id(self) & 0xffff)), True]
+        if self.owner:                                 # a container may cap /dev/shm (64 MB by default): refuse on every rank rather than fault on a page
+            try:
+                st = os.statvfs(os.path.dirname(names[0]))
+                names[1] = st.f_bavail * st.f_frsize >= nbytes + (8 << 20)
+            except OSError:
+                names[1] = False
         if world > 1:
             dist.broadcast_object_list(names, src=0, group=group)
         self.path = names[0]
+        if not names[1]:
+            self.pt = None
+            raise RuntimeError("HostRing: not enough room in %s for %d bytes of shared framebuffers" % (os.path.dirname(self.path), nbytes))
         if self.owner:
             with open(self.path, "wb") as f:
                 f.truncate(nbytes)                     # sparse file of zeros: header and images start at 0
@@ -120,10 +129,27 @@ class HostRing:
         self._f = open(self.path, "r+b")
         self._map = mmap.mmap(self._f.fileno(), nbytes)
         self.block = np.frombuffer(self._map, dtype=np.uint8)
-        pt.host_ring_attach(self.block, self.slots)
-        if world > 1:
-            dist.barrier(group=group)
         self._group, self._dist = group, dist
+        ok, why = True, ""
+        try:
+            pt.host_ring_attach(self.block, self.slots)
+        except Exception as ex:                        # noqa: BLE001 -- agreed on by all ranks below
+            ok, why = False, str(ex)
+        oks = [(ok, why)]
+        if world > 1:
+            oks = [None] * world
+            dist.all_gather_object(oks, (ok, why), group=group)
+        if not all(o for o, _ in oks):                 # one rank could not map the block: nobody uses it
+            if ok:
+                pt.host_ring_detach()
+            self.block = None
+            self._map.close(); self._f.close()
+            if world > 1:
+                dist.barrier(group=group)
+            if self.owner:
+                os.unlink(self.path)
+            self.pt = None
+            raise RuntimeError("HostRing: " + "; ".join(w for o, w in oks if not o))
 
     def close(self):
         if self.pt is None:
