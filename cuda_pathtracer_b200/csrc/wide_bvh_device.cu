@@ -277,15 +277,21 @@ int buildWideBVHDevice(cudaStream_t st, const pt_bvh_node* d_bvh2, uint32_t n_bv
         WCK(cudaMemcpyAsync(lvl, head, sizeof head, cudaMemcpyHostToDevice, st));
         WCK(cudaMemsetAsync(order, 0, sizeof(uint), st));
         const uint grid = std::max(1u, std::min((n_bvh2 + WB_THREADS - 1) / WB_THREADS, 1184u));
-        for (uint l = 0; l < WB_DP_MAX_LEVELS; l++) {
-            k_dp_expand<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, order, lvl, l, n_bvh2);
-            k_dp_close<<<1, 1, 0, st>>>(lvl, l, n_bvh2);
+        // levels in chunks of 16 launches pairs; after each chunk the level starts come back and the walk stops at the first empty level
+        uint levels = 0; bool tooDeep = true;
+        for (uint l0 = 0; l0 < WB_DP_MAX_LEVELS && tooDeep; l0 += 16) {
+            for (uint l = l0; l < l0 + 16 && l < WB_DP_MAX_LEVELS; l++) {
+                k_dp_expand<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, order, lvl, l, n_bvh2);
+                k_dp_close<<<1, 1, 0, st>>>(lvl, l, n_bvh2);
+            }
+            WCK(cudaMemcpyAsync(head, lvl, sizeof head, cudaMemcpyDeviceToHost, st));
+            WCK(cudaStreamSynchronize(st));
+            const uint upTo = std::min<uint>(l0 + 16, WB_DP_MAX_LEVELS);
+            for (uint l = l0; l <= upTo; l++)
+                if (head[l] == head[l + 1]) { levels = l; tooDeep = false; break; }      // level l is empty: the tree has l levels
         }
-        uint tailLevel[2] = {0, 0};                                         // lvl[MAX], lvl[MAX + 1]: nodes on level WB_DP_MAX_LEVELS = the tree is too deep
-        WCK(cudaMemcpyAsync(tailLevel, lvl + WB_DP_MAX_LEVELS, sizeof tailLevel, cudaMemcpyDeviceToHost, st));
-        WCK(cudaStreamSynchronize(st));
-        if (tailLevel[1] == tailLevel[0]) {
-            for (int l = WB_DP_MAX_LEVELS - 1; l >= 0; l--)
+        if (!tooDeep) {                                                     // nodes on level WB_DP_MAX_LEVELS: too deep, greedy rule (as the host converter)
+            for (int l = (int)levels - 1; l >= 0; l--)
                 k_dp_level<<<grid, WB_THREADS, 0, st>>>((const float4*)d_bvh2, d_tris, order, lvl, (uint)l, table);
             dp.table = table;
         }
