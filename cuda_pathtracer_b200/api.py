@@ -93,6 +93,7 @@ def load_library():
     L.pt_deliver_image_async.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
     L.pt_host_ring_wait.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(C.c_float))]
     L.pt_host_ring_release.argtypes = [C.c_void_p, C.c_uint64]
+    L.pt_host_wide_bvh.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_double), C.POINTER(C.c_uint32)]
     L.pt_debug_check_report.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
     L.pt_debug_trace_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.POINTER(C.c_float), C.c_void_p]
     _LIB = L
@@ -464,3 +465,19 @@ def check_report():
     if r != 0:
         raise PtError("pt_debug_check_report failed (%d)" % r)
     return tuple(int(x) for x in out)
+
+
+def host_wide_bvh(bvh2, triangles, optimal=True):
+    """Host-only (no GPU): (nodes [n, 20] uint32, triangle records [m, 12] uint32, sah_cost, max_depth) of the 8-wide BVH the host
+    converter cuts from one model's BVH2 (abi.BVH_NODE array) over the scene's triangle array (abi.TRIANGLE_V)."""
+    L = load_library()
+    bvh2, triangles = np.ascontiguousarray(bvh2), np.ascontiguousarray(triangles)
+    nn, nt, cost, depth = C.c_uint32(), C.c_uint32(), C.c_double(), C.c_uint32()
+    r = L.pt_host_wide_bvh(abi.ptr(bvh2), len(bvh2), abi.ptr(triangles), int(bool(optimal)), None, C.byref(nn), None, C.byref(nt), None, None)
+    if r != 0:
+        raise PtError("pt_host_wide_bvh failed (%d)" % r)
+    nodes, tris = np.zeros((nn.value, 20), np.uint32), np.zeros((nt.value, 12), np.uint32)
+    r = L.pt_host_wide_bvh(abi.ptr(bvh2), len(bvh2), abi.ptr(triangles), int(bool(optimal)), abi.ptr(nodes), C.byref(nn), abi.ptr(tris), C.byref(nt), C.byref(cost), C.byref(depth))
+    if r != 0:
+        raise PtError("pt_host_wide_bvh failed (%d)" % r)
+    return nodes, tris, cost.value, depth.value

@@ -620,6 +620,21 @@ static int checkTopLevel(const pt_instance* inst, uint32_t n, const pt_tlas_node
 }
 
 // Test hook: the wide BVH as it sits on the device (80-byte nodes, 48-byte triangle records).  NULL pointers: sizes only.
+// Host-only (no GPU, no context): the BVH2 -> 8-wide conversion of ONE model as pt_upload_scene's host converter does it (wide_bvh.cpp).
+// nodes / wtris may be NULL (counts only); otherwise *n_nodes / *n_tris say how many entries the buffers hold.  optimal = 0: round 1's
+// largest-area collapse.  sah_cost (optional): sum over all children of area / root area x (1 per inner child, triangle count per leaf child).
+PT_API int pt_host_wide_bvh(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangle_v* triangles, int optimal,
+                            void* nodes, uint32_t* n_nodes, void* wtris, uint32_t* n_tris, double* sah_cost, uint32_t* max_depth) {
+    if (!bvh2 || !n_bvh2 || !triangles || !n_nodes || !n_tris) return PT_ERR_INVALID;
+    std::vector<WideNode> vn; std::vector<WideTri> vt; WideBuildStats st;
+    buildWideBVH(bvh2, n_bvh2, triangles, vn, vt, &st, optimal != 0);
+    if (nodes) { if (*n_nodes < vn.size()) return PT_ERR_INVALID; memcpy(nodes, vn.data(), vn.size() * sizeof(WideNode)); }
+    if (wtris) { if (*n_tris < vt.size()) return PT_ERR_INVALID; memcpy(wtris, vt.data(), vt.size() * sizeof(WideTri)); }
+    *n_nodes = (uint32_t)vn.size(); *n_tris = (uint32_t)vt.size();
+    if (sah_cost) *sah_cost = st.sah_cost;
+    if (max_depth) *max_depth = st.max_depth;
+    return PT_OK;
+}
 PT_API int pt_debug_read_wide_bvh(pt_ctx* ctx, void* nodes, uint32_t* n_nodes, void* tris, uint32_t* n_tris) {
     if (!ctx || !ctx->haveScene) return PT_ERR_INVALID;
     CK(cudaSetDevice(ctx->cfg.device));

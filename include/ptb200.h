@@ -302,6 +302,11 @@ PT_API int  pt_debug_trace_resident(pt_ctx*, const pt_ray* host_rays, uint32_t n
 #define PT_STATIC_SCRATCH_BYTES (256u + PT_STATIC_TRACE_MAX_RAYS * 48u)
 PT_API int  pt_trace_static(pt_ctx*, const pt_ray* host_rays, uint32_t n, int any_hit, pt_hit* host_out);
 
+/* Host-only, no GPU and no context: the BVH2 -> 8-wide conversion of one model exactly as pt_upload_scene's host converter does it (the device
+ * converter produces the same bytes).  No counterpart in the reference (its traversal walks the BVH2).  nodes (80 B each) / wtris (48 B each)
+ * may be NULL to ask for the counts; optimal = 0 selects round 1's largest-area collapse instead of the SAH-optimal one. */
+PT_API int  pt_host_wide_bvh(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangle_v* triangles_global, int optimal,
+                             void* nodes, uint32_t* n_nodes, void* wtris, uint32_t* n_tris, double* sah_cost, uint32_t* max_depth);
 /* Bounds-checked build only (make -C cuda_pathtracer_b200/csrc variant NAME=_chk DEFS=-DPT_BOUNDS_CHECK; compute-sanitizer is not
  * available on the GPU pool): every index the kernels form is compared with its array's extent; out4 = failures since the last
  * report, code / index / limit of the first.  Other builds answer PT_ERR_INVALID.  pt_version() names the build. */
