@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include <deque>
+#include <cstdlib>
 #include <utility>
 
 namespace ptb {
@@ -22,7 +23,7 @@ struct Box3 {
 
 // Temporary binary tree: the reference BVH2 with every leaf cut down to <= 3 triangles (the wide node
 // encodes a leaf's triangle count in 3 unary bits).  Triangle ranges stay in reference order.
-struct TNode { Box3 box; int left, right; uint32_t first, count; bool virt; };   // virt: made by cutting a reference leaf (not a node of the reference tree)
+struct TNode { Box3 box; int left, right; uint32_t first, count; bool virt; uint32_t mask; };   // mask != 0: the triangles first + i of the set bits i (a 4-triangle reference leaf cut by wbBestCut4); count = their number   // virt: made by cutting a reference leaf (not a node of the reference tree)
 
 static Box3 triBounds(const pt_triangle_v* tris, uint32_t first, uint32_t count) {
     Box3 b; b.reset();
@@ -30,11 +31,31 @@ static Box3 triBounds(const pt_triangle_v* tris, uint32_t first, uint32_t count)
     return b;
 }
 
+static bool wbCut4Enabled() { return getenv("PTB200_LEAF_INDEX_CUT") == nullptr; }      // developer knob: round 1's cut by index (A/B)
+
+static Box3 maskBounds(const pt_triangle_v* tris, uint32_t first, uint32_t mask) {
+    Box3 b; b.reset();
+    for (uint32_t i = 0; i < 4; i++) if (mask >> i & 1u) { b.grow(&tris[first + i].v0.x); b.grow(&tris[first + i].v1.x); b.grow(&tris[first + i].v2.x); }
+    return b;
+}
+
 static int splitLeaf(std::vector<TNode>& t, const pt_triangle_v* tris, uint32_t first, uint32_t count, const Box3* known) {
-    TNode n; n.left = n.right = -1; n.first = first; n.count = count; n.virt = true;
+    TNode n; n.left = n.right = -1; n.first = first; n.count = count; n.virt = true; n.mask = 0;
     n.box = known ? *known : triBounds(tris, first, count);
     int idx = (int)t.size(); t.push_back(n);
-    if (count > 3) {
+    if (count == 4 && wbCut4Enabled()) {
+        // the common leaf of the reference builder (it stops at <= 4 triangles): of the seven ways to cut four triangles into two leaves
+        // of <= 3, take the one with the least area x count (wide_bvh.h wbBestCut4; the device converter evaluates the same floats)
+        float area[16];
+        for (uint32_t m = 1; m < 15; m++) area[m] = maskBounds(tris, first, m).area();
+        const uint32_t lm = wbBestCut4(area);
+        for (int side = 0; side < 2; side++) {
+            TNode c; c.left = c.right = -1; c.first = first; c.mask = side ? (15u ^ lm) : lm; c.count = (uint32_t)__builtin_popcount(c.mask); c.virt = true;
+            c.box = maskBounds(tris, first, c.mask);
+            (side ? t[idx].right : t[idx].left) = (int)t.size(); t.push_back(c);
+        }
+        t[idx].count = 0;
+    } else if (count > 3) {
         uint32_t lc = count / 2;
         int l = splitLeaf(t, tris, first, lc, nullptr);
         int r = splitLeaf(t, tris, first + lc, count - lc, nullptr);
@@ -56,7 +77,7 @@ static int convert(std::vector<TNode>& t, const pt_bvh_node* bvh2, const pt_tria
         int idx;
         if (count > 0) idx = splitLeaf(t, tris, first, count, &box);
         else {
-            TNode n; n.box = box; n.left = n.right = -1; n.first = 0; n.count = 0; n.virt = false;
+            TNode n; n.box = box; n.left = n.right = -1; n.first = 0; n.count = 0; n.virt = false; n.mask = 0;
             idx = (int)t.size(); t.push_back(n);
             stack.push_back({first + 1, idx, true});
             stack.push_back({first, idx, false});
@@ -202,7 +223,8 @@ uint32_t buildWideBVH(const pt_bvh_node* bvh2, uint32_t n_bvh2, const pt_triangl
             } else {
                 static const uint8_t unary[4] = {0, 1, 3, 7};
                 meta = (uint8_t)((unary[cn.count] << 5) | triOffset);
-                for (uint32_t i = cn.first; i < cn.first + cn.count; i++) {
+                for (uint32_t i = cn.first; i < cn.first + (cn.mask ? 4u : cn.count); i++) {
+                    if (cn.mask && !(cn.mask >> (i - cn.first) & 1u)) continue;
                     const pt_triangle_v& tv = triangles[i];
                     WideTri wt; memset(&wt, 0, sizeof(wt));
                     wt.v0[0] = tv.v0.x; wt.v0[1] = tv.v0.y; wt.v0[2] = tv.v0.z; wt.id = i;

@@ -67,6 +67,23 @@ WB_HD inline void wdpCombine(WideDP& d, const WideDP& L, const WideDP& R, float 
 // children a subtree may take out of `budget`: the largest budget that still pays (k != 0), 1 = the subtree stays one child
 WB_HD inline int wdpEffective(const WideDP& d, int budget) { while (budget > 1 && d.k[budget - 1] == 0) budget--; return budget; }
 
+// ---- cutting the reference builder's usual leaf -------------------------------------------------------------------------------
+// createBVHBinned stops at <= 4 triangles, a wide leaf child holds <= 3: three of four reference leaves (sibenik proxy: 28,585 of 37,583)
+// have to be cut in two.  Round 1 cut by index (2 + 2 in reference order); wbBestCut4 picks, of the seven cuts {a | bcd} x 4 and
+// {ab | cd} x 3, the one with the least sum of area x triangle count.  area[m] = surface area of the box of the triangles in bit mask m
+// (1..14).  Returns the mask of the left leaf; ties go to the first cut in this order.  Shared by both converters.
+WB_HD inline uint32_t wbBestCut4(const float* area) {
+    const uint32_t cuts[7] = {3u, 5u, 6u, 1u, 2u, 4u, 8u};          // left masks: the three pairings (the one holding triangle 0 on the left), then each single
+    uint32_t best = 3u; float bestCost = 3.0e38f;
+    for (int i = 0; i < 7; i++) {
+        const uint32_t l = cuts[i], r = 15u ^ l;
+        const float nl = i < 3 ? 2.0f : 1.0f, nr = i < 3 ? 2.0f : 3.0f;
+        const float c = area[l] * nl + area[r] * nr;
+        if (c < bestCost) { bestCost = c; best = l; }
+    }
+    return best;
+}
+
 struct WideBuildStats { uint32_t nodes, leaves, tris, max_depth; double sah_cost; };
 
 // Appends the wide BVH of one model to `nodes` / `tris` (indices stored in nodes are absolute).

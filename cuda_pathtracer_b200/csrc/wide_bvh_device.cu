@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <cub/device/device_scan.cuh>
 #include "wide_bvh.h"
@@ -18,15 +19,17 @@ typedef unsigned int uint;
 typedef unsigned long long u64;
 #define WB_THREADS 128
 
-// A node of the temporary binary tree of wide_bvh.cpp, by reference: b == 0 -> BVH2 node a; b > 0 -> the triangle
-// range [a, a + b) of a BVH2 leaf that was cut down to <= 3 triangles per leaf.
+// A node of the temporary binary tree of wide_bvh.cpp, by reference: b == 0 -> BVH2 node a; b > 0 -> triangles of a BVH2 leaf that
+// was cut down to <= 3 triangles per leaf: the range [a, a + (b & 0xFFFFFF)), or -- b >> 24 != 0 -- the triangles a + i of the set
+// bits i of that 4-bit mask (one side of a 4-triangle leaf cut by wbBestCut4, wide_bvh.h).
 struct TRef { uint a, b; };
 struct TInfo {
     float lo[3], hi[3];
     TRef self, left, right;
-    uint first, count;
+    uint first, count, mask;      // mask != 0: count = its population; the triangles are first + i of its set bits
     bool internal;
 };
+__constant__ int c_cut4;          // 1: 4-triangle leaves are cut by wbBestCut4, 0: by index (PTB200_LEAF_INDEX_CUT, as the host converter)
 
 __device__ __forceinline__ float stdmin(float a, float b) { return (b < a) ? b : a; }     // std::min / std::max operand rules
 __device__ __forceinline__ float stdmax(float a, float b) { return (a < b) ? b : a; }
@@ -40,19 +43,44 @@ __device__ void rangeBounds(const pt_triangle_v* tris, uint first, uint count, f
     }
 }
 
+__device__ void maskBounds(const pt_triangle_v* tris, uint first, uint mask, float* lo, float* hi) {
+    for (int a = 0; a < 3; a++) { lo[a] = 3.0e38f; hi[a] = -3.0e38f; }
+    for (uint i = 0; i < 4; i++) {
+        if (!(mask >> i & 1u)) continue;
+        const float* p = &tris[first + i].v0.x;
+        for (int v = 0; v < 3; v++)
+            for (int a = 0; a < 3; a++) { lo[a] = stdmin(lo[a], p[3 * v + a]); hi[a] = stdmax(hi[a], p[3 * v + a]); }
+    }
+}
+__device__ uint bestCut4(const pt_triangle_v* tris, uint first) {
+    float area[16];
+    for (uint m = 1; m < 15; m++) {
+        float lo[3], hi[3]; maskBounds(tris, first, m, lo, hi);
+        const float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+        area[m] = (x < 0 || y < 0 || z < 0) ? 0.0f : 2.0f * (x * y + x * z + y * z);
+    }
+    return wbBestCut4(area);
+}
+
 __device__ void loadRef(const float4* bvh2, const pt_triangle_v* tris, TRef r, TInfo& t) {
-    t.self = r;
+    t.self = r; t.mask = 0;
     if (r.b == 0) {
         const float4 lo = bvh2[2 * (size_t)r.a], hi = bvh2[2 * (size_t)r.a + 1];
         t.lo[0] = lo.x; t.lo[1] = lo.y; t.lo[2] = lo.z; t.hi[0] = hi.x; t.hi[1] = hi.y; t.hi[2] = hi.z;
         t.first = __float_as_uint(lo.w); t.count = __float_as_uint(hi.w);
         if (t.count == 0) { t.internal = true; t.left = TRef{t.first, 0}; t.right = TRef{t.first + 1, 0}; return; }
+    } else if (r.b >> 24) {
+        t.first = r.a; t.mask = r.b >> 24; t.count = (uint)__popc(t.mask);
+        maskBounds(tris, r.a, t.mask, t.lo, t.hi);
     } else {
         t.first = r.a; t.count = r.b;
         rangeBounds(tris, r.a, r.b, t.lo, t.hi);
     }
     t.internal = t.count > 3;
-    if (t.internal) { const uint lc = t.count / 2; t.left = TRef{t.first, lc}; t.right = TRef{t.first + lc, t.count - lc}; }
+    if (t.internal && t.count == 4 && c_cut4) {
+        const uint lm = bestCut4(tris, t.first), rm = 15u ^ lm;
+        t.left = TRef{t.first, (uint)__popc(lm) | (lm << 24)}; t.right = TRef{t.first, (uint)__popc(rm) | (rm << 24)};
+    } else if (t.internal) { const uint lc = t.count / 2; t.left = TRef{t.first, lc}; t.right = TRef{t.first + lc, t.count - lc}; }
 }
 
 __device__ __forceinline__ float boxArea(const TInfo& t) {
@@ -220,13 +248,15 @@ __global__ void __launch_bounds__(WB_THREADS) k_wide_emit(const float4* bvh2, co
         } else {
             const unsigned char unary[4] = {0, 1, 3, 7};
             meta = (unsigned char)((unary[cn.count] << 5) | triOffset);
-            for (uint t = cn.first; t < cn.first + cn.count; t++) {
+            uint k = 0;
+            for (uint t = cn.first; t < cn.first + (cn.mask ? 4u : cn.count); t++) {
+                if (cn.mask && !(cn.mask >> (t - cn.first) & 1u)) continue;
                 const pt_triangle_v tv = tris[t];
                 WideTri wt;
                 wt.v0[0] = tv.v0.x; wt.v0[1] = tv.v0.y; wt.v0[2] = tv.v0.z; wt.id = t;
                 wt.e1[0] = tv.v1.x - tv.v0.x; wt.e1[1] = tv.v1.y - tv.v0.y; wt.e1[2] = tv.v1.z - tv.v0.z; wt.pad1 = 0;   // kernels.h:171
                 wt.e2[0] = tv.v2.x - tv.v0.x; wt.e2[1] = tv.v2.y - tv.v0.y; wt.e2[2] = tv.v2.z - tv.v0.z; wt.pad2 = 0;   // kernels.h:172
-                wtris[triBase + triOffset + (t - cn.first)] = wt;
+                wtris[triBase + triOffset + k++] = wt;
             }
             triOffset += cn.count;
         }
@@ -264,6 +294,7 @@ int buildWideBVHDevice(cudaStream_t st, const pt_bvh_node* d_bvh2, uint32_t n_bv
     cudaError_t e;
 #define WCK(call) do { e = (call); if (e != cudaSuccess) { *err = cudaGetErrorString(e); return PT_ERR_CUDA; } } while (0)
     WCK(cudaMemcpyAsync(refs, &root, sizeof root, cudaMemcpyHostToDevice, st));
+    { const int cut4 = getenv("PTB200_LEAF_INDEX_CUT") ? 0 : 1; WCK(cudaMemcpyToSymbolAsync(c_cut4, &cut4, sizeof cut4, 0, cudaMemcpyHostToDevice, st)); }
     // ---- SAH-optimal collapse: the reference tree level by level (lists), then the tables from the deepest level up ----
     DPView dp{nullptr};
     if (dpScratch && n_bvh2) {

@@ -17,7 +17,7 @@ if len(sys.argv) > 1:
         VARIANTS.append((name, dict(kv.split("=", 1) for kv in rest.split(";") if kv) if rest else {}))
 arrays = scenes.sibenik_scene().arrays()
 cams = scenes.camera_sweep("sibenik", 1920, 1080, 16)
-KNOBS = ["PTB200_NO_PDL", "PTB200_SORT", "PTB200_TAIL_BOUNCE", "PTB200_MIN_WIDTH", "PTB200_SETS", "PTB200_NO_TAIL_PAIR", "PTB200_COOP", "PTB200_TAIL_GRID", "PTB200_TAIL_PAIR_MAX", "PTB200_PDL_ALWAYS", "PTB200_NO_MIX", "PTB200_TAIL_ALONE", "PTB200_NO_FEEDBACK", "PTB200_HEAD_AT", "PTB200_ANY_FAR_FIRST", "PTB200_SPLIT", "PTB200_HOST_WIDE_BVH", "PTB200_WIDE_GREEDY"]
+KNOBS = ["PTB200_NO_PDL", "PTB200_SORT", "PTB200_TAIL_BOUNCE", "PTB200_MIN_WIDTH", "PTB200_SETS", "PTB200_NO_TAIL_PAIR", "PTB200_COOP", "PTB200_TAIL_GRID", "PTB200_TAIL_PAIR_MAX", "PTB200_PDL_ALWAYS", "PTB200_NO_MIX", "PTB200_TAIL_ALONE", "PTB200_NO_FEEDBACK", "PTB200_HEAD_AT", "PTB200_ANY_FAR_FIRST", "PTB200_SPLIT", "PTB200_HOST_WIDE_BVH", "PTB200_WIDE_GREEDY", "PTB200_LEAF_INDEX_CUT"]
 
 
 def measure(world, env):
